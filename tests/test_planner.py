@@ -1,0 +1,66 @@
+"""Planner properties (hypothesis) and exactness of the decomposition: np in {1..8} output ==
+np=1 output — the property the reference's V2.2/V4 decomposition fails."""
+import pytest
+import torch
+from hypothesis import given, settings, strategies as st
+
+from b200cnn import default_config
+from b200cnn.config import INIT_RAND
+from b200cnn.models.init import make_problem
+from b200cnn.models.alexnet import forward_cpu
+from b200cnn.parallel.planner import make_plan, validate_plan, split_rows
+from b200cnn.parallel.emulate import forward_cpu_decomposed
+
+
+def test_split_rows_matches_reference_rule():
+    # base = H/size, first H%size ranks get one more (ref v2.2 main.cpp:102-109)
+    assert split_rows(227, 2) == [(0, 114), (114, 227)]
+    assert [b - a for a, b in split_rows(13, 8)] == [2, 2, 2, 2, 2, 1, 1, 1]
+    assert [b - a for a, b in split_rows(3, 5)] == [1, 1, 1, 0, 0]
+
+
+def test_plan_227_np2_rows():
+    plan = make_plan(default_config(), 2)
+    validate_plan(plan)
+    r0, r1 = plan.ranks
+    assert r0.out_rows == (0, 7) and r1.out_rows == (7, 13)
+    assert r0.conv2_rows == (0, 15) and r1.conv2_rows == (14, 27)
+    assert r0.pool1_need == (0, 17) and r1.pool1_need == (12, 27)
+    assert r0.pool1_own == (0, 14) and r1.pool1_own == (14, 27)
+    assert r0.halo == [(1, 14, 17)] and r1.halo == [(0, 12, 14)]
+    # receptive field of App. A.3: input rows [16a-16, 16b+50] clipped (recompute strategy)
+    rc = make_plan(default_config(), 2, "recompute")
+    assert rc.ranks[1].in_rows == (16 * 7 - 16, 227)
+
+
+@settings(max_examples=150, deadline=None)
+@given(H=st.integers(35, 700), world=st.integers(1, 12),
+       strategy=st.sampled_from(["halo", "recompute"]))
+def test_plan_invariants(H, world, strategy):
+    plan = make_plan(default_config(H=H, W=67), world, strategy)
+    validate_plan(plan)
+    for rp in plan.ranks:
+        if rp.active:
+            # input slab is large enough for every conv1 row the rank computes
+            q0, q1 = rp.conv1_rows
+            assert rp.in_rows[0] <= 4 * q0 and 4 * (q1 - 1) + 11 <= rp.in_rows[1]
+
+
+@pytest.mark.parametrize("world", [2, 3, 4, 8])
+@pytest.mark.parametrize("strategy", ["halo", "recompute"])
+def test_decomposed_equals_whole_227(world, strategy):
+    cfg = default_config(init=INIT_RAND, seed=11)
+    x, w = make_problem(cfg)
+    ref = forward_cpu(x, w, cfg)
+    got = forward_cpu_decomposed(x, w, cfg, world, strategy)
+    assert got.shape == ref.shape == (1, 13, 13, 256)
+    assert torch.equal(got, ref)        # same op order per output => bit-identical
+
+
+def test_decomposed_more_ranks_than_rows():
+    cfg = default_config(H=83, W=83, batch=2, init=INIT_RAND, seed=5)   # 4 final rows
+    x, w = make_problem(cfg)
+    ref = forward_cpu(x, w, cfg)
+    assert ref.shape[1] == 4
+    got = forward_cpu_decomposed(x, w, cfg, 6)
+    assert torch.equal(got, ref)
