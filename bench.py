@@ -1,0 +1,191 @@
+#!/usr/bin/env python
+"""Headline benchmark: AlexNet blocks 1-2 forward, images/s, row-decomposed over N B200s.
+
+Config (BASELINE.json #3): 227x227x3 fp32 inputs, batch 128, synthetic data (V1 rand() stream),
+random-init weights, spatial row decomposition with peer-memory scatter/halo/gather, TF32
+tensor-core kernels (the reference computes in fp32; --precision simt gives the exact-fp32 twin).
+
+    python bench.py [--gpus N --steps K --warmup W]              # our framework
+    python bench.py --impl reference [...]                       # unmodified reference (baseline/_ref)
+
+For N>1 launch with torchrun (one rank per GPU).  Rank 0 prints ONE JSON line.
+  value      device-timed images/s: CUDA events around each forward on the launching stream, L2
+             flushed between timed iterations (outside the events), max over ranks.
+  e2e.value  images/s through the public API (b200cnn.models.session.Session): every step copies
+             its input from pinned host memory, runs the forward, and copies the result back.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+# Reference's published best V4 images/s per np (best_runs.csv:10-12; other HW).
+REF_V4_BEST_IMG_S = {1: 1 / 0.183, 2: 1 / 0.181, 4: 1 / 0.250}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--batch", type=int, default=128)
+    ap.add_argument("--height", type=int, default=227)
+    ap.add_argument("--width", type=int, default=227)
+    ap.add_argument("--precision", choices=["tf32", "simt"], default=None)
+    ap.add_argument("--strategy", choices=["halo", "recompute"], default="halo")
+    ap.add_argument("--scatter", choices=["p2p", "sharded"], default="p2p",
+                    help="device-timed run: where the images live (p2p = all on rank 0, pulled by conv1)")
+    ap.add_argument("--e2e-scatter", choices=["p2p", "sharded"], default="sharded",
+                    help="end-to-end run: p2p = rank 0 feeds everything; sharded = each rank feeds its slab")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def run_ours(a):
+    import torch
+    import b200cnn
+    from b200cnn.config import INIT_RAND
+    from b200cnn.models.init import make_problem
+    from b200cnn.models.session import Session
+    from b200cnn.parallel import dist as bdist
+    from b200cnn.utils.clocks import ClockSampler, rejected
+
+    ctx = bdist.init()
+    if ctx.world != a.gpus:
+        if ctx.is_root:
+            sys.stderr.write(f"bench: --gpus {a.gpus} but WORLD_SIZE={ctx.world}; using WORLD_SIZE\n")
+    N = ctx.world
+    precision = a.precision
+    if precision is None:
+        try:
+            from b200cnn.ops import tc  # noqa: F401
+            precision = "tf32"
+        except ImportError:
+            precision = "simt"
+    cfg = b200cnn.default_config(H=a.height, W=a.width, batch=a.batch, init=INIT_RAND, seed=1,
+                                 precision=precision)
+    x, w = make_problem(cfg)             # synthetic inputs, random-init weights (same on every rank)
+    dev = ctx.device
+    torch.cuda.set_device(dev)
+
+    def measure_device(sess):
+        e = sess.engine
+        if e.in_rows > 0:
+            lo, hi = sess.input_rows
+            for i in range(2):
+                e.input_view(i).copy_(x[:, lo:hi].to(dev))
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+        for _ in range(a.warmup):
+            e.forward_enqueue(0, 0)
+        torch.cuda.synchronize(dev)
+        ctx.barrier()
+        torch.cuda.synchronize(dev)
+        sampler = ClockSampler(dev.index or 0).start()
+        l0 = e.launches
+        total_ms = 0.0
+        for i in range(a.steps):
+            flush.fill_(i & 0xFF)                # evict L2 (not timed)
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record()
+            e.forward_enqueue(i % 2, i % 2)
+            ev1.record()
+            ev1.synchronize()
+            total_ms += ev0.elapsed_time(ev1)
+        torch.cuda.synchronize(dev)
+        ctx.barrier()
+        clocks = sampler.stop()
+        launches = e.launches - l0
+        e.check_status()
+        del flush
+        return ctx.max_float(total_ms), launches, clocks
+
+    def measure_e2e(sess):
+        e = sess.engine
+        lo, hi = sess.input_rows
+        hx = None
+        if e.in_rows > 0:
+            hx = [x[:, lo:hi].contiguous().pin_memory() for _ in range(2)]
+        for i in range(max(a.warmup, 3)):
+            sess.submit(hx[i % 2] if hx else None)
+        sess.drain()
+        ctx.barrier()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        tickets = []
+        for i in range(a.steps):
+            tickets.append(sess.submit(hx[i % 2] if hx else None))
+            if len(tickets) >= 2:        # keep <= 2 steps in flight, consume results in order
+                sess.result(tickets.pop(0))
+        for t in tickets:
+            sess.result(t)
+        sess.drain()
+        torch.cuda.synchronize(dev)
+        ms = (time.perf_counter() - t0) * 1e3
+        e.check_status()
+        return ctx.max_float(ms), sess.h2d_bytes, sess.d2h_bytes
+
+    sess = Session(cfg, w, dist=ctx if N > 1 else None, device=dev, precision=precision,
+                   strategy=a.strategy, scatter=a.scatter)
+    total_ms, launches, clocks = measure_device(sess)
+    if rejected(clocks):                                  # thermal/hw slowdown: re-measure once
+        total_ms, launches, clocks = measure_device(sess)
+    clocks.pop("samples", None)
+    e2e = None
+    if not a.no_e2e:
+        if a.e2e_scatter != a.scatter and N > 1:
+            del sess
+            torch.cuda.empty_cache()
+            sess = Session(cfg, w, dist=ctx, device=dev, precision=precision,
+                           strategy=a.strategy, scatter=a.e2e_scatter)
+        e2e_ms, h2d, d2h = measure_e2e(sess)
+        h2d_all = sum(ctx.all_gather_object(h2d))
+        d2h_all = sum(ctx.all_gather_object(d2h))
+        e2e = {"value": round(a.batch * a.steps / (e2e_ms / 1e3), 2), "unit": "images/s",
+               "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": d2h_all,
+               "scatter": a.e2e_scatter if N > 1 else "local", "pipelined_steps_in_flight": 2}
+    ms_per_step = total_ms / a.steps
+    value = a.batch / (ms_per_step / 1e3)
+    base = REF_V4_BEST_IMG_S.get(N)
+    line = {
+        "metric": "AlexNet blk1-2 images/s (device-timed, max over ranks)",
+        "value": round(value, 2), "unit": "images/s", "n_gpus": N, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": round(value / base, 2) if base else None,
+        "dtype": "tf32 (fp32 in/out, fp32 accumulate)" if precision == "tf32" else "fp32",
+        "data": "synthetic (glibc rand() stream, seed 1), random-init weights",
+        "config": {"model": "AlexNet blocks 1-2 (conv1-relu-pool1-conv2-relu-pool2-lrn2)",
+                   "global_batch": a.batch, "input": f"{a.height}x{a.width}x3",
+                   "parallelism": f"spatial-rows{N}" if N > 1 else "single-gpu",
+                   "strategy": a.strategy, "scatter": a.scatter if N > 1 else "local",
+                   "l2": "flushed between timed iterations (256 MiB fill, untimed)"},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "impl": "ours",
+    }
+    if ctx.is_root:
+        print(json.dumps(line), flush=True)
+    ctx.finalize()
+
+
+def run_reference(a):
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        import ref_arm
+    except Exception as ex:  # pragma: no cover
+        print(json.dumps({"impl": "reference", "unavailable": f"baseline/ref_arm.py: {ex}"}))
+        return
+    ref_arm.main(a)
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)

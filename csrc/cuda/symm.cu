@@ -1,0 +1,111 @@
+// Symmetric (peer-mapped) device memory and cross-GPU flag kernels.
+//
+// The reference moves every message through host std::vectors over TCP MPI
+// (ref v4_mpi_cuda/src/main_mpi_cuda.cpp:58-79,124-130).  Here each rank
+// cudaMalloc's a zeroed buffer, exports a CUDA IPC handle, and maps every peer's buffer into its
+// own address space; kernels then ld/st peer memory directly over NVLink 5 / NVSwitch.
+// torch.distributed is used only to exchange the 64-byte handles.
+//
+// Flag kernels implement MPI_Barrier's role (ref main_mpi_cuda.cpp:151,154) and the "gather
+// complete" notification on the device, stream-ordered, without host involvement.
+#include "common.cuh"
+
+#include <cstring>
+
+using namespace b200;
+
+extern "C" int b200_symm_alloc(size_t bytes, void** ptr) {
+    if (!ptr || bytes == 0) return B200_ERR_ARG;
+    B200_CUDA_TRY(cudaMalloc(ptr, bytes));
+    B200_CUDA_TRY(cudaMemset(*ptr, 0, bytes));
+    B200_CUDA_TRY(cudaDeviceSynchronize());
+    return B200_OK;
+}
+
+extern "C" int b200_symm_free(void* ptr) {
+    if (ptr) B200_CUDA_TRY(cudaFree(ptr));
+    return B200_OK;
+}
+
+extern "C" int b200_ipc_export(void* ptr, unsigned char* handle64) {
+    if (!ptr || !handle64) return B200_ERR_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    B200_CUDA_TRY(cudaIpcGetMemHandle(&h, ptr));
+    memcpy(handle64, &h, 64);
+    return B200_OK;
+}
+
+extern "C" int b200_ipc_open(const unsigned char* handle64, void** ptr) {
+    if (!ptr || !handle64) return B200_ERR_ARG;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    B200_CUDA_TRY(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return B200_OK;
+}
+
+extern "C" int b200_ipc_close(void* ptr) {
+    if (ptr) B200_CUDA_TRY(cudaIpcCloseMemHandle(ptr));
+    return B200_OK;
+}
+
+extern "C" int b200_can_access_peer(int dev, int peer) {
+    int ok = 0;
+    if (cudaDeviceCanAccessPeer(&ok, dev, peer) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return ok;
+}
+
+// Same-process peers (several GPUs driven by one process, or the single-GPU emulation): plain
+// cudaDeviceEnablePeerAccess instead of IPC.
+extern "C" int b200_enable_peer(int peer) {
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return B200_OK; }
+    B200_CUDA_TRY(e);
+    return B200_OK;
+}
+
+namespace {
+
+struct SignalArgs { int n; int* target[16]; };
+
+__global__ void flag_signal_kernel(SignalArgs a, int add) {
+    // stream order put every earlier kernel's stores before us; publish them system-wide, then bump
+    __threadfence_system();
+    if ((int)threadIdx.x < a.n) red_release_sys_add(a.target[threadIdx.x], add);
+}
+
+struct WaitArgs { int n; const int* flag[16]; int target[16]; };
+
+__global__ void flag_wait_kernel(WaitArgs a, int* status, unsigned long long timeout_ns) {
+    if ((int)threadIdx.x < a.n)
+        wait_flag_ge(a.flag[threadIdx.x], a.target[threadIdx.x], status, timeout_ns);
+    __syncthreads();
+    __threadfence_system();
+}
+
+}  // namespace
+
+// targets: up to 16 counters (local or peer); each gets += add
+extern "C" int b200_flag_signal(int* const* targets, int n, int add, void* stream) {
+    if (n < 0 || n > 16 || (n && !targets)) return B200_ERR_ARG;
+    if (n == 0) return B200_OK;
+    SignalArgs a;
+    a.n = n;
+    for (int i = 0; i < n; ++i) a.target[i] = targets[i];
+    flag_signal_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(a, add);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+// waits (on the stream) until flags[i] >= target[i] for all i; watchdog -> *status = TIMEOUT
+extern "C" int b200_flag_wait(const int* const* flags, const int* target, int n, int* status,
+                              unsigned long long timeout_ns, void* stream) {
+    if (n < 0 || n > 16 || (n && (!flags || !target))) return B200_ERR_ARG;
+    if (n == 0) return B200_OK;
+    WaitArgs a;
+    a.n = n;
+    for (int i = 0; i < n; ++i) { a.flag[i] = flags[i]; a.target[i] = target[i]; }
+    flag_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(a, status, timeout_ns);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}

@@ -1,0 +1,322 @@
+"""GPU engine for AlexNet blocks 1-2: resident weights and activations, two fused kernels per
+forward, peer-memory scatter / halo / gather.
+
+One :class:`Blocks12Engine` is one rank.  It is the replacement for the reference's L3
+orchestrators — ``alexnetForwardPassCUDA`` (10 cudaMalloc + 5 H2D + 7 launches + D2H + 10
+cudaFree per call, ref v3_cuda_only/src/alexnet_cuda.cu:22-95), ``alexnetTileForwardCUDA``
+(re-uploads 2.6 MB of weights per call, ref v4_mpi_cuda/src/alexnet_mpi_cuda.cu:157-205) and the
+decomposition logic inlined in V4's main (ref v4_mpi_cuda/src/main_mpi_cuda.cpp:52-130):
+
+* buffers are allocated once (symmetric memory), weights are packed and uploaded once;
+* block 1 = conv1+bias+ReLU+pool1 in ONE kernel whose loader pulls the input rows it needs from
+  rank 0's image buffer over NVLink (the scatter) and whose epilogue bumps per-image arrival
+  counters on the ranks that will read its pool1 rows;
+* block 2 = conv2+bias+ReLU+pool2+LRN in ONE kernel whose loader reads halo pool1 rows straight
+  from the owning peer (gated by those counters) and whose epilogue stores the final rows straight
+  into rank 0's output tensor (the gather);
+* a device-side barrier opens every forward and a completion counter closes it, so the whole
+  multi-GPU forward is stream-ordered with no host synchronisation.
+
+``precision``: ``"simt"`` exact FP32 (validation twin) or ``"tf32"`` tcgen05 tensor cores.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Optional
+
+import torch
+
+from ..config import NetConfig
+from ..ops import cuda as cu
+from ..ops._ctypes import LrnParams, LRN_MODES
+from ..parallel.planner import make_plan, Plan, RankPlan
+from ..parallel.symm import LocalSymm, DevBuf
+from .init import Blocks12Weights
+
+
+@dataclass
+class _Layout:
+    """int32 flag pad layout inside the per-rank "flags" buffer."""
+    world: int
+    nmax: int
+
+    @property
+    def arr_off(self):      # arrival counters [src_rank][image]
+        return 0
+
+    @property
+    def bar_off(self):      # barrier counters [src_rank]
+        return self.world * self.nmax
+
+    @property
+    def done_off(self):     # completion counters [src_rank]
+        return self.bar_off + self.world
+
+    @property
+    def status_off(self):
+        return self.done_off + self.world
+
+    @property
+    def count(self):
+        return self.status_off + 16
+
+
+class Blocks12Engine:
+    def __init__(self, cfg: NetConfig, weights: Blocks12Weights, symm, rank: int = 0,
+                 world: int = 1, *, precision: Optional[str] = None, strategy: str = "halo",
+                 scatter: str = "p2p", timeout_ns: int = cu.DEFAULT_TIMEOUT_NS):
+        if scatter not in ("p2p", "sharded"):
+            raise ValueError(scatter)
+        self.cfg = cfg
+        self.rank, self.world = rank, world
+        self.symm = symm
+        self.device = torch.device(symm.device)
+        self.precision = precision or cfg.precision
+        self.scatter = scatter
+        self.timeout_ns = timeout_ns
+        self.plan: Plan = make_plan(cfg, world, strategy)
+        self.rp: RankPlan = self.plan.ranks[rank]
+        self.sh = self.plan.shapes
+        self.epoch = 0
+        self.launches = 0            # kernels launched by this engine (bench reports it)
+        self.lay = _Layout(world, cfg.batch)
+        sh, rp, N = self.sh, self.rp, cfg.batch
+
+        # ---- weights: packed once, resident ------------------------------------------------
+        with torch.cuda.device(self.device):
+            self.b1 = weights.b1.to(self.device).contiguous()
+            self.b2 = weights.b2.to(self.device).contiguous()
+            if self.precision == "simt":
+                self.w1p = cu.pack_weights_ffck(weights.w1).to(self.device)
+                self.w2p = cu.pack_weights_ffck(weights.w2).to(self.device)
+            elif self.precision == "tf32":
+                from ..ops import tc
+                self.tc1 = tc.TcConv(weights.w1, self.device)
+                self.tc2 = tc.TcConv(weights.w2, self.device)
+            else:
+                raise ValueError(self.precision)
+
+        # ---- symmetric buffers ---------------------------------------------------------------
+        f4 = 4
+        self.n_in_buf = 2
+        if scatter == "p2p":
+            in_rows = sh.H if rank == 0 else 0
+            self.in_base = 0
+        else:
+            in_rows = rp.in_rows[1] - rp.in_rows[0]
+            self.in_base = rp.in_rows[0]
+        self.in_rows = in_rows
+        self.in_bytes = N * in_rows * sh.W * sh.C * f4
+        self.buf_in = [symm.alloc(f"in{i}", self.in_bytes) for i in range(self.n_in_buf)]
+        own = rp.pool1_own[1] - rp.pool1_own[0]
+        self.buf_pool1 = symm.alloc("pool1", N * own * sh.Wp1 * sh.K1 * f4)
+        out_rows = sh.Hp2 if rank == 0 else 0
+        self.n_out_buf = 2
+        self.buf_out = [symm.alloc(f"out{i}", N * out_rows * sh.Wp2 * sh.K2 * f4)
+                        for i in range(self.n_out_buf)]
+        self.buf_flags = symm.alloc("flags", self.lay.count * 4)
+        self._final = False
+
+    # ------------------------------------------------------------------------------------------
+    def finalize(self) -> None:
+        """Call after every rank allocated and ``symm.commit()`` ran: resolves peer pointers."""
+        self._final = True
+        if self.rank == 0:
+            sh = self.sh
+            self.outs = [b.tensor((self.cfg.batch, sh.Hp2, sh.Wp2, sh.K2)) for b in self.buf_out]
+        else:
+            self.outs = [None] * self.n_out_buf
+        self.out = self.outs[0]
+        self.flags_t = self.buf_flags.tensor((self.lay.count,), torch.int32)
+        # tiles per image of every rank's block 1 (arrival-counter targets)
+        self._b1_tiles = [self._tiles(self._geom_block1(r, probe=True)) for r in range(self.world)]
+
+    def _flag_ptr(self, rank: int, int_index: int) -> int:
+        return self.symm.ptr(rank, "flags") + 4 * int_index
+
+    def _tiles(self, g) -> int:
+        if self.precision == "simt":
+            return cu.simt_block_tiles(g)
+        from ..ops import tc
+        return tc.block_tiles(g)
+
+    # ---- geometry ------------------------------------------------------------------------------
+    def input_view(self, i: int = 0) -> torch.Tensor:
+        """This rank's input buffer ``i`` (rank 0 holds the whole batch in p2p-scatter mode)."""
+        sh = self.sh
+        return self.buf_in[i].tensor((self.cfg.batch, self.in_rows, sh.W, sh.C))
+
+    def _geom_block1(self, r: int, probe: bool = False, in_idx: int = 0):
+        cfg, sh, p1 = self.cfg, self.sh, self.cfg.conv1
+        rp = self.plan.ranks[r]
+        if probe:
+            segs = [dict(ptr=1, base=0, slab=sh.H, lo=0, hi=sh.H)]
+            signals, out_ptr = [], 0
+        else:
+            if self.scatter == "p2p":
+                segs = [dict(ptr=self.symm.ptr(0, f"in{in_idx}"), base=0, slab=sh.H, lo=0, hi=sh.H)]
+            else:
+                segs = [dict(ptr=self.buf_in[in_idx].ptr, base=self.in_base, slab=self.in_rows,
+                             lo=rp.in_rows[0], hi=rp.in_rows[1])]
+            signals = [self._flag_ptr(peer, self.lay.arr_off + r * self.lay.nmax)
+                       for peer in sorted({p for p, _, _ in rp.serves})]
+        g = cu.make_block_geom(
+            N=cfg.batch, H=sh.H, W=sh.W, Cin=sh.C, K=p1.K, F=p1.F, S=p1.S, P=p1.P,
+            Hc=sh.Hc1, Wc=sh.Wc1, Hp=sh.Hp1, Wp=sh.Wp1, rows=rp.pool1_own,
+            out_base=rp.pool1_own[0], out_slab=rp.pool1_own[1] - rp.pool1_own[0], lrn=None,
+            segs=segs, signals=signals,
+            status_ptr=0 if probe else self._flag_ptr(self.rank, self.lay.status_off),
+            timeout_ns=self.timeout_ns)
+        return g
+
+    def _geom_block2(self):
+        cfg, sh, p2, rp = self.cfg, self.sh, self.cfg.conv2, self.rp
+        own0, own1 = rp.pool1_own
+        segs = []
+        if own1 > own0:
+            segs.append(dict(ptr=self.buf_pool1.ptr, base=own0, slab=own1 - own0, lo=own0, hi=own1))
+        for peer, lo, hi in rp.halo:
+            po = self.plan.ranks[peer].pool1_own
+            segs.append(dict(ptr=self.symm.ptr(peer, "pool1"), base=po[0], slab=po[1] - po[0],
+                             lo=lo, hi=hi,
+                             flag=self._flag_ptr(self.rank, self.lay.arr_off + peer * self.lay.nmax),
+                             target=self.epoch * self._b1_tiles[peer]))
+        lrn = LrnParams(p2.N_lrn, p2.alpha, p2.beta, p2.k_lrn, LRN_MODES[cfg.lrn_mode])
+        return cu.make_block_geom(
+            N=cfg.batch, H=sh.Hp1, W=sh.Wp1, Cin=sh.K1, K=p2.K, F=p2.F, S=p2.S, P=p2.P,
+            Hc=sh.Hc2, Wc=sh.Wc2, Hp=sh.Hp2, Wp=sh.Wp2, rows=rp.out_rows,
+            out_base=0, out_slab=sh.Hp2, lrn=lrn, segs=segs, signals=[],
+            status_ptr=self._flag_ptr(self.rank, self.lay.status_off), timeout_ns=self.timeout_ns)
+
+    # ---- forward stages (each enqueues on the current stream) ----------------------------------
+    def stage_begin(self) -> None:
+        self.epoch += 1
+
+    def stage_barrier_signal(self) -> None:
+        if self.world > 1:
+            cu.flag_signal([self._flag_ptr(r, self.lay.bar_off + self.rank)
+                            for r in range(self.world)])
+            self.launches += 1
+
+    def stage_barrier_wait(self) -> None:
+        if self.world > 1:
+            cu.flag_wait([self._flag_ptr(self.rank, self.lay.bar_off + r) for r in range(self.world)],
+                         [self.epoch] * self.world,
+                         self._flag_ptr(self.rank, self.lay.status_off), self.timeout_ns)
+            self.launches += 1
+
+    def stage_block1(self, in_idx: int = 0) -> None:
+        rp = self.rp
+        if rp.pool1_own[1] <= rp.pool1_own[0]:
+            return
+        g = self._geom_block1(self.rank, in_idx=in_idx)
+        if self.precision == "simt":
+            cu.simt_block(self.w1p, self.b1, self.buf_pool1.ptr, g)
+        else:
+            self.tc1.run(self.b1, self.buf_pool1.ptr, g)
+        self.launches += 1
+
+    def stage_block2(self, out_idx: int = 0) -> None:
+        if not self.rp.active:
+            return
+        g = self._geom_block2()
+        out_ptr = self.symm.ptr(0, f"out{out_idx}")
+        if self.precision == "simt":
+            cu.simt_block(self.w2p, self.b2, out_ptr, g)
+        else:
+            self.tc2.run(self.b2, out_ptr, g)
+        self.launches += 1
+
+    def stage_done_signal(self) -> None:
+        if self.world > 1:
+            cu.flag_signal([self._flag_ptr(0, self.lay.done_off + self.rank)])
+            self.launches += 1
+
+    def stage_done_wait(self) -> None:
+        if self.world > 1 and self.rank == 0:
+            cu.flag_wait([self._flag_ptr(0, self.lay.done_off + r) for r in range(self.world)],
+                         [self.epoch] * self.world,
+                         self._flag_ptr(0, self.lay.status_off), self.timeout_ns)
+            self.launches += 1
+
+    def forward_enqueue(self, in_idx: int = 0, out_idx: int = 0) -> Optional[torch.Tensor]:
+        """Enqueue one forward on the current stream (real multi-rank or single GPU).  The input
+        must already be in ``input_view(in_idx)`` (rank 0 in p2p mode, every rank in sharded
+        mode).  Returns rank 0's output tensor ``out_idx`` (valid once the stream gets here).
+        Every rank must pass the same ``in_idx`` / ``out_idx`` for the same forward."""
+        assert self._final, "call finalize() first"
+        with torch.cuda.device(self.device):
+            self.stage_begin()
+            self.stage_barrier_signal()
+            self.stage_barrier_wait()
+            self.stage_block1(in_idx)
+            self.stage_block2(out_idx)
+            self.stage_done_signal()
+            self.stage_done_wait()
+        return self.outs[out_idx]
+
+    def forward(self, x: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+        """Device-tensor API: copies ``x`` (this rank's input; whole batch on rank 0 in p2p mode)
+        into the resident buffer and runs one forward."""
+        if x is not None and self.in_rows > 0:
+            self.input_view(0).copy_(x, non_blocking=True)
+        return self.forward_enqueue(0)
+
+    def status(self) -> int:
+        """First error latched by a device-side wait (0 = ok).  Synchronises."""
+        torch.cuda.synchronize(self.device)
+        return int(self.flags_t[self.lay.status_off].item())
+
+    def check_status(self) -> None:
+        s = self.status()
+        if s != 0:
+            raise RuntimeError(f"[Rank {self.rank}] device-side failure: status {s} "
+                               f"(-4 = cross-GPU flag wait timed out)")
+
+
+def single_gpu_engine(cfg: NetConfig, weights: Blocks12Weights, device="cuda:0",
+                      precision: Optional[str] = None) -> Blocks12Engine:
+    """V3-equivalent: one GPU, whole image, two kernels per forward."""
+    symm = LocalSymm(1, device).view(0)
+    e = Blocks12Engine(cfg, weights, symm, 0, 1, precision=precision)
+    e.finalize()
+    return e
+
+
+class EmulatedWorld:
+    """All ranks of a row-decomposed forward on ONE device in ONE process.  Kernels of different
+    ranks are launched layer by layer, so every flag a kernel waits on is already set (spinning
+    co-scheduled ranks on one GPU is forbidden).  Exercises the exact peer-pointer, halo, scatter
+    and gather index math of the multi-GPU path."""
+
+    def __init__(self, cfg: NetConfig, weights: Blocks12Weights, world: int, device="cuda:0",
+                 precision: Optional[str] = None, strategy: str = "halo", scatter: str = "p2p"):
+        self.symm = LocalSymm(world, device)
+        self.engines: List[Blocks12Engine] = [
+            Blocks12Engine(cfg, weights, self.symm.view(r), r, world, precision=precision,
+                           strategy=strategy, scatter=scatter) for r in range(world)]
+        for e in self.engines:
+            e.finalize()
+        self.cfg = cfg
+
+    def load_input(self, x: torch.Tensor) -> None:
+        for e in self.engines:
+            if e.in_rows > 0:
+                if e.scatter == "p2p":
+                    e.input_view(0).copy_(x)
+                else:
+                    a, b = e.rp.in_rows
+                    e.input_view(0).copy_(x[:, a:b])
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        self.load_input(x)
+        E = self.engines
+        for e in E: e.stage_begin()
+        for e in E: e.stage_barrier_signal()
+        for e in E: e.stage_barrier_wait()
+        for e in E: e.stage_block1(0)
+        for e in E: e.stage_block2()
+        for e in E: e.stage_done_signal()
+        for e in E: e.stage_done_wait()
+        for e in E: e.check_status()
+        return E[0].out

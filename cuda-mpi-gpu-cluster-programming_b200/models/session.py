@@ -1,0 +1,116 @@
+"""Public inference API: host tensors in, host tensors out.
+
+``Session`` is what a user of the reference's ``./template`` / ``mpirun -np N ./template``
+switches to when they want the forward pass as a library call:
+
+    sess = Session(cfg, weights)                  # one GPU
+    y = sess.infer(x_pinned)                      # [N,H,W,C] fp32 host -> [N,13,13,256] host
+
+    sess = Session(cfg, weights, dist=ctx)        # one process per GPU (torchrun / bin/mpirun)
+    y = sess.infer(x_host_on_rank0)               # scatter="p2p": rank 0 owns the images
+    y = sess.infer(my_row_slab)                   # scatter="sharded": each rank feeds its slab
+
+Every call does the host->device copy of that call's input from pinned memory, the forward, and
+the device->host copy of the result.  ``submit``/``result`` expose the same thing pipelined:
+double-buffered input and output slots, a copy-in stream, a compute stream and a copy-out
+stream, so step i+1's H2D overlaps step i's kernels and step i-1's D2H.  (The reference does
+synchronous pageable cudaMemcpy inside its timed region,
+ref v3_cuda_only/src/alexnet_cuda.cu:67-71,88.)
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from ..config import NetConfig
+from ..parallel.symm import LocalSymm, IpcSymm
+from .engine import Blocks12Engine
+from .init import Blocks12Weights
+
+
+class Session:
+    def __init__(self, cfg: NetConfig, weights: Blocks12Weights, dist=None, device=None,
+                 precision: Optional[str] = None, strategy: str = "halo", scatter: str = "p2p"):
+        self.cfg = cfg
+        self.dist = dist
+        world = dist.world if dist is not None else 1
+        rank = dist.rank if dist is not None else 0
+        if world > 1:
+            self.symm = IpcSymm(dist)
+        else:
+            self.symm = LocalSymm(1, device or (dist.device if dist else "cuda:0")).view(0)
+        self.engine = Blocks12Engine(cfg, weights, self.symm, rank, world, precision=precision,
+                                     strategy=strategy, scatter=scatter)
+        self.symm.commit()
+        self.engine.finalize()
+        e = self.engine
+        self.device = e.device
+        with torch.cuda.device(self.device):
+            self.s_in = torch.cuda.Stream()
+            self.s_compute = torch.cuda.Stream()
+            self.s_out = torch.cuda.Stream()
+            self.ev_h2d = [torch.cuda.Event() for _ in range(2)]
+            self.ev_compute = [torch.cuda.Event() for _ in range(2)]
+            self.ev_d2h = [torch.cuda.Event() for _ in range(2)]
+        self.step = 0
+        self.h_out = None
+        if rank == 0:
+            sh = e.sh
+            self.h_out = [torch.empty((cfg.batch, sh.Hp2, sh.Wp2, sh.K2), dtype=torch.float32,
+                                      pin_memory=True) for _ in range(2)]
+        self.h2d_bytes = e.in_bytes
+        self.d2h_bytes = (self.h_out[0].numel() * 4) if rank == 0 else 0
+
+    # -- what this rank must feed ---------------------------------------------------------------
+    @property
+    def input_rows(self):
+        """Global input rows this rank supplies to ``infer``/``submit`` ((0,H) on rank 0 in p2p
+        mode, nothing on other ranks; the rank's slab in sharded mode)."""
+        e = self.engine
+        return (e.in_base, e.in_base + e.in_rows)
+
+    def submit(self, x_host: Optional[torch.Tensor]) -> int:
+        e = self.engine
+        i = self.step % 2
+        self.step += 1
+        with torch.cuda.device(self.device):
+            if e.in_rows > 0:
+                assert x_host is not None and x_host.is_pinned(), "feed pinned host memory"
+                # slot i is free once the forward that last read it has finished
+                self.s_in.wait_event(self.ev_compute[i])
+                with torch.cuda.stream(self.s_in):
+                    e.input_view(i).copy_(x_host, non_blocking=True)
+                    self.ev_h2d[i].record(self.s_in)
+                self.s_compute.wait_event(self.ev_h2d[i])
+            # output slot i must have been drained by its previous D2H
+            self.s_compute.wait_event(self.ev_d2h[i])
+            with torch.cuda.stream(self.s_compute):
+                out = e.forward_enqueue(i, i)
+                self.ev_compute[i].record(self.s_compute)
+            if out is not None:
+                self.s_out.wait_event(self.ev_compute[i])
+                with torch.cuda.stream(self.s_out):
+                    self.h_out[i].copy_(out, non_blocking=True)
+                    self.ev_d2h[i].record(self.s_out)
+        return i
+
+    def result(self, ticket: int) -> Optional[torch.Tensor]:
+        """Blocks until the ticket's output is in host memory (rank 0) / its forward is done."""
+        if self.h_out is not None:
+            self.ev_d2h[ticket].synchronize()
+            return self.h_out[ticket]
+        self.ev_compute[ticket].synchronize()
+        return None
+
+    def infer(self, x_host: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+        if x_host is not None and not x_host.is_pinned():
+            x_host = x_host.pin_memory()
+        y = self.result(self.submit(x_host))
+        self.engine.check_status()
+        return y
+
+    def drain(self) -> None:
+        with torch.cuda.device(self.device):
+            for s in (self.s_in, self.s_compute, self.s_out):
+                s.synchronize()

@@ -1,0 +1,130 @@
+"""ctypes bindings of libb200cnn_cuda.so (hand-written sm_100a kernels, include/b200cnn.h).
+
+There is no PyTorch fallback: if the library cannot be loaded on a machine that has a GPU the
+import of this module's ``lib()`` raises, so a silent eager-mode path can never masquerade as
+the native one.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _build
+from ._ctypes import LrnParams, LRN_MODES, check, fptr, NativeError
+
+MAX_SEG = 4
+MAX_SIGNAL = 4
+DEFAULT_TIMEOUT_NS = 5_000_000_000
+
+
+class RowSeg(C.Structure):
+    _fields_ = [("ptr", C.c_void_p), ("base", C.c_int), ("slab", C.c_int), ("lo", C.c_int),
+                ("hi", C.c_int), ("flag", C.c_void_p), ("target", C.c_int), ("pad_", C.c_int)]
+
+
+class BlockGeom(C.Structure):
+    _fields_ = [(n, C.c_int) for n in (
+        "N", "H", "W", "C", "K", "F", "S", "P", "Hc", "Wc", "Hp", "Wp", "p0", "p1",
+        "out_base", "out_slab")] + [
+        ("lrn", LrnParams), ("nseg", C.c_int), ("n_signal", C.c_int),
+        ("seg", RowSeg * MAX_SEG), ("signal", C.c_void_p * MAX_SIGNAL),
+        ("status", C.c_void_p), ("timeout_ns", C.c_ulonglong)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = C.CDLL(_build.build_cuda())
+        L.b200_last_error.restype = C.c_char_p
+        L.b200_pack_weights_ffck.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.b200_simt_block.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.POINTER(BlockGeom), C.c_void_p]
+        L.b200_simt_block_tiles.argtypes = [C.POINTER(BlockGeom)]
+        L.b200_symm_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
+        L.b200_symm_free.argtypes = [C.c_void_p]
+        L.b200_ipc_export.argtypes = [C.c_void_p, C.c_char_p]
+        L.b200_ipc_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+        L.b200_ipc_close.argtypes = [C.c_void_p]
+        L.b200_can_access_peer.argtypes = [C.c_int, C.c_int]
+        L.b200_enable_peer.argtypes = [C.c_int]
+        L.b200_flag_signal.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_void_p]
+        L.b200_flag_wait.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.c_int,
+                                     C.c_void_p, C.c_ulonglong, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def cu_check(rc: int, what: str) -> None:
+    if rc != 0:
+        check(rc, what, (lib().b200_last_error() or b"").decode())
+
+
+def current_stream_ptr() -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def pack_weights_ffck(w: torch.Tensor) -> torch.Tensor:
+    """[K,C,F,F] -> [F,F,C,K] (host), see csrc/cuda/common.cu."""
+    w = w.detach().cpu().contiguous()
+    K, Cc, F, _ = w.shape
+    o = torch.empty((F, F, Cc, K), dtype=torch.float32)
+    cu_check(lib().b200_pack_weights_ffck(fptr(w), fptr(o), K, Cc, F), "pack_weights_ffck")
+    return o
+
+
+def make_block_geom(*, N, H, W, Cin, K, F, S, P, Hc, Wc, Hp, Wp, rows: Tuple[int, int],
+                    out_base: int, out_slab: int, lrn: Optional[LrnParams],
+                    segs: Sequence[dict], signals: Sequence[int] = (),
+                    status_ptr: int = 0, timeout_ns: int = DEFAULT_TIMEOUT_NS) -> BlockGeom:
+    g = BlockGeom()
+    g.N, g.H, g.W, g.C = N, H, W, Cin
+    g.K, g.F, g.S, g.P = K, F, S, P
+    g.Hc, g.Wc, g.Hp, g.Wp = Hc, Wc, Hp, Wp
+    g.p0, g.p1 = rows
+    g.out_base, g.out_slab = out_base, out_slab
+    g.lrn = lrn if lrn is not None else LrnParams(0, 0.0, 0.0, 0.0, 0)
+    if not 1 <= len(segs) <= MAX_SEG:
+        raise NativeError(f"need 1..{MAX_SEG} row segments, got {len(segs)}")
+    if len(signals) > MAX_SIGNAL:
+        raise NativeError(f"at most {MAX_SIGNAL} signal targets, got {len(signals)}")
+    g.nseg = len(segs)
+    for i, s in enumerate(segs):
+        g.seg[i] = RowSeg(s["ptr"], s["base"], s["slab"], s["lo"], s["hi"],
+                          s.get("flag", 0) or None, s.get("target", 0), 0)
+    g.n_signal = len(signals)
+    for i, p in enumerate(signals):
+        g.signal[i] = p
+    g.status = status_ptr or None
+    g.timeout_ns = timeout_ns
+    return g
+
+
+def simt_block(w_ffck: torch.Tensor, bias: torch.Tensor, out_ptr: int, g: BlockGeom) -> None:
+    cu_check(lib().b200_simt_block(fptr(w_ffck), fptr(bias), C.c_void_p(out_ptr), C.byref(g),
+                                   current_stream_ptr()), "simt_block")
+
+
+def simt_block_tiles(g: BlockGeom) -> int:
+    return int(lib().b200_simt_block_tiles(C.byref(g)))
+
+
+def flag_signal(targets: Sequence[int], add: int = 1) -> None:
+    if not targets:
+        return
+    arr = (C.c_void_p * len(targets))(*targets)
+    cu_check(lib().b200_flag_signal(arr, len(targets), add, current_stream_ptr()), "flag_signal")
+
+
+def flag_wait(flags: Sequence[int], targets: Sequence[int], status_ptr: int = 0,
+              timeout_ns: int = DEFAULT_TIMEOUT_NS) -> None:
+    if not flags:
+        return
+    fa = (C.c_void_p * len(flags))(*flags)
+    ta = (C.c_int * len(flags))(*targets)
+    cu_check(lib().b200_flag_wait(fa, ta, len(flags), C.c_void_p(status_ptr or None),
+                                  timeout_ns, current_stream_ptr()), "flag_wait")

@@ -88,24 +88,70 @@ int  b200_hw1_check(const double* C, const double* Cref, size_t n, double tol);
 const char* b200_last_error(void);
 int b200_cuda_device_count(void);
 
-/* Exact-FP32 SIMT path (V3/V4 kernel equivalents, fused; ref v3_cuda_only/src/layers_cuda.cu:20-139,
- * v4_mpi_cuda/src/layers_mpi_cuda.cu:25-89).  conv + bias + ReLU + max-pool in one kernel;
- * optionally + LRN.  `g` describes the conv; pool geometry is (Fp,Sp) on the conv output;
- * pooled rows [p0,p1) are written to `out` slab (pool_base, pool_slab).
- * wt = weights re-packed [F][F][C][K] (b200_pack_weights_fck). */
+/* A row segment of a (possibly distributed) NHWC tensor: global rows [lo,hi) live in the slab
+ * `ptr` (first slab row = global row `base`, `slab` rows per image).  `ptr` may be local memory
+ * or a peer GPU's memory mapped over NVLink.  When `flag` is non-null the rows of image n may
+ * only be read once flag[n] >= target (per-image arrival counter in local symmetric memory,
+ * bumped by the producing rank's epilogue). */
 typedef struct {
-    b200_win_geom conv;      /* o0/o1 ignored: derived from pooled rows                   */
-    int Fp, Sp;              /* pool window / stride                                      */
-    int Hp, Wp;              /* logical pooled dims                                       */
-    int pool_base, pool_slab;
+    const float* ptr;
+    int base, slab;
+    int lo, hi;
+    const int* flag;
+    int target;
+    int pad_;
+} b200_row_seg;
+
+#define B200_MAX_SEG 4
+#define B200_MAX_SIGNAL 4
+
+/* One fused block: conv(F,S,P) + bias + ReLU + max-pool(3,2) [+ cross-channel LRN], for pooled
+ * rows [p0,p1) of every image.  Replaces the reference's 3-4 separate kernels per block
+ * (ref v3_cuda_only/src/layers_cuda.cu:20-139, v4_mpi_cuda/src/layers_mpi_cuda.cu:25-89) and,
+ * through `seg`/`signal`, its host-staged scatter / halo / gather
+ * (ref v4_mpi_cuda/src/main_mpi_cuda.cpp:58-79,100-130). */
+typedef struct {
+    int N;                   /* images                                                    */
+    int H, W, C;             /* logical conv input                                        */
+    int K, F, S, P;
+    int Hc, Wc;              /* logical conv output                                       */
+    int Hp, Wp;              /* logical pooled output (pool window 3, stride 2)           */
     int p0, p1;              /* pooled rows to produce                                    */
+    int out_base, out_slab;  /* output slab: (n,h,w,k) at ((n*out_slab+h-out_base)*Wp+w)*K+k */
     b200_lrn_params lrn;     /* N_lrn == 0 => no LRN                                      */
+    int nseg;
+    int n_signal;
+    b200_row_seg seg[B200_MAX_SEG];
+    int* signal[B200_MAX_SIGNAL];   /* per-image counters (usually on peers) bumped per finished tile */
+    int* status;             /* device word: first error code of the launch (0 = ok)      */
+    unsigned long long timeout_ns;
 } b200_block_geom;
 
-int b200_pack_weights_kfc(const float* w_kcff, float* w_kffc, int K, int C, int F);   /* host */
+/* host: [K][C][F][F] (reference layout) -> [F][F][C][K] used by the SIMT kernels */
+int b200_pack_weights_ffck(const float* w_kcff, float* w_ffck, int K, int C, int F);
 
-int b200_simt_block(const float* in, const float* w_kffc, const float* bias, float* out,
+/* Exact-FP32 SIMT path (validation twin of the tensor-core path; V3 equivalent).
+ * Number of tiles per image (needed by peers to compute flag targets) via *_tiles. */
+int b200_simt_block(const float* w_ffck, const float* bias, float* out,
                     const b200_block_geom* g, void* stream);
+int b200_simt_block_tiles(const b200_block_geom* g);
+
+/* Symmetric (peer-mapped) memory: zeroed cudaMalloc + CUDA IPC handles (64 bytes) exchanged by
+ * the caller (torch.distributed); replaces MPI host buffers. */
+int b200_symm_alloc(size_t bytes, void** ptr);
+int b200_symm_free(void* ptr);
+int b200_ipc_export(void* ptr, unsigned char* handle64);
+int b200_ipc_open(const unsigned char* handle64, void** ptr);
+int b200_ipc_close(void* ptr);
+int b200_can_access_peer(int dev, int peer);
+int b200_enable_peer(int peer);
+
+/* Stream-ordered device flag ops (MPI_Barrier / completion notification equivalents,
+ * ref v4_mpi_cuda/src/main_mpi_cuda.cpp:151,154): signal = fence.sys + red.release.sys add on up
+ * to 16 counters (local or peer); wait = spin until flags[i] >= target[i] with a watchdog. */
+int b200_flag_signal(int* const* targets, int n, int add, void* stream);
+int b200_flag_wait(const int* const* flags, const int* target, int n, int* status,
+                   unsigned long long timeout_ns, void* stream);
 
 #ifdef __cplusplus
 }
