@@ -1,0 +1,605 @@
+// tcgen05 / TMEM / TMA fused conv block for sm_100a:
+//   implicit-GEMM conv (kind::tf32, fp32 accumulate in TMEM) + bias + ReLU + 3x3/2 max-pool
+//   [+ cross-channel LRN], with the scatter pull / halo read / gather store over peer memory.
+//
+// Replaces, per block, the reference's convKernel + reluKernel + poolKernel (+ lrnKernel)
+// (ref v3_cuda_only/src/layers_cuda.cu:20-139, v4_mpi_cuda/src/layers_mpi_cuda.cu:25-89) and the
+// host-staged MPI traffic around them (ref v4_mpi_cuda/src/main_mpi_cuda.cpp:58-79,100-130).
+//
+// GEMM view.  M = conv output pixels, N = output channels (all of them in one CTA so that LRN,
+// a window over channels, can run in the epilogue), K = F*F*C ordered (fy, fx, c).
+//   * A (im2col rows) never exists in memory.  8 producer warps gather it straight from the NHWC
+//     activation — local slab or NVLink-mapped peer slab, chosen per input row through
+//     b200_row_seg — round to TF32 and store it into shared memory in the canonical K-major
+//     128B-swizzled UMMA layout, then fence.proxy.async + mbarrier arrive.
+//   * B (weights, K-major [N][Kpad]) arrives by TMA (cp.async.bulk.tensor.2d, SWIZZLE_128B) on the
+//     same mbarrier (expect_tx).
+//   * One elected thread issues tcgen05.mma.cta_group::1.kind::tf32 (M=128 x N x K=8); a tile is
+//     up to 256 pixels = two M=128 accumulators sharing every B stage (halves B traffic per FLOP).
+//     tcgen05.commit releases the stage / signals the epilogue.
+//   * A tile is a TR x TC patch of conv pixels = (2PR+1) x (2PC+1), so PR x PC pooled outputs are
+//     complete inside the tile.  Epilogue: tcgen05.ld 32 columns at a time -> smem patch ->
+//     max-pool -> (+bias, ReLU; they commute with max) -> LRN over the channel axis -> store.
+//     The store target is whatever `out` points at: for block 2 that is rank 0's output tensor
+//     (the gather); the epilogue also bumps arrival counters on peers that will read this tile.
+//
+// Warp roles (320 threads): warps 0-7 producers, then epilogue; warp 8 MMA issuer + TMEM owner;
+// warp 9 TMA issuer.  Persistent: grid = min(tiles, SMs), static round-robin over tiles.
+#include "common.cuh"
+
+#include <cuda.h>
+#include <cstring>
+#include <vector>
+
+namespace {
+
+using namespace b200;
+
+constexpr int kProducerWarps = 8;
+constexpr int kProducerThreads = kProducerWarps * 32;
+constexpr int kMmaWarp = 8;
+constexpr int kTmaWarp = 9;
+constexpr int kThreads = 320;
+constexpr int kBlockK = 32;                        // fp32 per k-block = one 128 B swizzle row
+constexpr int kTileM = 256;                        // pixel slots per tile (2 x UMMA_M)
+constexpr int kAStageBytes = kTileM * 128;         // 32 KB
+constexpr int kCbufPitch = 33;                     // floats; conflict-free row/column access
+constexpr int kCbufBytes = kTileM * kCbufPitch * 4;
+constexpr int kMaxPooled = 64;                     // pooled outputs per tile
+constexpr unsigned long long kSpinTimeoutNs = 4000000000ull;
+
+struct TcParams {
+    b200_block_geom g;
+    int TR, TC, PR, PC;
+    int tiles_r, tiles_c;
+    int nacc;
+    int nkb, Kdim;
+    int stages, b_stage_bytes;
+    int vec_mode;
+    int tmem_cols;
+    int any_flag;
+    uint32_t idesc;
+    long long total_tiles;
+};
+
+// ------------------------------------------------------------------ PTX wrappers ----
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// Bounded wait: a protocol bug must become a launch failure, never a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    if (mbar_try_wait(bar, parity)) return;
+    const unsigned long long t0 = globaltimer_ns();
+    unsigned spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if ((++spins & 0xFFF) == 0 && globaltimer_ns() - t0 > kSpinTimeoutNs) asm volatile("trap;");
+    }
+}
+__device__ __forceinline__ void fence_mbar_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1,
+                                            uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%2, %3}], [%4];"
+        ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem),
+                 "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols)
+                 : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+          "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+          "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]),
+          "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+          "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void bar_producers() {     // named barrier 1: the 8 producer warps
+    asm volatile("bar.sync 1, %0;" ::"n"(kProducerThreads) : "memory");
+}
+__device__ __forceinline__ float to_tf32(float x) {
+    uint32_t u;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+    return __uint_as_float(u);
+}
+
+// K-major, 128B-swizzled operand tile: 8-row groups of 1024 B, rows 128 B apart inside a group.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFF);       // start address
+    d |= (uint64_t)1 << 16;                       // leading byte offset (unused for SW128 K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;             // stride byte offset: next 8-row group
+    d |= (uint64_t)1 << 46;                       // descriptor version (Blackwell)
+    d |= (uint64_t)2 << 61;                       // SWIZZLE_128B
+    return d;
+}
+
+__device__ __forceinline__ const float* seg_row_ptr(const b200_block_geom& g, int n, int h) {
+#pragma unroll
+    for (int s = 0; s < B200_MAX_SEG; ++s) {
+        if (s < g.nseg && h >= g.seg[s].lo && h < g.seg[s].hi)
+            return g.seg[s].ptr + ((size_t)n * g.seg[s].slab + (h - g.seg[s].base)) * g.W * g.C;
+    }
+    return nullptr;
+}
+
+// ------------------------------------------------------------------------ kernel ----
+__global__ void __launch_bounds__(kThreads, 1)
+tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant__ TcParams p,
+                const float* __restrict__ bias, float* __restrict__ out) {
+    extern __shared__ uint8_t smem_raw[];
+    const b200_block_geom& g = p.g;
+    const int N = g.K;                                        // GEMM N = output channels
+
+    // carve shared memory (1024 B aligned for the swizzle atoms)
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
+    const uint32_t a_off = 0;
+    const uint32_t b_off = p.stages * kAStageBytes;
+    const uint32_t ctl_off = b_off + p.stages * p.b_stage_bytes;
+    const uint32_t full_bar = base + ctl_off;                 // [stages]
+    const uint32_t empty_bar = full_bar + 8 * p.stages;       // [stages]
+    const uint32_t tmem_full_bar = empty_bar + 8 * p.stages;
+    const uint32_t tile_free_bar = tmem_full_bar + 8;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + ctl_off + 16 * p.stages + 16);
+    float* s_bias = reinterpret_cast<float*>(gbase + ctl_off + 16 * p.stages + 32);
+    float* cbuf0 = reinterpret_cast<float*>(gbase);           // epilogue buffers alias the stages
+    float* pbuf = reinterpret_cast<float*>(gbase + 2 * kCbufBytes);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < p.stages; ++s) {
+            mbar_init(full_bar + 8 * s, kProducerWarps + 1);
+            mbar_init(empty_bar + 8 * s, 1);
+        }
+        mbar_init(tmem_full_bar, 1);
+        mbar_init(tile_free_bar, kProducerWarps);
+        fence_mbar_init();
+    }
+    for (int i = threadIdx.x; i < N; i += kThreads) s_bias[i] = bias[i];
+    if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int tiles_per_img = p.tiles_r * p.tiles_c;
+    int stage = 0;
+    uint32_t phase = 0;
+
+    if (warp < kProducerWarps) {
+        // =============================== producers, then epilogue =========================
+        const int tid = threadIdx.x;
+        const int j = tid & 7;                                // 16 B chunk inside the 128 B row
+        const int m_base = tid >> 3;                          // rows m_base + 32*i
+        const uint32_t row_sw = (uint32_t)(m_base & 7);       // (m & 7) is the same for all i
+        int it = 0;
+        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x, ++it) {
+            const int n = (int)(w / tiles_per_img);
+            const int rem = (int)(w - (long long)n * tiles_per_img);
+            const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
+            const int pr0 = g.p0 + tr_i * p.PR, pc0 = tc_i * p.PC;
+            const int cr0 = 2 * pr0, cc0 = 2 * pc0;
+
+            if (p.any_flag) {                                  // consumer side of the halo flags
+                if (tid == 0) {
+                    const int ir0 = cr0 * g.S - g.P, ir1 = (cr0 + p.TR - 1) * g.S - g.P + g.F;
+                    for (int s = 0; s < g.nseg; ++s)
+                        if (g.seg[s].flag && ir0 < g.seg[s].hi && ir1 > g.seg[s].lo)
+                            wait_flag_ge(g.seg[s].flag + n, g.seg[s].target, g.status, g.timeout_ns);
+                }
+                bar_producers();
+            }
+
+            int h0[8], w0[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int m = m_base + 32 * i;
+                const int pi = m / p.TC, pj = m - pi * p.TC;
+                const int cy = cr0 + pi, cx = cc0 + pj;
+                const bool ok = (m < p.TR * p.TC) && cy < g.Hc && cx < g.Wc;
+                h0[i] = ok ? cy * g.S - g.P : -(1 << 20);      // invalid slot -> always out of range
+                w0[i] = cx * g.S - g.P;
+            }
+
+            for (int kb = 0; kb < p.nkb; ++kb) {
+                mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+                const uint32_t a_stage = base + a_off + stage * kAStageBytes;
+                float4 v[8];
+                if (p.vec_mode) {
+                    const int cpb = g.C / kBlockK;
+                    const int tap = kb / cpb, c0 = (kb - tap * cpb) * kBlockK + 4 * j;
+                    const int fy = tap / g.F, fx = tap - fy * g.F;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int h = h0[i] + fy, x = w0[i] + fx;
+                        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (h >= 0 && h < g.H && x >= 0 && x < g.W) {
+                            const float* rp = seg_row_ptr(g, n, h);
+                            if (rp) v[i] = *reinterpret_cast<const float4*>(rp + (size_t)x * g.C + c0);
+                        }
+                    }
+                } else {
+                    const int FC = g.F * g.C, WC = g.W * g.C;
+                    const int k0 = kb * kBlockK + 4 * j;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        float e[4];
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const int k = k0 + q;
+                            const int fy = k / FC, t = k - fy * FC;
+                            const int h = h0[i] + fy, cf = w0[i] * g.C + t;
+                            e[q] = 0.f;
+                            if (k < p.Kdim && h >= 0 && h < g.H && cf >= 0 && cf < WC) {
+                                const float* rp = seg_row_ptr(g, n, h);
+                                if (rp) e[q] = rp[cf];
+                            }
+                        }
+                        v[i] = make_float4(e[0], e[1], e[2], e[3]);
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int m = m_base + 32 * i;
+                    const uint32_t dst = a_stage + (uint32_t)(m >> 3) * 1024u + row_sw * 128u +
+                                         (((uint32_t)j ^ row_sw) << 4);
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst),
+                                 "f"(to_tf32(v[i].x)), "f"(to_tf32(v[i].y)), "f"(to_tf32(v[i].z)),
+                                 "f"(to_tf32(v[i].w))
+                                 : "memory");
+                }
+                fence_proxy_async_smem();                      // generic stores -> async proxy (UMMA)
+                __syncwarp();
+                if (lane == 0) mbar_arrive(full_bar + 8 * stage);
+                if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+
+            // ------------------------------ epilogue ------------------------------------
+            mbar_wait(tmem_full_bar, (uint32_t)(it & 1));
+            tc_fence_after();
+            const int q4 = warp & 3, hacc = warp >> 2;         // TMEM lane quarter, accumulator
+            const int row = hacc * 128 + q4 * 32 + lane;       // pixel slot this thread drains
+            const bool has_acc = hacc < p.nacc;
+            const int PP = p.PR * p.PC;
+            const int nchunk = N / 32;
+            const bool do_lrn = g.lrn.N_lrn > 0;
+            for (int cc = 0; cc < nchunk; ++cc) {
+                float* cb = cbuf0 + (cc & 1) * (kCbufBytes / 4);
+                if (has_acc) {
+                    uint32_t r[32];
+                    tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(hacc * N + cc * 32), r);
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) cb[row * kCbufPitch + c] = __uint_as_float(r[c]);
+                }
+                bar_producers();
+                // pool: lane = channel inside the chunk, warp strides over pooled pixels
+                const float bch = s_bias[cc * 32 + lane];
+                for (int pp = warp; pp < PP; pp += kProducerWarps) {
+                    const int pi = pp / p.PC, pj = pp - pi * p.PC;
+                    const float* c0p = cb + ((2 * pi) * p.TC + 2 * pj) * kCbufPitch + lane;
+                    float mx = -INFINITY;
+#pragma unroll
+                    for (int a = 0; a < 3; ++a)
+#pragma unroll
+                        for (int b = 0; b < 3; ++b)
+                            mx = fmaxf(mx, c0p[(a * p.TC + b) * kCbufPitch]);
+                    const float val = fmaxf(mx + bch, 0.f);    // relu(max(x)+b) == max(relu(x+b))
+                    if (do_lrn) {
+                        pbuf[pp * N + cc * 32 + lane] = val;
+                    } else {
+                        const int pr = pr0 + pi, pc = pc0 + pj;
+                        if (pr < g.p1 && pr < g.Hp && pc < g.Wp)
+                            out[(((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N +
+                                cc * 32 + lane] = val;
+                    }
+                }
+            }
+            if (do_lrn) {
+                bar_producers();
+                const int half = g.lrn.N_lrn / 2;
+                const float al = g.lrn.mode == B200_LRN_ALPHA_OVER_N
+                                     ? g.lrn.alpha / (float)g.lrn.N_lrn : g.lrn.alpha;
+                for (int idx = tid; idx < PP * N; idx += kProducerThreads) {
+                    const int pp = idx / N, c = idx - pp * N;
+                    const int pi = pp / p.PC, pj = pp - pi * p.PC;
+                    const int pr = pr0 + pi, pc = pc0 + pj;
+                    if (pr >= g.p1 || pr >= g.Hp || pc >= g.Wp) continue;
+                    float ss = 0.f;
+                    const int c_lo = max(0, c - half), c_hi = min(N - 1, c + half);
+                    for (int q = c_lo; q <= c_hi; ++q) {
+                        const float x = pbuf[pp * N + q];
+                        ss = fmaf(x, x, ss);
+                    }
+                    const float val = pbuf[idx] / powf(g.lrn.k + al * ss, g.lrn.beta);
+                    out[(((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N + c] = val;
+                }
+            }
+            // hand the stages / TMEM back: all tcgen05.ld of this warp are complete (wait::ld)
+            tc_fence_before();
+            bar_producers();                                   // everyone is done with cbuf/pbuf
+            if (g.n_signal > 0 && tid == 0) {                  // producer side of the halo flags
+                __threadfence_system();
+                for (int i = 0; i < g.n_signal; ++i) red_release_sys_add(g.signal[i] + n, 1);
+            }
+            if (lane == 0) mbar_arrive(tile_free_bar);
+        }
+    } else if (warp == kMmaWarp) {
+        // ======================================= MMA issuer ==============================
+        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
+            for (int kb = 0; kb < p.nkb; ++kb) {
+                mbar_wait(full_bar + 8 * stage, phase);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint32_t a_stage = base + a_off + stage * kAStageBytes;
+                    const uint32_t b_stage = base + b_off + stage * p.b_stage_bytes;
+                    const uint64_t db = make_smem_desc(b_stage);
+#pragma unroll
+                    for (int ks = 0; ks < kBlockK / 8; ++ks) {
+                        for (int h = 0; h < p.nacc; ++h) {
+                            const uint64_t da = make_smem_desc(a_stage + h * (128 * 128));
+                            umma_tf32(tmem_base + (uint32_t)(h * N), da + 2 * ks, db + 2 * ks, p.idesc,
+                                      (kb | ks) != 0 ? 1u : 0u);
+                        }
+                    }
+                    umma_commit(empty_bar + 8 * stage);        // frees the stage when the MMAs retire
+                    if (kb == p.nkb - 1) umma_commit(tmem_full_bar);
+                }
+                __syncwarp();
+                if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else {
+        // ======================================= TMA issuer (B) ==========================
+        int it = 0;
+        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x, ++it) {
+            // the previous tile's epilogue buffers alias the stages: wait until they are released
+            if (it > 0) mbar_wait(tile_free_bar, (uint32_t)((it - 1) & 1));
+            for (int kb = 0; kb < p.nkb; ++kb) {
+                mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+                if (lane == 0) {
+                    const uint32_t fb = full_bar + 8 * stage;
+                    mbar_arrive_expect_tx(fb, (uint32_t)p.b_stage_bytes);
+                    tma_load_2d(base + b_off + stage * p.b_stage_bytes, &tmapB, kb * kBlockK, 0, fb);
+                }
+                __syncwarp();
+                if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kMmaWarp) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, p.tmem_cols);
+    }
+}
+
+// --------------------------------------------------------------------------- host ----
+struct TcConv {
+    int K, C, F, Kdim, Kpad, device;
+    float* d_w;
+    CUtensorMap tmap;
+};
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            return nullptr;
+        fn = (EncodeTiledFn)f;
+    }
+    return fn;
+}
+
+inline float host_tf32(float x) {                     // round to nearest, ties away (cvt.rna)
+    uint32_t u;
+    memcpy(&u, &x, 4);
+    if ((u & 0x7F800000u) != 0x7F800000u) u = (u + 0x1000u) & ~0x1FFFu;
+    memcpy(&x, &u, 4);
+    return x;
+}
+
+inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+// Tile planner: PR x PC pooled outputs per tile, (2PR+1)(2PC+1) <= 128*nacc pixel slots; minimise
+// tiles * nacc (MMA time), then slots.  Deterministic: peers call it to predict tile counts.
+bool plan_tiles(const b200_block_geom* g, TcParams* p) {
+    const int rows = g->p1 - g->p0;
+    long best = -1;
+    for (int nacc = 1; nacc <= 2; ++nacc)
+        for (int PR = 1; PR <= rows && PR <= 63; ++PR)
+            for (int PC = 1; PC <= g->Wp; ++PC) {
+                const int slots = (2 * PR + 1) * (2 * PC + 1);
+                if (slots > 128 * nacc) break;
+                if (PR * PC > kMaxPooled) break;
+                const long cost = (long)cdiv(rows, PR) * cdiv(g->Wp, PC) * nacc * 1024 + slots;
+                if (best < 0 || cost < best) {
+                    best = cost;
+                    p->PR = PR; p->PC = PC; p->TR = 2 * PR + 1; p->TC = 2 * PC + 1; p->nacc = nacc;
+                    p->tiles_r = cdiv(rows, PR); p->tiles_c = cdiv(g->Wp, PC);
+                }
+            }
+    return best >= 0;
+}
+
+int fill_params(const b200_block_geom* g, TcParams* p) {
+    if (g->K % 32 != 0 || g->K > 256 || g->K < 32) return B200_ERR_UNSUPPORTED;
+    memset(p, 0, sizeof(*p));
+    p->g = *g;
+    if (!plan_tiles(g, p)) return B200_ERR_ARG;
+    p->Kdim = g->F * g->F * g->C;
+    p->nkb = cdiv(p->Kdim, kBlockK);
+    p->vec_mode = (g->C % kBlockK == 0) ? 1 : 0;
+    p->b_stage_bytes = g->K * 128;
+    const int stage_bytes = kAStageBytes + p->b_stage_bytes;
+    int stages = (200 * 1024) / stage_bytes;
+    if (stages > 4) stages = 4;
+    if (stages < 2) return B200_ERR_UNSUPPORTED;
+    p->stages = stages;
+    int cols = 32;
+    while (cols < 2 * g->K) cols *= 2;                 // two accumulators of N columns
+    p->tmem_cols = cols;
+    p->any_flag = 0;
+    for (int s = 0; s < g->nseg; ++s)
+        if (g->seg[s].flag) p->any_flag = 1;
+    // instruction descriptor: D=f32, A=B=tf32, both K-major, M=128, N=K
+    p->idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(g->K >> 3) << 17) | ((128u >> 4) << 24);
+    p->total_tiles = (long long)g->N * p->tiles_r * p->tiles_c;
+    return B200_OK;
+}
+
+size_t smem_bytes(const TcParams& p) {
+    size_t pipe = (size_t)p.stages * (kAStageBytes + p.b_stage_bytes);
+    size_t epi = 2 * (size_t)kCbufBytes + (size_t)kMaxPooled * p.g.K * 4;
+    if (epi > pipe) pipe = epi;                         // epilogue buffers alias the stages
+    return 1024 + pipe + 16 * p.stages + 32 + (size_t)p.g.K * 4 + 64;
+}
+
+}  // namespace
+
+extern "C" int b200_tc_conv_create(const float* w_kcff, int K, int C, int F, void** handle) {
+    if (!w_kcff || !handle || K <= 0 || C <= 0 || F <= 0) return B200_ERR_ARG;
+    EncodeTiledFn enc = get_encode();
+    if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return B200_ERR_CUDA; }
+    TcConv* t = new TcConv();
+    t->K = K; t->C = C; t->F = F;
+    t->Kdim = F * F * C;
+    t->Kpad = cdiv(t->Kdim, kBlockK) * kBlockK;
+    B200_CUDA_TRY(cudaGetDevice(&t->device));
+    // [K][C][F][F] -> K-major rows [K][Kpad], k = (fy*F+fx)*C + c, TF32-rounded, zero padded
+    std::vector<float> wk((size_t)K * t->Kpad, 0.f);
+    for (int k = 0; k < K; ++k)
+        for (int c = 0; c < C; ++c)
+            for (int fy = 0; fy < F; ++fy)
+                for (int fx = 0; fx < F; ++fx)
+                    wk[(size_t)k * t->Kpad + (fy * F + fx) * C + c] =
+                        host_tf32(w_kcff[(((size_t)k * C + c) * F + fy) * F + fx]);
+    B200_CUDA_TRY(cudaMalloc(&t->d_w, wk.size() * sizeof(float)));
+    B200_CUDA_TRY(cudaMemcpy(t->d_w, wk.data(), wk.size() * sizeof(float), cudaMemcpyHostToDevice));
+    cuuint64_t dims[2] = {(cuuint64_t)t->Kpad, (cuuint64_t)K};
+    cuuint64_t strides[1] = {(cuuint64_t)t->Kpad * sizeof(float)};
+    cuuint32_t box[2] = {(cuuint32_t)kBlockK, (cuuint32_t)K};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(&t->tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, t->d_w, dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed: %d (K=%d Kpad=%d)", (int)r, K, t->Kpad);
+        cudaFree(t->d_w);
+        delete t;
+        return B200_ERR_CUDA;
+    }
+    *handle = t;
+    return B200_OK;
+}
+
+extern "C" int b200_tc_conv_destroy(void* handle) {
+    TcConv* t = (TcConv*)handle;
+    if (t) {
+        cudaFree(t->d_w);
+        delete t;
+    }
+    return B200_OK;
+}
+
+extern "C" int b200_tc_block_tiles(const b200_block_geom* g) {
+    if (!g) return B200_ERR_ARG;
+    if (g->p1 <= g->p0) return 0;
+    TcParams p;
+    int rc = fill_params(g, &p);
+    if (rc != B200_OK) return rc;
+    return p.tiles_r * p.tiles_c;
+}
+
+extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const b200_block_geom* g,
+                             void* stream) {
+    TcConv* t = (TcConv*)handle;
+    if (!t || !bias || !out || !g) return B200_ERR_ARG;
+    if (g->nseg < 1 || g->nseg > B200_MAX_SEG || g->n_signal < 0 || g->n_signal > B200_MAX_SIGNAL)
+        return B200_ERR_ARG;
+    if (g->K != t->K || g->C != t->C || g->F != t->F) return B200_ERR_ARG;
+    if (g->p1 <= g->p0 || g->N <= 0) return B200_OK;
+    TcParams p;
+    int rc = fill_params(g, &p);
+    if (rc != B200_OK) return rc;
+    const size_t smem = smem_bytes(p);
+    if (smem > 227 * 1024) return B200_ERR_UNSUPPORTED;
+    static int sms = 0;
+    if (!sms) B200_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, t->device));
+    B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem));
+    const unsigned grid = (unsigned)(p.total_tiles < sms ? p.total_tiles : sms);
+    tc_block_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(t->tmap, p, bias, out);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}

@@ -1,0 +1,61 @@
+"""tcgen05 tensor-core conv blocks (csrc/cuda/tc_block.cu): TF32 operands, fp32 accumulate in TMEM.
+
+``TcConv`` owns the device copy of one layer's weights in the K-major, TF32-rounded, k-padded
+layout the kernel's TMA descriptor points at (created once; the reference re-uploads weights on
+every call, ref v4_mpi_cuda/src/alexnet_mpi_cuda.cu:188-191)."""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import cuda as cu
+from ._ctypes import fptr
+
+_bound = False
+
+
+def _lib():
+    global _bound
+    L = cu.lib()
+    if not _bound:
+        if not hasattr(L, "b200_tc_block"):
+            raise ImportError("libb200cnn_cuda.so was built without tc_block.cu")
+        L.b200_tc_conv_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.b200_tc_conv_destroy.argtypes = [C.c_void_p]
+        L.b200_tc_block_tiles.argtypes = [C.POINTER(cu.BlockGeom)]
+        L.b200_tc_block.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(cu.BlockGeom),
+                                    C.c_void_p]
+        _bound = True
+    return L
+
+
+class TcConv:
+    def __init__(self, w: torch.Tensor, device):
+        w = w.detach().cpu().contiguous().float()
+        self.K, self.C, self.F, _ = w.shape
+        self.device = torch.device(device)
+        h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            cu.cu_check(_lib().b200_tc_conv_create(fptr(w), self.K, self.C, self.F, C.byref(h)),
+                        "tc_conv_create")
+        self._h = h
+
+    def run(self, bias: torch.Tensor, out_ptr: int, g: cu.BlockGeom) -> None:
+        cu.cu_check(_lib().b200_tc_block(self._h, fptr(bias), C.c_void_p(out_ptr), C.byref(g),
+                                         cu.current_stream_ptr()), "tc_block")
+
+    def __del__(self):
+        try:
+            if self._h:
+                _lib().b200_tc_conv_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+def block_tiles(g: cu.BlockGeom) -> int:
+    n = int(_lib().b200_tc_block_tiles(C.byref(g)))
+    if n < 0:
+        cu.cu_check(n, "tc_block_tiles")
+    return n

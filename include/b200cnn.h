@@ -136,6 +136,15 @@ int b200_simt_block(const float* w_ffck, const float* bias, float* out,
                     const b200_block_geom* g, void* stream);
 int b200_simt_block_tiles(const b200_block_geom* g);
 
+/* tcgen05 / TMEM / TMA tensor-core path (TF32 operands, fp32 accumulate); same b200_block_geom.
+ * A handle owns one layer's weights on the device, K-major [K][Kpad], TF32-rounded, plus the TMA
+ * descriptor over them.  K must be a multiple of 32 and <= 256 (all channels in one CTA). */
+int b200_tc_conv_create(const float* w_kcff, int K, int C, int F, void** handle);
+int b200_tc_conv_destroy(void* handle);
+int b200_tc_block(void* handle, const float* bias, float* out, const b200_block_geom* g,
+                  void* stream);
+int b200_tc_block_tiles(const b200_block_geom* g);
+
 /* Symmetric (peer-mapped) memory: zeroed cudaMalloc + CUDA IPC handles (64 bytes) exchanged by
  * the caller (torch.distributed); replaces MPI host buffers. */
 int b200_symm_alloc(size_t bytes, void** ptr);

@@ -1,0 +1,67 @@
+"""tcgen05 TF32 fused kernels vs the fp32 oracle (tolerances are TF32's: 10-bit mantissa operands,
+fp32 accumulate; SURVEY §7.3 'exactness ladder')."""
+import pytest
+import torch
+
+from b200cnn import default_config
+from b200cnn.config import INIT_RAND, LRN_V1, LRN_V3
+from b200cnn.models.init import make_problem
+from b200cnn.models.alexnet import forward_torch_reference
+
+pytestmark = pytest.mark.gpu
+TOL = 4e-3          # max abs err / max abs ref
+
+
+def _rel(a, b):
+    return ((a - b).abs().max() / b.abs().max()).item()
+
+
+@pytest.mark.parametrize("H,W,batch", [(227, 227, 3), (99, 131, 2), (67, 67, 1), (163, 227, 5)])
+def test_tc_matches_oracle(H, W, batch):
+    from b200cnn.models.engine import single_gpu_engine
+    cfg = default_config(H=H, W=W, batch=batch, init=INIT_RAND, seed=5, precision="tf32")
+    x, w = make_problem(cfg)
+    ref = forward_torch_reference(x, w, cfg)
+    eng = single_gpu_engine(cfg, w, "cuda:0")
+    y = eng.forward(x.cuda()).cpu()
+    eng.check_status()
+    p1 = eng.buf_pool1.tensor((batch, eng.sh.Hp1, eng.sh.Wp1, eng.sh.K1)).cpu()
+    assert _rel(p1, forward_torch_reference(x, w, cfg, upto="pool1")) < TOL
+    assert y.shape == ref.shape
+    assert _rel(y, ref) < TOL
+    y2 = eng.forward(x.cuda()).cpu()
+    assert torch.equal(y, y2)
+
+
+def test_tc_const_closed_form():
+    from b200cnn.models.engine import single_gpu_engine
+    for mode, want in ((LRN_V1, 44.4152), (LRN_V3, 29.2932)):
+        cfg = default_config(lrn_mode=mode, precision="tf32")
+        x, w = make_problem(cfg)
+        eng = single_gpu_engine(cfg, w, "cuda:0")
+        y = eng.forward(x.cuda()).cpu()
+        assert abs(y[0, 0, 0, 0].item() - want) / want < 2e-3
+        assert abs(y[0, 12, 12, 255].item() - want) / want < 2e-3
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("strategy,scatter", [("halo", "p2p"), ("halo", "sharded"), ("recompute", "p2p")])
+def test_tc_emulated_ranks_equal_single(world, strategy, scatter):
+    from b200cnn.models.engine import single_gpu_engine, EmulatedWorld
+    cfg = default_config(batch=2, init=INIT_RAND, seed=9, precision="tf32")
+    x, w = make_problem(cfg)
+    one = single_gpu_engine(cfg, w, "cuda:0").forward(x.cuda()).clone()
+    ew = EmulatedWorld(cfg, w, world, "cuda:0", strategy=strategy, scatter=scatter)
+    for _ in range(2):
+        y = ew.forward(x.cuda())
+        # every output is the same K-ordered tensor-core accumulation wherever its tile lies
+        assert torch.equal(y, one)
+
+
+def test_tc_agrees_with_simt_twin():
+    from b200cnn.models.engine import single_gpu_engine
+    cfg = default_config(batch=2, init=INIT_RAND, seed=21)
+    x, w = make_problem(cfg)
+    a = single_gpu_engine(cfg, w, "cuda:0", "simt").forward(x.cuda()).clone()
+    b = single_gpu_engine(cfg, w, "cuda:0", "tf32").forward(x.cuda()).clone()
+    assert _rel(b, a) < TOL
