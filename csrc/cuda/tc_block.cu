@@ -48,16 +48,21 @@ constexpr int kCbufBytes = kTileM * kCbufPitch * 4;
 constexpr int kMaxPooled = 64;                     // pooled outputs per tile
 constexpr unsigned long long kSpinTimeoutNs = 4000000000ull;
 
+constexpr int kRowTab = 192;                       // row-pointer table entries (vec mode)
+
 struct TcParams {
     b200_block_geom g;
     int TR, TC, PR, PC;
     int tiles_r, tiles_c;
     int nacc;
-    int nkb, Kdim;
+    int nkb;
     int stages, b_stage_bytes;
-    int vec_mode;
     int tmem_cols;
     int any_flag;
+    int round_out;               // round stored outputs to TF32 (next layer's A operand is then exact)
+    int FCpad;                   // patch mode: floats per filter row in K (F*C rounded up to 4)
+    int patch_rows, patch_pitch; // patch mode: staged input patch (rows incl. 1 guard row, floats per row)
+    uint32_t patch_off, ctl_off;
     uint32_t idesc;
     long long total_tiles;
 };
@@ -156,6 +161,21 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 __device__ __forceinline__ void bar_producers() {     // named barrier 1: the 8 producer warps
     asm volatile("bar.sync 1, %0;" ::"n"(kProducerThreads) : "memory");
 }
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src, uint32_t bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.wait_all;" ::: "memory");
+}
+// the mbarrier gets one arrival from this thread once all its earlier cp.async have landed
+__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ float to_tf32(float x) {
     uint32_t u;
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
@@ -183,6 +203,16 @@ __device__ __forceinline__ const float* seg_row_ptr(const b200_block_geom& g, in
 }
 
 // ------------------------------------------------------------------------ kernel ----
+// kPatch = false ("vec" mode, C % 32 == 0: conv2..5): a k-block is 32 channels of one filter tap;
+//   every A row is 128 contiguous bytes of the activation -> cp.async 16 B straight into the
+//   swizzled stage, completion tracked by the stage's mbarrier (cp.async.mbarrier.arrive.noinc).
+//   K order (channel-chunk, fy, fx, c%32): consecutive k-blocks re-read neighbouring pixels, so
+//   the small L1 that is left catches most of the im2col re-reads (local and NVLink-mapped rows).
+// kPatch = true  (conv1, C = 3): the input patch of the tile is staged ONCE in shared memory (one
+//   pull over NVLink in p2p-scatter mode instead of (F/S)^2 re-reads), then expanded to A with
+//   LDS.128 -> cvt.rna.tf32 -> STS.128.  K order (fy, [fx,c] padded to a multiple of 4): for a fixed
+//   filter row the F*C inputs of a pixel are contiguous, so every 16 B chunk is an aligned LDS.128.
+template <bool kPatch>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant__ TcParams p,
                 const float* __restrict__ bias, float* __restrict__ out) {
@@ -193,15 +223,15 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
     // carve shared memory (1024 B aligned for the swizzle atoms)
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
-    const uint32_t a_off = 0;
     const uint32_t b_off = p.stages * kAStageBytes;
-    const uint32_t ctl_off = b_off + p.stages * p.b_stage_bytes;
-    const uint32_t full_bar = base + ctl_off;                 // [stages]
+    const uint32_t full_bar = base + p.ctl_off;               // [stages]
     const uint32_t empty_bar = full_bar + 8 * p.stages;       // [stages]
     const uint32_t tmem_full_bar = empty_bar + 8 * p.stages;
     const uint32_t tile_free_bar = tmem_full_bar + 8;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + ctl_off + 16 * p.stages + 16);
-    float* s_bias = reinterpret_cast<float*>(gbase + ctl_off + 16 * p.stages + 32);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + p.ctl_off + 16 * p.stages + 16);
+    const float** rowtab = reinterpret_cast<const float**>(gbase + p.ctl_off + 16 * p.stages + 32);
+    float* s_bias = reinterpret_cast<float*>(gbase + p.ctl_off + 16 * p.stages + 32 + kRowTab * 8);
+    float* patch = reinterpret_cast<float*>(gbase + p.patch_off);
     float* cbuf0 = reinterpret_cast<float*>(gbase);           // epilogue buffers alias the stages
     float* pbuf = reinterpret_cast<float*>(gbase + 2 * kCbufBytes);
 
@@ -209,7 +239,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.stages; ++s) {
-            mbar_init(full_bar + 8 * s, kProducerWarps + 1);
+            mbar_init(full_bar + 8 * s, kProducerThreads + 1);    // every producer thread + TMA
             mbar_init(empty_bar + 8 * s, 1);
         }
         mbar_init(tmem_full_bar, 1);
@@ -233,6 +263,9 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
         const int j = tid & 7;                                // 16 B chunk inside the 128 B row
         const int m_base = tid >> 3;                          // rows m_base + 32*i
         const uint32_t row_sw = (uint32_t)(m_base & 7);       // (m & 7) is the same for all i
+        // byte offset of (row m_base, chunk j) inside a stage; row m_base+32*i adds i*4096
+        const uint32_t dst0 = (uint32_t)(m_base >> 3) * 1024u + row_sw * 128u + (((uint32_t)j ^ row_sw) << 4);
+        const int IRT = (p.TR - 1) * g.S + g.F;               // input rows a tile touches
         int it = 0;
         for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x, ++it) {
             const int n = (int)(w / tiles_per_img);
@@ -240,78 +273,92 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
             const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
             const int pr0 = g.p0 + tr_i * p.PR, pc0 = tc_i * p.PC;
             const int cr0 = 2 * pr0, cc0 = 2 * pc0;
+            const int ir0 = cr0 * g.S - g.P;                   // first input row of the tile
 
             if (p.any_flag) {                                  // consumer side of the halo flags
                 if (tid == 0) {
-                    const int ir0 = cr0 * g.S - g.P, ir1 = (cr0 + p.TR - 1) * g.S - g.P + g.F;
                     for (int s = 0; s < g.nseg; ++s)
-                        if (g.seg[s].flag && ir0 < g.seg[s].hi && ir1 > g.seg[s].lo)
+                        if (g.seg[s].flag && ir0 < g.seg[s].hi && ir0 + IRT > g.seg[s].lo)
                             wait_flag_ge(g.seg[s].flag + n, g.seg[s].target, g.status, g.timeout_ns);
                 }
                 bar_producers();
             }
 
-            int h0[8], w0[8];
+            int rsel[8];        // vec: row-table index of the pixel's first input row; patch: float offset
+            int xo[8];          // vec: input column of the pixel's first tap
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int m = m_base + 32 * i;
                 const int pi = m / p.TC, pj = m - pi * p.TC;
-                const int cy = cr0 + pi, cx = cc0 + pj;
-                const bool ok = (m < p.TR * p.TC) && cy < g.Hc && cx < g.Wc;
-                h0[i] = ok ? cy * g.S - g.P : -(1 << 20);      // invalid slot -> always out of range
-                w0[i] = cx * g.S - g.P;
+                const bool ok = (m < p.TR * p.TC) && (cr0 + pi) < g.Hc && (cc0 + pj) < g.Wc;
+                if (kPatch) {
+                    rsel[i] = ok ? pi * g.S * p.patch_pitch + pj * g.S * g.C : 0;
+                    xo[i] = 0;
+                } else {
+                    rsel[i] = ok ? pi * g.S : IRT;             // IRT.. = null rows -> zero fill
+                    xo[i] = (cc0 + pj) * g.S - g.P;
+                }
             }
 
+            if (kPatch) {
+                // ---- stage the input patch once (rows ir0.., float columns cf0..) ----
+                const int cf0 = (cc0 * g.S - g.P) * g.C, WC = g.W * g.C;
+                const uint32_t patch_s = smem_u32(patch);
+                for (int r = 0; r < p.patch_rows; ++r) {
+                    const int h = ir0 + r;
+                    const float* rp = (h >= 0 && h < g.H) ? seg_row_ptr(g, n, h) : nullptr;
+                    for (int f = tid; f < p.patch_pitch; f += kProducerThreads) {
+                        const int cf = cf0 + f;
+                        const bool v = rp && cf >= 0 && cf < WC;
+                        cp_async4(patch_s + (uint32_t)(r * p.patch_pitch + f) * 4u,
+                                  v ? (const void*)(rp + cf) : (const void*)g.seg[0].ptr, v ? 4u : 0u);
+                    }
+                }
+                cp_async_wait_all();
+                bar_producers();
+            } else {
+                // ---- row-pointer table: base pointer of every input row of this tile ----
+                if (tid < IRT + g.F) {
+                    const int h = ir0 + tid;
+                    rowtab[tid] = (tid < IRT && h >= 0 && h < g.H) ? seg_row_ptr(g, n, h) : nullptr;
+                }
+                bar_producers();
+            }
+
+            // k-block walk state
+            int fy = 0, fx = 0, cch = 0;                        // vec: tap + channel chunk (uniform)
+            int pfy = (4 * j) / p.FCpad, pt = (4 * j) - pfy * p.FCpad;   // patch: this thread's chunk
             for (int kb = 0; kb < p.nkb; ++kb) {
                 mbar_wait(empty_bar + 8 * stage, phase ^ 1);
-                const uint32_t a_stage = base + a_off + stage * kAStageBytes;
-                float4 v[8];
-                if (p.vec_mode) {
-                    const int cpb = g.C / kBlockK;
-                    const int tap = kb / cpb, c0 = (kb - tap * cpb) * kBlockK + 4 * j;
-                    const int fy = tap / g.F, fx = tap - fy * g.F;
+                const uint32_t a_dst = base + stage * kAStageBytes + dst0;
+                const uint32_t fb = full_bar + 8 * stage;
+                if (kPatch) {
+                    const float* src = patch + pfy * p.patch_pitch + pt;
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
-                        const int h = h0[i] + fy, x = w0[i] + fx;
-                        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (h >= 0 && h < g.H && x >= 0 && x < g.W) {
-                            const float* rp = seg_row_ptr(g, n, h);
-                            if (rp) v[i] = *reinterpret_cast<const float4*>(rp + (size_t)x * g.C + c0);
-                        }
+                        const float4 v = *reinterpret_cast<const float4*>(src + rsel[i]);
+                        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a_dst + i * 4096u),
+                                     "f"(to_tf32(v.x)), "f"(to_tf32(v.y)), "f"(to_tf32(v.z)),
+                                     "f"(to_tf32(v.w))
+                                     : "memory");
                     }
+                    fence_proxy_async_smem();                  // generic stores -> async proxy (UMMA)
+                    mbar_arrive(fb);
+                    pt += kBlockK;
+                    while (pt >= p.FCpad) { pt -= p.FCpad; ++pfy; }
                 } else {
-                    const int FC = g.F * g.C, WC = g.W * g.C;
-                    const int k0 = kb * kBlockK + 4 * j;
+                    const int coff = cch * kBlockK + 4 * j;
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
-                        float e[4];
-#pragma unroll
-                        for (int q = 0; q < 4; ++q) {
-                            const int k = k0 + q;
-                            const int fy = k / FC, t = k - fy * FC;
-                            const int h = h0[i] + fy, cf = w0[i] * g.C + t;
-                            e[q] = 0.f;
-                            if (k < p.Kdim && h >= 0 && h < g.H && cf >= 0 && cf < WC) {
-                                const float* rp = seg_row_ptr(g, n, h);
-                                if (rp) e[q] = rp[cf];
-                            }
-                        }
-                        v[i] = make_float4(e[0], e[1], e[2], e[3]);
+                        const float* rp = rowtab[rsel[i] + fy];
+                        const int x = xo[i] + fx;
+                        const bool v = rp != nullptr && (unsigned)x < (unsigned)g.W;
+                        const float* src = v ? rp + (size_t)x * g.C + coff : g.seg[0].ptr;
+                        cp_async16(a_dst + i * 4096u, src, v ? 16u : 0u);
                     }
+                    cp_async_mbar_arrive_noinc(fb);            // arrives when this thread's copies land
+                    if (++fx == g.F) { fx = 0; if (++fy == g.F) { fy = 0; ++cch; } }
                 }
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const int m = m_base + 32 * i;
-                    const uint32_t dst = a_stage + (uint32_t)(m >> 3) * 1024u + row_sw * 128u +
-                                         (((uint32_t)j ^ row_sw) << 4);
-                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst),
-                                 "f"(to_tf32(v[i].x)), "f"(to_tf32(v[i].y)), "f"(to_tf32(v[i].z)),
-                                 "f"(to_tf32(v[i].w))
-                                 : "memory");
-                }
-                fence_proxy_async_smem();                      // generic stores -> async proxy (UMMA)
-                __syncwarp();
-                if (lane == 0) mbar_arrive(full_bar + 8 * stage);
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
 
@@ -344,11 +391,12 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
 #pragma unroll
                         for (int b = 0; b < 3; ++b)
                             mx = fmaxf(mx, c0p[(a * p.TC + b) * kCbufPitch]);
-                    const float val = fmaxf(mx + bch, 0.f);    // relu(max(x)+b) == max(relu(x+b))
+                    float val = fmaxf(mx + bch, 0.f);          // relu(max(x)+b) == max(relu(x+b))
                     if (do_lrn) {
                         pbuf[pp * N + cc * 32 + lane] = val;
                     } else {
                         const int pr = pr0 + pi, pc = pc0 + pj;
+                        if (p.round_out) val = to_tf32(val);
                         if (pr < g.p1 && pr < g.Hp && pc < g.Wp)
                             out[(((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N +
                                 cc * 32 + lane] = val;
@@ -371,7 +419,8 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                         const float x = pbuf[pp * N + q];
                         ss = fmaf(x, x, ss);
                     }
-                    const float val = pbuf[idx] / powf(g.lrn.k + al * ss, g.lrn.beta);
+                    float val = pbuf[idx] / powf(g.lrn.k + al * ss, g.lrn.beta);
+                    if (p.round_out) val = to_tf32(val);
                     out[(((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N + c] = val;
                 }
             }
@@ -391,7 +440,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                 mbar_wait(full_bar + 8 * stage, phase);
                 tc_fence_after();
                 if (lane == 0) {
-                    const uint32_t a_stage = base + a_off + stage * kAStageBytes;
+                    const uint32_t a_stage = base + stage * kAStageBytes;
                     const uint32_t b_stage = base + b_off + stage * p.b_stage_bytes;
                     const uint64_t db = make_smem_desc(b_stage);
 #pragma unroll
@@ -438,7 +487,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
 
 // --------------------------------------------------------------------------- host ----
 struct TcConv {
-    int K, C, F, Kdim, Kpad, device;
+    int K, C, F, Kpad, device, patch_mode, FCpad;
     float* d_w;
     CUtensorMap tmap;
 };
@@ -470,46 +519,73 @@ inline float host_tf32(float x) {                     // round to nearest, ties 
 }
 
 inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+inline bool is_patch_mode(int C) { return C % kBlockK != 0; }
+inline int fcpad(int F, int C) { return (F * C + 3) & ~3; }
+inline int num_kblocks(int F, int C) {
+    return is_patch_mode(C) ? cdiv(F * fcpad(F, C), kBlockK) : (C / kBlockK) * F * F;
+}
+
+constexpr int kMaxPatchBytes = 64 * 1024;
 
 // Tile planner: PR x PC pooled outputs per tile, (2PR+1)(2PC+1) <= 128*nacc pixel slots; minimise
 // tiles * nacc (MMA time), then slots.  Deterministic: peers call it to predict tile counts.
 bool plan_tiles(const b200_block_geom* g, TcParams* p) {
     const int rows = g->p1 - g->p0;
+    const bool patch = is_patch_mode(g->C);
     long best = -1;
     for (int nacc = 1; nacc <= 2; ++nacc)
         for (int PR = 1; PR <= rows && PR <= 63; ++PR)
             for (int PC = 1; PC <= g->Wp; ++PC) {
-                const int slots = (2 * PR + 1) * (2 * PC + 1);
+                const int TR = 2 * PR + 1, TC = 2 * PC + 1;
+                const int slots = TR * TC;
                 if (slots > 128 * nacc) break;
                 if (PR * PC > kMaxPooled) break;
+                if ((TR - 1) * g->S + 2 * g->F > kRowTab) break;
+                if (patch) {
+                    const int prow = (TR - 1) * g->S + g->F + 1;
+                    const int pitch = ((TC - 1) * g->S * g->C + fcpad(g->F, g->C) + 3) & ~3;
+                    if (prow * pitch * 4 > kMaxPatchBytes) break;
+                }
                 const long cost = (long)cdiv(rows, PR) * cdiv(g->Wp, PC) * nacc * 1024 + slots;
                 if (best < 0 || cost < best) {
                     best = cost;
-                    p->PR = PR; p->PC = PC; p->TR = 2 * PR + 1; p->TC = 2 * PC + 1; p->nacc = nacc;
+                    p->PR = PR; p->PC = PC; p->TR = TR; p->TC = TC; p->nacc = nacc;
                     p->tiles_r = cdiv(rows, PR); p->tiles_c = cdiv(g->Wp, PC);
                 }
             }
     return best >= 0;
 }
 
-int fill_params(const b200_block_geom* g, TcParams* p) {
+int fill_params(const b200_block_geom* g, TcParams* p, int flags) {
     if (g->K % 32 != 0 || g->K > 256 || g->K < 32) return B200_ERR_UNSUPPORTED;
+    const bool patch = is_patch_mode(g->C);
+    if (patch && (g->S * g->C) % 4 != 0) return B200_ERR_UNSUPPORTED;   // LDS.128 alignment
     memset(p, 0, sizeof(*p));
     p->g = *g;
     if (!plan_tiles(g, p)) return B200_ERR_ARG;
-    p->Kdim = g->F * g->F * g->C;
-    p->nkb = cdiv(p->Kdim, kBlockK);
-    p->vec_mode = (g->C % kBlockK == 0) ? 1 : 0;
+    p->nkb = num_kblocks(g->F, g->C);
+    p->FCpad = fcpad(g->F, g->C);
+    p->round_out = flags & 1;
     p->b_stage_bytes = g->K * 128;
+    size_t patch_bytes = 0;
+    if (patch) {
+        p->patch_rows = (p->TR - 1) * g->S + g->F + 1;
+        p->patch_pitch = ((p->TC - 1) * g->S * g->C + p->FCpad + 3) & ~3;
+        patch_bytes = (size_t)p->patch_rows * p->patch_pitch * 4;
+    }
+    const size_t ctl_bytes = 16 * 4 + 32 + kRowTab * 8 + (size_t)g->K * 4 + 64;
+    const size_t epi = 2 * (size_t)kCbufBytes + (g->lrn.N_lrn > 0 ? (size_t)kMaxPooled * g->K * 4 : 0);
     const int stage_bytes = kAStageBytes + p->b_stage_bytes;
-    int stages = (200 * 1024) / stage_bytes;
+    const long avail = 226 * 1024 - 1024 - (long)patch_bytes - (long)ctl_bytes;
+    int stages = (int)(avail / stage_bytes);
     if (stages > 4) stages = 4;
-    if (stages < 2) return B200_ERR_UNSUPPORTED;
+    if (stages < 2 || (size_t)stages * stage_bytes < epi) return B200_ERR_UNSUPPORTED;
     p->stages = stages;
+    p->patch_off = (uint32_t)((size_t)stages * stage_bytes);
+    p->ctl_off = (uint32_t)((p->patch_off + patch_bytes + 15) & ~(size_t)15);
     int cols = 32;
     while (cols < 2 * g->K) cols *= 2;                 // two accumulators of N columns
     p->tmem_cols = cols;
-    p->any_flag = 0;
     for (int s = 0; s < g->nseg; ++s)
         if (g->seg[s].flag) p->any_flag = 1;
     // instruction descriptor: D=f32, A=B=tf32, both K-major, M=128, N=K
@@ -519,10 +595,7 @@ int fill_params(const b200_block_geom* g, TcParams* p) {
 }
 
 size_t smem_bytes(const TcParams& p) {
-    size_t pipe = (size_t)p.stages * (kAStageBytes + p.b_stage_bytes);
-    size_t epi = 2 * (size_t)kCbufBytes + (size_t)kMaxPooled * p.g.K * 4;
-    if (epi > pipe) pipe = epi;                         // epilogue buffers alias the stages
-    return 1024 + pipe + 16 * p.stages + 32 + (size_t)p.g.K * 4 + 64;
+    return 1024 + (size_t)p.ctl_off + 16 * p.stages + 32 + kRowTab * 8 + (size_t)p.g.K * 4 + 64;
 }
 
 }  // namespace
@@ -533,17 +606,22 @@ extern "C" int b200_tc_conv_create(const float* w_kcff, int K, int C, int F, voi
     if (!enc) { set_error("cuTensorMapEncodeTiled entry point not available"); return B200_ERR_CUDA; }
     TcConv* t = new TcConv();
     t->K = K; t->C = C; t->F = F;
-    t->Kdim = F * F * C;
-    t->Kpad = cdiv(t->Kdim, kBlockK) * kBlockK;
+    t->patch_mode = is_patch_mode(C) ? 1 : 0;
+    t->FCpad = fcpad(F, C);
+    t->Kpad = num_kblocks(F, C) * kBlockK;
     B200_CUDA_TRY(cudaGetDevice(&t->device));
-    // [K][C][F][F] -> K-major rows [K][Kpad], k = (fy*F+fx)*C + c, TF32-rounded, zero padded
+    // [K][C][F][F] -> K-major rows [K][Kpad], TF32-rounded, zero padded; k order per mode (see kernel)
     std::vector<float> wk((size_t)K * t->Kpad, 0.f);
     for (int k = 0; k < K; ++k)
         for (int c = 0; c < C; ++c)
             for (int fy = 0; fy < F; ++fy)
-                for (int fx = 0; fx < F; ++fx)
-                    wk[(size_t)k * t->Kpad + (fy * F + fx) * C + c] =
+                for (int fx = 0; fx < F; ++fx) {
+                    const int kk = t->patch_mode
+                                       ? fy * t->FCpad + fx * C + c
+                                       : ((c / kBlockK) * F * F + fy * F + fx) * kBlockK + c % kBlockK;
+                    wk[(size_t)k * t->Kpad + kk] =
                         host_tf32(w_kcff[(((size_t)k * C + c) * F + fy) * F + fx]);
+                }
     B200_CUDA_TRY(cudaMalloc(&t->d_w, wk.size() * sizeof(float)));
     B200_CUDA_TRY(cudaMemcpy(t->d_w, wk.data(), wk.size() * sizeof(float), cudaMemcpyHostToDevice));
     cuuint64_t dims[2] = {(cuuint64_t)t->Kpad, (cuuint64_t)K};
@@ -576,13 +654,14 @@ extern "C" int b200_tc_block_tiles(const b200_block_geom* g) {
     if (!g) return B200_ERR_ARG;
     if (g->p1 <= g->p0) return 0;
     TcParams p;
-    int rc = fill_params(g, &p);
+    int rc = fill_params(g, &p, 0);
     if (rc != B200_OK) return rc;
     return p.tiles_r * p.tiles_c;
 }
 
+// flags bit 0: round the stored outputs to TF32 (use for activations feeding another tc block)
 extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const b200_block_geom* g,
-                             void* stream) {
+                             int flags, void* stream) {
     TcConv* t = (TcConv*)handle;
     if (!t || !bias || !out || !g) return B200_ERR_ARG;
     if (g->nseg < 1 || g->nseg > B200_MAX_SEG || g->n_signal < 0 || g->n_signal > B200_MAX_SIGNAL)
@@ -590,16 +669,22 @@ extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const 
     if (g->K != t->K || g->C != t->C || g->F != t->F) return B200_ERR_ARG;
     if (g->p1 <= g->p0 || g->N <= 0) return B200_OK;
     TcParams p;
-    int rc = fill_params(g, &p);
+    int rc = fill_params(g, &p, flags);
     if (rc != B200_OK) return rc;
     const size_t smem = smem_bytes(p);
     if (smem > 227 * 1024) return B200_ERR_UNSUPPORTED;
     static int sms = 0;
     if (!sms) B200_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, t->device));
-    B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)smem));
     const unsigned grid = (unsigned)(p.total_tiles < sms ? p.total_tiles : sms);
-    tc_block_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(t->tmap, p, bias, out);
+    if (t->patch_mode) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_kernel<true>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        tc_block_kernel<true><<<grid, kThreads, smem, (cudaStream_t)stream>>>(t->tmap, p, bias, out);
+    } else {
+        B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_kernel<false>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        tc_block_kernel<false><<<grid, kThreads, smem, (cudaStream_t)stream>>>(t->tmap, p, bias, out);
+    }
     B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;
 }

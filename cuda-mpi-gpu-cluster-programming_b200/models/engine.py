@@ -213,7 +213,7 @@ class Blocks12Engine:
         if self.precision == "simt":
             cu.simt_block(self.w1p, self.b1, self.buf_pool1.ptr, g)
         else:
-            self.tc1.run(self.b1, self.buf_pool1.ptr, g)
+            self.tc1.run(self.b1, self.buf_pool1.ptr, g, round_out=True)
         self.launches += 1
 
     def stage_block2(self, out_idx: int = 0) -> None:

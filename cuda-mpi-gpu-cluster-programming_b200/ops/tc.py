@@ -25,7 +25,7 @@ def _lib():
         L.b200_tc_conv_destroy.argtypes = [C.c_void_p]
         L.b200_tc_block_tiles.argtypes = [C.POINTER(cu.BlockGeom)]
         L.b200_tc_block.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(cu.BlockGeom),
-                                    C.c_void_p]
+                                    C.c_int, C.c_void_p]
         _bound = True
     return L
 
@@ -41,9 +41,9 @@ class TcConv:
                         "tc_conv_create")
         self._h = h
 
-    def run(self, bias: torch.Tensor, out_ptr: int, g: cu.BlockGeom) -> None:
+    def run(self, bias: torch.Tensor, out_ptr: int, g: cu.BlockGeom, round_out: bool = False) -> None:
         cu.cu_check(_lib().b200_tc_block(self._h, fptr(bias), C.c_void_p(out_ptr), C.byref(g),
-                                         cu.current_stream_ptr()), "tc_block")
+                                         1 if round_out else 0, cu.current_stream_ptr()), "tc_block")
 
     def __del__(self):
         try:

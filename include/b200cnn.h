@@ -142,7 +142,7 @@ int b200_simt_block_tiles(const b200_block_geom* g);
 int b200_tc_conv_create(const float* w_kcff, int K, int C, int F, void** handle);
 int b200_tc_conv_destroy(void* handle);
 int b200_tc_block(void* handle, const float* bias, float* out, const b200_block_geom* g,
-                  void* stream);
+                  int flags /* bit0: round outputs to TF32 */, void* stream);
 int b200_tc_block_tiles(const b200_block_geom* g);
 
 /* Symmetric (peer-mapped) memory: zeroed cudaMalloc + CUDA IPC handles (64 bytes) exchanged by
