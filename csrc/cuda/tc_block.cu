@@ -284,8 +284,10 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                 bar_producers();
             }
 
+            // per-thread description of its 8 A rows (pixels m_base + 32*i)
             int rsel[8];        // vec: row-table index of the pixel's first input row; patch: float offset
-            int xo[8];          // vec: input column of the pixel's first tap
+            int cbyte[8];       // vec: byte offset of (first tap column, chunk j) inside an input row
+            uint32_t xmask[8];  // vec: bit fx set <=> input column x0+fx lies inside the image
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int m = m_base + 32 * i;
@@ -293,42 +295,59 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                 const bool ok = (m < p.TR * p.TC) && (cr0 + pi) < g.Hc && (cc0 + pj) < g.Wc;
                 if (kPatch) {
                     rsel[i] = ok ? pi * g.S * p.patch_pitch + pj * g.S * g.C : 0;
-                    xo[i] = 0;
+                    cbyte[i] = 0; xmask[i] = 0;
                 } else {
+                    const int x0 = (cc0 + pj) * g.S - g.P;
                     rsel[i] = ok ? pi * g.S : IRT;             // IRT.. = null rows -> zero fill
-                    xo[i] = (cc0 + pj) * g.S - g.P;
+                    cbyte[i] = (x0 * g.C + 4 * j) * 4;
+                    uint32_t mk = 0;
+                    for (int f = 0; f < g.F; ++f) mk |= ((unsigned)(x0 + f) < (unsigned)g.W ? 1u : 0u) << f;
+                    xmask[i] = mk;
                 }
+            }
+
+            // ---- row-pointer table: base pointer of every input row this tile touches ----
+            {
+                const int nrows = kPatch ? p.patch_rows : IRT + g.F;
+                const int nreal = kPatch ? p.patch_rows : IRT;
+                if (tid < nrows) {
+                    const int h = ir0 + tid;
+                    rowtab[tid] = (tid < nreal && h >= 0 && h < g.H) ? seg_row_ptr(g, n, h) : nullptr;
+                }
+                bar_producers();
             }
 
             if (kPatch) {
                 // ---- stage the input patch once (rows ir0.., float columns cf0..) ----
                 const int cf0 = (cc0 * g.S - g.P) * g.C, WC = g.W * g.C;
                 const uint32_t patch_s = smem_u32(patch);
-                for (int r = 0; r < p.patch_rows; ++r) {
-                    const int h = ir0 + r;
-                    const float* rp = (h >= 0 && h < g.H) ? seg_row_ptr(g, n, h) : nullptr;
-                    for (int f = tid; f < p.patch_pitch; f += kProducerThreads) {
-                        const int cf = cf0 + f;
-                        const bool v = rp && cf >= 0 && cf < WC;
-                        cp_async4(patch_s + (uint32_t)(r * p.patch_pitch + f) * 4u,
-                                  v ? (const void*)(rp + cf) : (const void*)g.seg[0].ptr, v ? 4u : 0u);
+                for (int f = tid; f < p.patch_pitch; f += kProducerThreads) {
+                    const int cf = cf0 + f;
+                    const bool cv = cf >= 0 && cf < WC;
+                    uint32_t dst = patch_s + (uint32_t)f * 4u;
+                    for (int r = 0; r < p.patch_rows; ++r, dst += (uint32_t)p.patch_pitch * 4u) {
+                        const float* rp = rowtab[r];
+                        const bool v = cv && rp != nullptr;
+                        cp_async4(dst, rp + cf, v ? 4u : 0u);   // size 0: nothing is read, zero fill
                     }
                 }
                 cp_async_wait_all();
-                bar_producers();
-            } else {
-                // ---- row-pointer table: base pointer of every input row of this tile ----
-                if (tid < IRT + g.F) {
-                    const int h = ir0 + tid;
-                    rowtab[tid] = (tid < IRT && h >= 0 && h < g.H) ? seg_row_ptr(g, n, h) : nullptr;
-                }
                 bar_producers();
             }
 
             // k-block walk state
             int fy = 0, fx = 0, cch = 0;                        // vec: tap + channel chunk (uniform)
             int pfy = (4 * j) / p.FCpad, pt = (4 * j) - pfy * p.FCpad;   // patch: this thread's chunk
+            const char* rp8[8];                                 // vec: row pointers for the current fy
+            uint32_t vm[8];                                     // vec: xmask, or 0 when the row is padding
             for (int kb = 0; kb < p.nkb; ++kb) {
+                if (!kPatch && fx == 0) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        rp8[i] = reinterpret_cast<const char*>(rowtab[rsel[i] + fy]);
+                        vm[i] = rp8[i] ? xmask[i] : 0u;
+                    }
+                }
                 mbar_wait(empty_bar + 8 * stage, phase ^ 1);
                 const uint32_t a_dst = base + stage * kAStageBytes + dst0;
                 const uint32_t fb = full_bar + 8 * stage;
@@ -347,14 +366,11 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                     pt += kBlockK;
                     while (pt >= p.FCpad) { pt -= p.FCpad; ++pfy; }
                 } else {
-                    const int coff = cch * kBlockK + 4 * j;
+                    const int off = (fx * g.C + cch * kBlockK) * 4;
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
-                        const float* rp = rowtab[rsel[i] + fy];
-                        const int x = xo[i] + fx;
-                        const bool v = rp != nullptr && (unsigned)x < (unsigned)g.W;
-                        const float* src = v ? rp + (size_t)x * g.C + coff : g.seg[0].ptr;
-                        cp_async16(a_dst + i * 4096u, src, v ? 16u : 0u);
+                        const uint32_t nb = ((vm[i] >> fx) & 1u) ? 16u : 0u;   // 0 => zero fill, no read
+                        cp_async16(a_dst + i * 4096u, rp8[i] + (cbyte[i] + off), nb);
                     }
                     cp_async_mbar_arrive_noinc(fb);            // arrives when this thread's copies land
                     if (++fx == g.F) { fx = 0; if (++fy == g.F) { fy = 0; ++cch; } }
@@ -408,20 +424,22 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                 const int half = g.lrn.N_lrn / 2;
                 const float al = g.lrn.mode == B200_LRN_ALPHA_OVER_N
                                      ? g.lrn.alpha / (float)g.lrn.N_lrn : g.lrn.alpha;
-                for (int idx = tid; idx < PP * N; idx += kProducerThreads) {
-                    const int pp = idx / N, c = idx - pp * N;
+                const float nbeta = -g.lrn.beta;
+                for (int pp = 0; pp < PP; ++pp) {
                     const int pi = pp / p.PC, pj = pp - pi * p.PC;
                     const int pr = pr0 + pi, pc = pc0 + pj;
-                    if (pr >= g.p1 || pr >= g.Hp || pc >= g.Wp) continue;
-                    float ss = 0.f;
-                    const int c_lo = max(0, c - half), c_hi = min(N - 1, c + half);
-                    for (int q = c_lo; q <= c_hi; ++q) {
-                        const float x = pbuf[pp * N + q];
-                        ss = fmaf(x, x, ss);
+                    if (pr >= g.p1 || pr >= g.Hp || pc >= g.Wp) continue;      // uniform
+                    const float* px = pbuf + pp * N;
+                    float* o = out + (((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N;
+                    for (int c = tid; c < N; c += kProducerThreads) {
+                        float ss = 0.f;
+                        const int c_lo = max(0, c - half), c_hi = min(N - 1, c + half);
+                        for (int q = c_lo; q <= c_hi; ++q) ss = fmaf(px[q], px[q], ss);
+                        // x / (k + a*ss)^beta; the base is >= k > 0, so exp2/log2 is safe and ~1 ulp-ish
+                        float val = px[c] * exp2f(nbeta * __log2f(g.lrn.k + al * ss));
+                        if (p.round_out) val = to_tf32(val);
+                        o[c] = val;
                     }
-                    float val = pbuf[idx] / powf(g.lrn.k + al * ss, g.lrn.beta);
-                    if (p.round_out) val = to_tf32(val);
-                    out[(((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N + c] = val;
                 }
             }
             // hand the stages / TMEM back: all tcgen05.ld of this warp are complete (wait::ld)
@@ -544,7 +562,7 @@ bool plan_tiles(const b200_block_geom* g, TcParams* p) {
                 if (patch) {
                     const int prow = (TR - 1) * g->S + g->F + 1;
                     const int pitch = ((TC - 1) * g->S * g->C + fcpad(g->F, g->C) + 3) & ~3;
-                    if (prow * pitch * 4 > kMaxPatchBytes) break;
+                    if (prow * pitch * 4 > kMaxPatchBytes || prow > kRowTab) break;
                 }
                 const long cost = (long)cdiv(rows, PR) * cdiv(g->Wp, PC) * nacc * 1024 + slots;
                 if (best < 0 || cost < best) {

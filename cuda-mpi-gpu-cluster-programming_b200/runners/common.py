@@ -1,0 +1,35 @@
+"""Shared pieces of the version runners (the L4 entry points)."""
+from __future__ import annotations
+
+import argparse
+import sys
+import time
+from typing import Optional
+
+from ..config import add_cli_flags, config_from_args, INIT_CONST, LRN_V1
+
+
+def make_parser(prog: str, *, init_default: str = INIT_CONST, lrn_default: str = LRN_V1):
+    ap = argparse.ArgumentParser(
+        prog=prog, description="With no arguments this reproduces the reference binary "
+        "(which ignores argv; SURVEY §0.2).  All flags are additions.")
+    add_cli_flags(ap, init_default=init_default, lrn_default=lrn_default)
+    ap.add_argument("--strategy", choices=["halo", "recompute"], default="halo")
+    ap.add_argument("--scatter", choices=["p2p", "sharded"], default="p2p")
+    ap.add_argument("--quiet-extras", action="store_true", help="print only the reference's lines")
+    return ap
+
+
+class WallTimer:
+    def __enter__(self):
+        self.t0 = time.perf_counter()
+        return self
+
+    def __exit__(self, *a):
+        self.ms = (time.perf_counter() - self.t0) * 1e3
+
+
+def fail(rank: int, msg: str, code: int = 1):
+    sys.stderr.write(f"[Rank {rank}] {msg}\n")
+    sys.stderr.flush()
+    raise SystemExit(code)
