@@ -28,6 +28,7 @@
 #include "common.cuh"
 
 #include <cuda.h>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -59,6 +60,7 @@ struct TcParams {
     int stages, b_stage_bytes;
     int tmem_cols;
     int any_flag;
+    int dbg;                     // perf experiments only: 1 skip A copies, 2 skip B TMA, 4 skip epilogue math
     int round_out;               // round stored outputs to TF32 (next layer's A operand is then exact)
     int FCpad;                   // patch mode: floats per filter row in K (F*C rounded up to 4)
     int patch_rows, patch_pitch; // patch mode: staged input patch (rows incl. 1 guard row, floats per row)
@@ -230,7 +232,9 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
     const uint32_t tile_free_bar = tmem_full_bar + 8;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + p.ctl_off + 16 * p.stages + 16);
     const float** rowtab = reinterpret_cast<const float**>(gbase + p.ctl_off + 16 * p.stages + 32);
-    float* s_bias = reinterpret_cast<float*>(gbase + p.ctl_off + 16 * p.stages + 32 + kRowTab * 8);
+    float* s_bias = reinterpret_cast<float*>(gbase + p.ctl_off + 16 * p.stages + 32 + kRowTab * 8 +
+                                             kMaxPooled * 8);
+    int2* ptab = reinterpret_cast<int2*>(gbase + p.ctl_off + 16 * p.stages + 32 + kRowTab * 8);
     float* patch = reinterpret_cast<float*>(gbase + p.patch_off);
     float* cbuf0 = reinterpret_cast<float*>(gbase);           // epilogue buffers alias the stages
     float* pbuf = reinterpret_cast<float*>(gbase + 2 * kCbufBytes);
@@ -266,6 +270,18 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
         // byte offset of (row m_base, chunk j) inside a stage; row m_base+32*i adds i*4096
         const uint32_t dst0 = (uint32_t)(m_base >> 3) * 1024u + row_sw * 128u + (((uint32_t)j ^ row_sw) << 4);
         const int IRT = (p.TR - 1) * g.S + g.F;               // input rows a tile touches
+        int pij[8];                                           // (pi << 16 | pj) of row i, -1 = unused slot
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int m = m_base + 32 * i;
+            const int pi = m / p.TC;
+            pij[i] = m < p.TR * p.TC ? (pi << 16) | (m - pi * p.TC) : -1;
+        }
+        if (tid < p.PR * p.PC) {                              // pooled pixel -> cbuf offset, (pi,pj)
+            const int pi = tid / p.PC, pj = tid - pi * p.PC;
+            ptab[tid] = make_int2(((2 * pi) * p.TC + 2 * pj) * kCbufPitch, (pi << 16) | pj);
+        }
+        bar_producers();
         int it = 0;
         for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x, ++it) {
             const int n = (int)(w / tiles_per_img);
@@ -290,9 +306,8 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
             uint32_t xmask[8];  // vec: bit fx set <=> input column x0+fx lies inside the image
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const int m = m_base + 32 * i;
-                const int pi = m / p.TC, pj = m - pi * p.TC;
-                const bool ok = (m < p.TR * p.TC) && (cr0 + pi) < g.Hc && (cc0 + pj) < g.Wc;
+                const int pi = pij[i] >> 16, pj = pij[i] & 0xFFFF;
+                const bool ok = pij[i] >= 0 && (cr0 + pi) < g.Hc && (cc0 + pj) < g.Wc;
                 if (kPatch) {
                     rsel[i] = ok ? pi * g.S * p.patch_pitch + pj * g.S * g.C : 0;
                     cbyte[i] = 0; xmask[i] = 0;
@@ -300,9 +315,8 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                     const int x0 = (cc0 + pj) * g.S - g.P;
                     rsel[i] = ok ? pi * g.S : IRT;             // IRT.. = null rows -> zero fill
                     cbyte[i] = (x0 * g.C + 4 * j) * 4;
-                    uint32_t mk = 0;
-                    for (int f = 0; f < g.F; ++f) mk |= ((unsigned)(x0 + f) < (unsigned)g.W ? 1u : 0u) << f;
-                    xmask[i] = mk;
+                    const int lo = max(0, -x0), hi = min(g.F, g.W - x0);   // valid taps [lo,hi)
+                    xmask[i] = hi > lo ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
                 }
             }
 
@@ -351,7 +365,9 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                 mbar_wait(empty_bar + 8 * stage, phase ^ 1);
                 const uint32_t a_dst = base + stage * kAStageBytes + dst0;
                 const uint32_t fb = full_bar + 8 * stage;
-                if (kPatch) {
+                if (p.dbg & 1) {
+                    mbar_arrive(fb);
+                } else if (kPatch) {
                     const float* src = patch + pfy * p.patch_pitch + pt;
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
@@ -373,6 +389,8 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                         cp_async16(a_dst + i * 4096u, rp8[i] + (cbyte[i] + off), nb);
                     }
                     cp_async_mbar_arrive_noinc(fb);            // arrives when this thread's copies land
+                }
+                if (!kPatch) {
                     if (++fx == g.F) { fx = 0; if (++fy == g.F) { fy = 0; ++cch; } }
                 }
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
@@ -387,7 +405,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
             const int PP = p.PR * p.PC;
             const int nchunk = N / 32;
             const bool do_lrn = g.lrn.N_lrn > 0;
-            for (int cc = 0; cc < nchunk; ++cc) {
+            for (int cc = 0; cc < ((p.dbg & 4) ? 0 : nchunk); ++cc) {
                 float* cb = cbuf0 + (cc & 1) * (kCbufBytes / 4);
                 if (has_acc) {
                     uint32_t r[32];
@@ -399,8 +417,8 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                 // pool: lane = channel inside the chunk, warp strides over pooled pixels
                 const float bch = s_bias[cc * 32 + lane];
                 for (int pp = warp; pp < PP; pp += kProducerWarps) {
-                    const int pi = pp / p.PC, pj = pp - pi * p.PC;
-                    const float* c0p = cb + ((2 * pi) * p.TC + 2 * pj) * kCbufPitch + lane;
+                    const int2 e = ptab[pp];
+                    const float* c0p = cb + e.x + lane;
                     float mx = -INFINITY;
 #pragma unroll
                     for (int a = 0; a < 3; ++a)
@@ -411,7 +429,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                     if (do_lrn) {
                         pbuf[pp * N + cc * 32 + lane] = val;
                     } else {
-                        const int pr = pr0 + pi, pc = pc0 + pj;
+                        const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
                         if (p.round_out) val = to_tf32(val);
                         if (pr < g.p1 && pr < g.Hp && pc < g.Wp)
                             out[(((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N +
@@ -419,15 +437,15 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                     }
                 }
             }
-            if (do_lrn) {
+            if (do_lrn && !(p.dbg & 4)) {
                 bar_producers();
                 const int half = g.lrn.N_lrn / 2;
                 const float al = g.lrn.mode == B200_LRN_ALPHA_OVER_N
                                      ? g.lrn.alpha / (float)g.lrn.N_lrn : g.lrn.alpha;
                 const float nbeta = -g.lrn.beta;
                 for (int pp = 0; pp < PP; ++pp) {
-                    const int pi = pp / p.PC, pj = pp - pi * p.PC;
-                    const int pr = pr0 + pi, pc = pc0 + pj;
+                    const int2 e = ptab[pp];
+                    const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
                     if (pr >= g.p1 || pr >= g.Hp || pc >= g.Wp) continue;      // uniform
                     const float* px = pbuf + pp * N;
                     float* o = out + (((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N;
@@ -486,8 +504,12 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                 mbar_wait(empty_bar + 8 * stage, phase ^ 1);
                 if (lane == 0) {
                     const uint32_t fb = full_bar + 8 * stage;
-                    mbar_arrive_expect_tx(fb, (uint32_t)p.b_stage_bytes);
-                    tma_load_2d(base + b_off + stage * p.b_stage_bytes, &tmapB, kb * kBlockK, 0, fb);
+                    if (p.dbg & 2) {
+                        mbar_arrive(fb);
+                    } else {
+                        mbar_arrive_expect_tx(fb, (uint32_t)p.b_stage_bytes);
+                        tma_load_2d(base + b_off + stage * p.b_stage_bytes, &tmapB, kb * kBlockK, 0, fb);
+                    }
                 }
                 __syncwarp();
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
@@ -584,6 +606,7 @@ int fill_params(const b200_block_geom* g, TcParams* p, int flags) {
     p->nkb = num_kblocks(g->F, g->C);
     p->FCpad = fcpad(g->F, g->C);
     p->round_out = flags & 1;
+    if (const char* e = getenv("B200_TC_DBG")) p->dbg = atoi(e);
     p->b_stage_bytes = g->K * 128;
     size_t patch_bytes = 0;
     if (patch) {
@@ -591,7 +614,7 @@ int fill_params(const b200_block_geom* g, TcParams* p, int flags) {
         p->patch_pitch = ((p->TC - 1) * g->S * g->C + p->FCpad + 3) & ~3;
         patch_bytes = (size_t)p->patch_rows * p->patch_pitch * 4;
     }
-    const size_t ctl_bytes = 16 * 4 + 32 + kRowTab * 8 + (size_t)g->K * 4 + 64;
+    const size_t ctl_bytes = 16 * 4 + 32 + kRowTab * 8 + kMaxPooled * 8 + (size_t)g->K * 4 + 64;
     const size_t epi = 2 * (size_t)kCbufBytes + (g->lrn.N_lrn > 0 ? (size_t)kMaxPooled * g->K * 4 : 0);
     const int stage_bytes = kAStageBytes + p->b_stage_bytes;
     const long avail = 226 * 1024 - 1024 - (long)patch_bytes - (long)ctl_bytes;
@@ -613,7 +636,8 @@ int fill_params(const b200_block_geom* g, TcParams* p, int flags) {
 }
 
 size_t smem_bytes(const TcParams& p) {
-    return 1024 + (size_t)p.ctl_off + 16 * p.stages + 32 + kRowTab * 8 + (size_t)p.g.K * 4 + 64;
+    return 1024 + (size_t)p.ctl_off + 16 * p.stages + 32 + kRowTab * 8 + kMaxPooled * 8 +
+           (size_t)p.g.K * 4 + 64;
 }
 
 }  // namespace

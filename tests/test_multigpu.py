@@ -1,0 +1,39 @@
+"""Real multi-GPU runs (one process per GPU over NCCL bootstrap + CUDA IPC peer memory).
+Needs >= 2 GPUs: spawned through bin/mpirun like the reference's `mpirun -np N ./template`."""
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+
+
+def _run(np_, variant, extra=()):
+    cmd = [sys.executable, os.path.join(ROOT, "bin", "mpirun"), "--oversubscribe", "-np", str(np_),
+           sys.executable, "-m", "b200cnn.runners.v4", variant, "--init", "rand", "--seed", "3",
+           "--batch", "4", "--iters", "3", *extra]
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+    assert p.returncode == 0, p.stdout + p.stderr
+    fnv = re.search(r"Output FNV1a64: (0x[0-9a-f]+)", p.stdout).group(1)
+    shape = re.search(r"^Final Output Shape: (\S+)", p.stdout, re.M).group(1)
+    return fnv, shape, p.stdout
+
+
+@pytest.mark.parametrize("variant", ["v4", "v5"])
+def test_np2_equals_np1(variant):
+    f1, s1, _ = _run(1, variant)
+    f2, s2, out = _run(2, variant)
+    assert s1 == s2 == "52x13x256"          # batch 4 x 13 rows
+    assert f1 == f2, out
+
+
+def test_all_gpus_equal_np1():
+    n = torch.cuda.device_count()
+    f1, _, _ = _run(1, "v4")
+    fn, _, out = _run(n, "v4")
+    assert f1 == fn, out
