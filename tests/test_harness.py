@@ -1,0 +1,74 @@
+"""Log-line contract and harness parser round trips."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+from b200cnn.harness import suite
+from b200cnn.utils import logfmt as L
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_cxx_float_matches_iostream():
+    assert L.cxx_float(44.415199) == "44.4152"
+    assert L.cxx_float(0.058493614) == "0.0584936"
+    assert L.cxx_float(87.12) == "87.12"
+    assert L.cxx_float(1e-5) == "1e-05"
+    assert L.cxx_float(123456789.0) == "1.23457e+08"
+
+
+def test_first_ms_wins_rule():
+    # extras never use the "<num> ms" form, so the canonical line is the first match
+    lines = L.v3_lines([1.0] * 10, 12.5) + list(L.extras(shape=(13, 13, 256), fnv=1, wall_ms=12.5,
+                                                          device_forward_ms_warm=0.5))
+    text = "\n".join(lines)
+    t, shape, vals = suite.parse_run_log(text)
+    assert t == "12.5" and shape == "13x13x256" and vals == "1 1 1 1 1"
+    assert text.count(" ms") == 1
+
+
+def test_parse_reference_style_logs():
+    v1 = "  [Input] Dimensions: H=227, W=227, C=3\nAlexNet Serial Forward Pass completed in 742 ms\n" \
+         "Final Output (first 10 values): 0.1 0.2 0.3 0.4 0.5 0.6 0.7 0.8 0.9 1...\n"
+    assert suite.parse_run_log(v1) == ("742", "227x227x3", "0.1 0.2 0.3 0.4 0.5")   # the reference's mis-parse
+    v2 = "shape: 13x13x256\nSample values: 44.4152 42.4612 40.6967 40.6967 40.6967\nExecution Time: 286.9 ms\n"
+    assert suite.parse_run_log(v2) == ("286.9", "13x13x256", "44.4152 42.4612 40.6967 40.6967 40.6967")
+    v4 = "Final Output Shape: 13x13x256\nFinal Output (first 10 values): 29.2932 25.9153 23.3255 23.3255 " \
+         "23.3255 23.3255 23.3255 23.3255 23.3255 23.3255\nAlexNet MPI+CUDA Forward Pass completed in 183.2 ms\n"
+    assert suite.parse_run_log(v4) == ("183.2", "13x13x256", "29.2932 25.9153 23.3255 23.3255 23.3255")
+
+
+def test_failure_classification():
+    assert suite.classify_failure(1, "CUDA error: no CUDA-capable device is detected")[0] == 2
+    assert suite.classify_failure(1, "There are not enough slots available in the system")[0] == 3
+    assert suite.classify_failure(139, "")[0] == 4
+    assert suite.classify_failure(124, "")[0] == 124
+    assert suite.classify_failure(7, "boom")[0] == 1
+
+
+def test_csv_header_is_the_references():
+    assert len(suite.CSV_HEADER) == 20
+    assert suite.CSV_HEADER[4:6] == ["ProjectVariant", "NumProcesses"]
+    assert suite.CSV_HEADER[-3:] == ["ExecutionTime_ms", "OutputShape", "OutputFirst5Values"]
+
+
+def test_suite_end_to_end_cpu_variants(tmp_path):
+    """make + run + parse for V1 and V2.2 np2 through the launchers and the mpirun shim."""
+    cases = [c for c in suite.default_cases((2,)) if c.name in ("V1 Serial", "V2 2.2-scatter-halo")]
+    csv_path, rows = suite.run_suite("pytest", cases, timeout=300, logs_root=str(tmp_path))
+    assert [r["OverallStatusSymbol"] for r in rows] == ["✔", "✔"], rows
+    assert rows[0]["OutputShape"] == "13x13x256"          # extra Final Output Shape line fixes V1
+    assert rows[1]["OutputFirst5Values"].startswith("44.4152 42.4612 40.6967")
+    assert os.path.exists(csv_path)
+
+
+def test_mpirun_fail_stop(tmp_path):
+    """One rank exiting non-zero takes the job down with its exit code (MPI_Abort semantics)."""
+    prog = tmp_path / "p.py"
+    prog.write_text("import os,sys,time\nr=int(os.environ['OMPI_COMM_WORLD_RANK'])\n"
+                    "sys.exit(3) if r==1 else time.sleep(30)\n")
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "bin", "mpirun"), "--oversubscribe", "-np", "3",
+                        sys.executable, str(prog)], capture_output=True, text=True, timeout=25)
+    assert p.returncode == 3
