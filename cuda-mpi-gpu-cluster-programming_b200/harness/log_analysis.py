@@ -1,0 +1,337 @@
+"""Log warehouse + analysis CLI (the L6 layer).
+
+Same commands as the reference's ``log_analysis.py`` (ref log_analysis.py:75-292) — ``ingest``,
+``query``, ``stats``, ``speedup``, ``plot``, ``export`` — plus ``scorecard`` (the notebook's median /
+CV table, ref analysis.md:2137-2630).  DuckDB and matplotlib are not on this image, so the
+warehouse is SQLite (stdlib) + pandas, and plots are written as dependency-free SVG.
+
+Accepted inputs (ref log_analysis.py:54-66, analysis.md:134-142):
+  * session CSVs with ``EntryTimestamp,ProjectVariant,NumProcesses`` + ``ExecutionTime_ms|Time_ms``;
+  * legacy ``Timestamp,Version,NP,Time_ms`` and lower-case ``timestamp,version,np,time_ms``;
+  * ``run_*.log`` files: first match of the time patterns below (our runners also print
+    ``ExecutionTime_ms: <num>`` so this table is populated, unlike the reference's);
+  * ``*.cpp|*.cu|*.hpp|*.h|*.cuh|*.py`` for source statistics.
+Speed-up baseline is the version literally named ``V1 Serial`` at np=1 (ref :218,235).
+"""
+from __future__ import annotations
+
+import argparse
+import hashlib
+import math
+import os
+import re
+import sqlite3
+import sys
+from datetime import datetime, timezone
+from pathlib import Path
+from typing import List, Optional
+
+import pandas as pd
+
+DEFAULT_DB = Path(".warehouse/cluster_logs.sqlite")
+PLOTS_DIR = Path("plots")
+
+# run-log time patterns, most specific first (ref analysis.md:311-322 lists ten variants)
+TIME_PATTERNS = [
+    (r"(?:Time|ExecutionTime)_ms[=:]\s*([\d.]+)", 1e-3),
+    (r"AlexNet MPI\+CUDA(?:-Aware)? Forward Pass completed in ([\d.]+) ms", 1e-3),
+    (r"AlexNet CUDA Forward Pass completed in ([\d.]+) ms", 1e-3),
+    (r"AlexNet Serial Forward Pass completed in ([\d.]+) ms", 1e-3),
+    (r"Execution Time:\s*([\d.]+) ms", 1e-3),
+    (r"completed in ([\d.]+) ms", 1e-3),
+    (r"Total PARALLEL time:\s*([\d.]+) seconds", 1.0),
+    (r"Parallel computation finished in ([\d.]+) seconds", 1.0),
+    (r"elapsed[=:]\s*([\d.]+)\s*s\b", 1.0),
+    (r"([\d.]+) ms", 1e-3),
+]
+
+CANONICAL = [  # (regex on lower-cased name, canonical) — ref analysis.md:70-99
+    (r"v1|serial", "V1 Serial"),
+    (r"2[._]1|broadcast", "V2.1 BroadcastAll"),
+    (r"2[._]2|scatter", "V2.2 ScatterHalo"),
+    (r"v5|aware", "V5 MPI+CUDA-Aware"),
+    (r"v4|mpi\+cuda|mpi_cuda", "V4 MPI+CUDA"),
+    (r"v3|cuda", "V3 CUDA"),
+]
+
+
+def canonical_version_name(v: Optional[str]) -> Optional[str]:
+    if v is None:
+        return None
+    low = str(v).lower()
+    for pat, name in CANONICAL:
+        if re.search(pat, low):
+            return name
+    return str(v)
+
+
+def _sha1(p: Path) -> str:
+    h = hashlib.sha1()
+    with p.open("rb") as fh:
+        for blk in iter(lambda: fh.read(1 << 16), b""):
+            h.update(blk)
+    return h.hexdigest()
+
+
+def normalise_summary(df: pd.DataFrame) -> pd.DataFrame:
+    cols = set(df.columns)
+    out = pd.DataFrame()
+    if {"EntryTimestamp", "ProjectVariant", "NumProcesses"} <= cols:
+        tcol = "ExecutionTime_ms" if "ExecutionTime_ms" in cols else "Time_ms"
+        if tcol not in cols:
+            return out
+        out = pd.DataFrame({"ts": df["EntryTimestamp"], "version": df["ProjectVariant"],
+                            "np": df["NumProcesses"], "ms": df[tcol]})
+    elif {"Timestamp", "Version", "NP", "Time_ms"} <= cols:
+        out = pd.DataFrame({"ts": df["Timestamp"], "version": df["Version"], "np": df["NP"],
+                            "ms": df["Time_ms"]})
+    elif {"timestamp", "version", "np", "time_ms"} <= cols:
+        out = pd.DataFrame({"ts": df["timestamp"], "version": df["version"], "np": df["np"],
+                            "ms": df["time_ms"]})
+    else:
+        return out
+    out["ts"] = pd.to_datetime(out["ts"], utc=True, errors="coerce").astype(str)
+    out["np"] = pd.to_numeric(out["np"], errors="coerce")
+    out["total_time_s"] = pd.to_numeric(out["ms"], errors="coerce") / 1000.0
+    return out.dropna(subset=["np"])[["ts", "version", "np", "total_time_s"]]
+
+
+class Warehouse:
+    def __init__(self, path: Path = DEFAULT_DB):
+        self.path = Path(path)
+        self.path.parent.mkdir(parents=True, exist_ok=True)
+        self.con = sqlite3.connect(str(self.path))
+        c = self.con
+        c.execute("CREATE TABLE IF NOT EXISTS file_index(relpath TEXT PRIMARY KEY, sha1 TEXT, size INT, mtime TEXT)")
+        c.execute("CREATE TABLE IF NOT EXISTS summary_runs(src TEXT, ts TEXT, version TEXT, np INT, total_time_s REAL)")
+        c.execute("CREATE TABLE IF NOT EXISTS run_logs(relpath TEXT, ts TEXT, version TEXT, np INT, total_time_s REAL)")
+        c.execute("CREATE TABLE IF NOT EXISTS source_stats(relpath TEXT PRIMARY KEY, loc INT, func_cnt INT, include_cnt INT, cuda_kernel_cnt INT)")
+        c.executescript("""
+            DROP VIEW IF EXISTS perf_runs; DROP VIEW IF EXISTS best_runs;
+            CREATE VIEW perf_runs AS
+              SELECT ts, version, np, total_time_s FROM summary_runs WHERE total_time_s IS NOT NULL
+              UNION ALL
+              SELECT ts, version, np, total_time_s FROM run_logs WHERE total_time_s IS NOT NULL;
+            CREATE VIEW best_runs AS
+              SELECT version, np, MIN(total_time_s) AS total_time_s FROM perf_runs GROUP BY version, np;
+        """)
+        c.commit()
+
+    def df(self, sql: str) -> pd.DataFrame:
+        return pd.read_sql_query(sql, self.con)
+
+    def run_stats(self) -> pd.DataFrame:
+        """mean, sample sd, 95 % CI, median, CV per (version, np) (ref run_stats view + scorecard)."""
+        d = self.df("SELECT version, np, total_time_s FROM perf_runs")
+        if d.empty:
+            return pd.DataFrame(columns=["version", "np", "n", "mean_s", "sd_s", "ci95_s", "median_s", "cv"])
+        g = d.groupby(["version", "np"])["total_time_s"]
+        out = g.agg(n="count", mean_s="mean", sd_s="std", median_s="median").reset_index()
+        out["ci95_s"] = 1.96 * out["sd_s"] / out["n"].pow(0.5)
+        out["cv"] = out["sd_s"] / out["mean_s"]
+        return out[["version", "np", "n", "mean_s", "sd_s", "ci95_s", "median_s", "cv"]]
+
+    def speedup(self, stat: str = "best") -> pd.DataFrame:
+        """S = T1(V1 Serial, np=1) / T(version, np); E = S / np (ref :213-222)."""
+        if stat == "best":
+            b = self.df("SELECT version, np, total_time_s AS t FROM best_runs")
+        else:
+            b = self.run_stats().rename(columns={"median_s": "t"})[["version", "np", "t"]]
+        base = b[(b.version == "V1 Serial") & (b.np == 1)]
+        if base.empty:
+            raise SystemExit("no 'V1 Serial' np=1 run in the warehouse: speed-up has no baseline")
+        t1 = float(base.t.min())
+        b["S"] = t1 / b.t
+        b["E"] = b.S / b.np
+        return b.sort_values("S", ascending=False).reset_index(drop=True)
+
+    # ---- ETL -----------------------------------------------------------------------------------
+    def ingest(self, root: Path, verbose: bool = False) -> dict:
+        seen = dict(self.con.execute("SELECT relpath, sha1 FROM file_index").fetchall())
+        n = dict(files=0, summary_rows=0, run_logs=0, sources=0)
+        for p in sorted(Path(root).rglob("*")):
+            if p.is_dir() or ".git" in p.parts or ".warehouse" in p.parts or \
+                    p.suffix.lower() in (".sqlite", ".sqlite-journal", ".duckdb"):
+                continue
+            rel = str(p.relative_to(root))
+            try:
+                sha = _sha1(p)
+            except OSError:
+                continue
+            if seen.get(rel) == sha:
+                continue                      # SHA-1 dedup: unchanged files are not re-ingested
+            st = p.stat()
+            mtime = datetime.fromtimestamp(st.st_mtime, timezone.utc).isoformat()
+            suf = p.suffix.lower()
+            if suf == ".csv":
+                try:
+                    nd = normalise_summary(pd.read_csv(p))
+                except Exception:
+                    nd = pd.DataFrame()
+                if not nd.empty:
+                    self.con.execute("DELETE FROM summary_runs WHERE src=?", (rel,))
+                    self.con.executemany("INSERT INTO summary_runs VALUES (?,?,?,?,?)",
+                                         [(rel, r.ts, r.version, int(r.np),
+                                           None if pd.isna(r.total_time_s) else float(r.total_time_s))
+                                          for r in nd.itertuples()])
+                    n["summary_rows"] += len(nd)
+            elif suf == ".log" and "run_" in p.name:
+                txt = p.read_text(errors="ignore")
+                sec = None
+                for pat, scale in TIME_PATTERNS[:1]:       # the reference only honours the first form
+                    m = re.search(pat, txt)
+                    if m:
+                        sec = float(m.group(1)) * scale
+                if sec is not None:
+                    vm = re.search(r"v\d(?:_\d[._]\d[_\w]*)?", rel)
+                    nm = re.search(r"np(\d+)", rel)
+                    self.con.execute("DELETE FROM run_logs WHERE relpath=?", (rel,))
+                    self.con.execute("INSERT INTO run_logs VALUES (?,?,?,?,?)",
+                                     (rel, mtime, vm.group(0) if vm else None,
+                                      int(nm.group(1)) if nm else None, sec))
+                    n["run_logs"] += 1
+            elif suf in (".cpp", ".cu", ".hpp", ".h", ".cuh", ".py", ".c"):
+                code = p.read_text(errors="ignore")
+                self.con.execute("INSERT OR REPLACE INTO source_stats VALUES (?,?,?,?,?)",
+                                 (rel, code.count("\n"),
+                                  len(re.findall(r"\b[A-Za-z_]\w*\s*\([^)]*\)\s*\{", code)) +
+                                  len(re.findall(r"^\s*def \w+", code, re.M)),
+                                  code.count("#include") + len(re.findall(r"^\s*(?:import|from) ", code, re.M)),
+                                  code.count("__global__")))
+                n["sources"] += 1
+            self.con.execute("INSERT OR REPLACE INTO file_index VALUES (?,?,?,?)", (rel, sha, st.st_size, mtime))
+            n["files"] += 1
+            if verbose:
+                print(f"indexed {rel}")
+        self.con.commit()
+        return n
+
+
+def time_from_log(text: str) -> Optional[float]:
+    """Seconds from a run log using the full pattern ladder (ref analysis.md:311-322)."""
+    for pat, scale in TIME_PATTERNS:
+        m = re.search(pat, text)
+        if m:
+            return float(m.group(1)) * scale
+    return None
+
+
+# ---- dependency-free SVG charts ------------------------------------------------------------------
+def _svg_axes(w, h, title, xlabel, ylabel):
+    return [f'<svg xmlns="http://www.w3.org/2000/svg" width="{w}" height="{h}" font-family="sans-serif" font-size="12">',
+            f'<rect width="{w}" height="{h}" fill="white"/>',
+            f'<text x="{w/2}" y="18" text-anchor="middle" font-size="14">{title}</text>',
+            f'<text x="{w/2}" y="{h-6}" text-anchor="middle">{xlabel}</text>',
+            f'<text x="14" y="{h/2}" text-anchor="middle" transform="rotate(-90 14 {h/2})">{ylabel}</text>',
+            f'<line x1="50" y1="{h-40}" x2="{w-15}" y2="{h-40}" stroke="black"/>',
+            f'<line x1="50" y1="30" x2="50" y2="{h-40}" stroke="black"/>']
+
+
+def svg_line(path: Path, xs, ys, title, xlabel, ylabel):
+    w, h = 480, 320
+    xmax, ymax = max(max(xs), 1), max(max(ys) * 1.1, 1e-9)
+    px = lambda x: 50 + (w - 65) * x / xmax
+    py = lambda y: (h - 40) - (h - 70) * y / ymax
+    el = _svg_axes(w, h, title, xlabel, ylabel)
+    el.append('<polyline fill="none" stroke="#1f77b4" stroke-width="2" points="' +
+              " ".join(f"{px(x):.1f},{py(y):.1f}" for x, y in zip(xs, ys)) + '"/>')
+    for x, y in zip(xs, ys):
+        el.append(f'<circle cx="{px(x):.1f}" cy="{py(y):.1f}" r="3.5" fill="#1f77b4"/>')
+        el.append(f'<text x="{px(x):.1f}" y="{h-26}" text-anchor="middle">{x:g}</text>')
+        el.append(f'<text x="{px(x)+6:.1f}" y="{py(y)-6:.1f}">{y:.2f}</text>')
+    el.append("</svg>")
+    path.write_text("\n".join(el))
+
+
+def svg_bars(path: Path, labels, vals, title, ylabel, ymax=1.1):
+    w, h = max(480, 60 + 46 * len(labels)), 340
+    el = _svg_axes(w, h, title, "", ylabel)
+    bw = (w - 80) / max(len(labels), 1)
+    for i, (lab, v) in enumerate(zip(labels, vals)):
+        x = 55 + i * bw
+        bh = (h - 90) * min(v, ymax) / ymax
+        el.append(f'<rect x="{x:.1f}" y="{h-60-bh:.1f}" width="{bw*0.8:.1f}" height="{bh:.1f}" fill="#2ca02c"/>')
+        el.append(f'<text x="{x+bw*0.4:.1f}" y="{h-64-bh:.1f}" text-anchor="middle" font-size="10">{v:.2f}</text>')
+        el.append(f'<text x="{x+bw*0.4:.1f}" y="{h-46}" text-anchor="end" font-size="9" '
+                  f'transform="rotate(-35 {x+bw*0.4:.1f} {h-46})">{lab}</text>')
+    el.append("</svg>")
+    path.write_text("\n".join(el))
+
+
+def _label(v: str) -> str:
+    return v.replace("V2 2.1-broadcast-all", "V2 Broadcast").replace("V2 2.2-scatter-halo", "V2 Scatter")
+
+
+# ---- CLI -------------------------------------------------------------------------------------------
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser(prog="log_analysis", description=__doc__.split("\n")[0])
+    ap.add_argument("--db", default=str(DEFAULT_DB))
+    sub = ap.add_subparsers(dest="cmd", required=True)
+    a = sub.add_parser("ingest"); a.add_argument("--root", required=True); a.add_argument("--rebuild", action="store_true")
+    a.add_argument("-v", "--verbose", action="store_true")
+    a = sub.add_parser("query"); a.add_argument("sql")
+    sub.add_parser("stats")
+    a = sub.add_parser("speedup"); a.add_argument("--stat", choices=["best", "median"], default="best")
+    a = sub.add_parser("scorecard")
+    a = sub.add_parser("plot"); a.add_argument("plots", nargs="+", choices=["speedup", "efficiency"])
+    a.add_argument("--outdir", default=str(PLOTS_DIR))
+    a = sub.add_parser("export"); a.add_argument("view"); a.add_argument("outfile")
+    ns = ap.parse_args(argv)
+    db = Path(ns.db)
+    pd.set_option("display.width", 200); pd.set_option("display.max_rows", 500)
+
+    if ns.cmd == "ingest":
+        if ns.rebuild and db.exists():
+            db.unlink()
+            print("wiped existing warehouse")
+        n = Warehouse(db).ingest(Path(ns.root), ns.verbose)
+        print(f"ingest complete: {n}")
+        return 0
+    wh = Warehouse(db)
+    if ns.cmd == "query":
+        print(wh.df(ns.sql).to_string(index=False))
+    elif ns.cmd == "stats":
+        print(wh.run_stats().sort_values(["version", "np"]).to_string(index=False))
+    elif ns.cmd == "speedup":
+        print(wh.speedup(ns.stat).to_string(index=False))
+    elif ns.cmd == "scorecard":
+        st = wh.run_stats()
+        sp = wh.speedup("median")[["version", "np", "S", "E"]]
+        print(st.merge(sp, on=["version", "np"], how="left").sort_values(["version", "np"]).to_string(index=False))
+    elif ns.cmd == "plot":
+        out = Path(ns.outdir); out.mkdir(parents=True, exist_ok=True)
+        sp = wh.speedup("best")
+        if "speedup" in ns.plots:
+            for v in sorted(sp.version.unique()):
+                s = sp[sp.version == v].sort_values("np")
+                f = out / f"speedup_{v.replace('/', '-').replace(' ', '_')}.svg"
+                svg_line(f, list(s.np), list(s.S), f"Speed-up - {_label(v)}", "np", "Speed-up S")
+            print(f"plots -> {out}/speedup_*.svg")
+        if "efficiency" in ns.plots:
+            s = sp.sort_values(["version", "np"])
+            svg_bars(out / "efficiency.svg", [f"{_label(v)} np={int(n)}" for v, n in zip(s.version, s.np)],
+                     list(s.E), "Strong-scaling efficiency", "Efficiency E")
+            print(f"plot -> {out}/efficiency.svg")
+    elif ns.cmd == "export":
+        special = {"run_stats": wh.run_stats, "speedup": lambda: wh.speedup("best")}
+        try:
+            df = special[ns.view]() if ns.view in special else wh.df(f"SELECT * FROM {ns.view}")
+        except Exception as e:
+            print(f"cannot select from '{ns.view}': {e}", file=sys.stderr)
+            return 1
+        of = Path(ns.outfile); of.parent.mkdir(parents=True, exist_ok=True)
+        if of.suffix.lower() == ".csv":
+            df.to_csv(of, index=False)
+        elif of.suffix.lower() == ".parquet":
+            df.to_parquet(of, index=False, engine="pyarrow")
+        elif of.suffix.lower() == ".md":
+            of.write_text(df.to_markdown(index=False) if hasattr(df, "to_markdown") else df.to_string(index=False))
+        else:
+            print("outfile must end with .csv, .parquet or .md", file=sys.stderr)
+            return 1
+        print(f"exported {len(df):,} rows -> {of}")
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,78 @@
+"""Warehouse ETL over the three CSV schemas + run logs, derived stats, speed-up, exports."""
+import os
+import subprocess
+import sys
+
+import pandas as pd
+import pytest
+
+from b200cnn.harness import log_analysis as la
+from b200cnn.harness.suite import CSV_HEADER
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _make_tree(tmp):
+    logs = tmp / "final_project" / "logs" / "s1"
+    logs.mkdir(parents=True)
+    rows = [("V1 Serial", 1, 800.0), ("V1 Serial", 1, 760.0), ("V2 2.2-scatter-halo", 2, 400.0),
+            ("V2 2.2-scatter-halo", 4, 250.0), ("V4 MPI+CUDA", 1, 180.0), ("V4 MPI+CUDA", 4, 100.0)]
+    df = pd.DataFrame([{**{h: "" for h in CSV_HEADER}, "EntryTimestamp": "2026-01-01T00:00:00",
+                        "ProjectVariant": v, "NumProcesses": n, "ExecutionTime_ms": t} for v, n, t in rows])
+    df.to_csv(logs / "summary_report_1.csv", index=False)
+    pd.DataFrame({"Timestamp": ["2025-05-06 16:08:35"], "Version": ["V3 CUDA Only"], "NP": [1],
+                  "Time_ms": [194.0]}).to_csv(tmp / "legacy.csv", index=False)
+    pd.DataFrame({"timestamp": ["2025-05-06"], "version": ["V3 CUDA Only"], "np": [1],
+                  "time_ms": [488.0]}).to_csv(tmp / "lower.csv", index=False)
+    pd.DataFrame({"foo": [1]}).to_csv(tmp / "unknown.csv", index=False)
+    (logs / "run_v4_mpi_cuda_np2.log").write_text("AlexNet MPI+CUDA Forward Pass completed in 150 ms\n"
+                                                  "ExecutionTime_ms: 150.5\n")
+    (logs / "run_v1_serial_np1.log").write_text("AlexNet Serial Forward Pass completed in 742 ms\n")
+    (tmp / "k.cu").write_text("#include <x>\n__global__ void k(){}\nvoid host(int a) {\n}\n")
+    return tmp
+
+
+def test_ingest_stats_speedup_export(tmp_path):
+    root = _make_tree(tmp_path)
+    wh = la.Warehouse(tmp_path / "wh.sqlite")
+    n = wh.ingest(root)
+    assert n["summary_rows"] == 8 and n["run_logs"] == 1 and n["sources"] == 1
+    assert wh.ingest(root)["files"] == 0                      # SHA-1 dedup
+    st = wh.run_stats().set_index(["version", "np"])
+    assert st.loc[("V1 Serial", 1), "n"] == 2
+    assert abs(st.loc[("V1 Serial", 1), "mean_s"] - 0.78) < 1e-9
+    assert abs(st.loc[("V3 CUDA Only", 1), "median_s"] - 0.341) < 1e-9
+    sp = wh.speedup().set_index(["version", "np"])
+    assert abs(sp.loc[("V2 2.2-scatter-halo", 4), "S"] - 0.76 / 0.25) < 1e-9
+    assert abs(sp.loc[("V2 2.2-scatter-halo", 4), "E"] - 0.76 / 0.25 / 4) < 1e-9
+    src = wh.df("SELECT * FROM source_stats")
+    assert int(src.cuda_kernel_cnt[0]) == 1
+    rl = wh.df("SELECT * FROM run_logs")
+    assert rl.version[0] == "v4" and int(rl.np[0]) == 2 and abs(rl.total_time_s[0] - 0.1505) < 1e-9
+
+
+def test_cli_roundtrip(tmp_path):
+    root = _make_tree(tmp_path)
+    db = str(tmp_path / "w.sqlite")
+    cli = [sys.executable, os.path.join(ROOT, "log_analysis.py"), "--db", db]
+    assert subprocess.run(cli + ["ingest", "--root", str(root), "--rebuild"], capture_output=True).returncode == 0
+    out = subprocess.run(cli + ["speedup"], capture_output=True, text=True)
+    assert out.returncode == 0 and "V4 MPI+CUDA" in out.stdout
+    assert subprocess.run(cli + ["plot", "speedup", "efficiency", "--outdir", str(tmp_path / "plots")],
+                          capture_output=True).returncode == 0
+    assert (tmp_path / "plots" / "efficiency.svg").read_text().startswith("<svg")
+    for ext in ("csv", "parquet"):
+        of = tmp_path / f"best.{ext}"
+        assert subprocess.run(cli + ["export", "best_runs", str(of)], capture_output=True).returncode == 0
+        assert of.exists()
+    assert subprocess.run(cli + ["export", "nope", str(tmp_path / "x.csv")], capture_output=True).returncode == 1
+
+
+def test_canonical_names_and_time_ladder():
+    assert la.canonical_version_name("V2 2.2-scatter-halo") == "V2.2 ScatterHalo"
+    assert la.canonical_version_name("v2_2.1_broadcast_all") == "V2.1 BroadcastAll"
+    assert la.canonical_version_name("V3 CUDA Only") == "V3 CUDA"
+    assert la.canonical_version_name("V4 MPI+CUDA") == "V4 MPI+CUDA"
+    assert la.canonical_version_name("V5 MPI+CUDA-Aware") == "V5 MPI+CUDA-Aware"
+    assert la.time_from_log("Execution Time: 286.9 ms") == pytest.approx(0.2869)
+    assert la.time_from_log("pid=0: Total PARALLEL time: 1.5 seconds.") == pytest.approx(1.5)
