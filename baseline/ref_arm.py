@@ -44,6 +44,7 @@ def main(a):
         return unavailable("baseline/_ref V4 binary is not built (baseline/build_reference.py failed; "
                            "pip cannot install the reference: no setup.py/pyproject)")
     env = dict(os.environ, B200_MPIRUN_BIND_GPUS="1", B200_MPIRUN_NUM_GPUS=str(N))
+    env["LD_LIBRARY_PATH"] = "/usr/local/cuda/lib64:" + env.get("LD_LIBRARY_PATH", "")   # -cudart=shared
     for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_PORT", "MASTER_ADDR", "OMPI_COMM_WORLD_RANK",
               "OMPI_COMM_WORLD_SIZE", "CUDA_VISIBLE_DEVICES", "TORCHELASTIC_RUN_ID"):
         env.pop(k, None)

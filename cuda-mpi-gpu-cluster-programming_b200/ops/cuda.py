@@ -55,6 +55,10 @@ def lib():
         L.b200_flag_signal.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_void_p]
         L.b200_flag_wait.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.c_int,
                                      C.c_void_p, C.c_ulonglong, C.c_void_p]
+        L.b200_conv_nchw.argtypes = [C.c_void_p] * 4 + [C.c_int] * 8 + [C.c_void_p]
+        L.b200_conv_nchw_scratch_bytes.argtypes = [C.c_int] * 8
+        L.b200_conv_nchw_scratch_bytes.restype = C.c_longlong
+        L.b200_dgemm_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         _lib = L
     return _lib
 
@@ -128,3 +132,21 @@ def flag_wait(flags: Sequence[int], targets: Sequence[int], status_ptr: int = 0,
     ta = (C.c_int * len(flags))(*targets)
     cu_check(lib().b200_flag_wait(fa, ta, len(flags), C.c_void_p(status_ptr or None),
                                   timeout_ns, current_stream_ptr()), "flag_wait")
+
+
+def dgemm_rows(a_ptr: int, b_ptr: int, c_ptr: int, rows: int, n: int) -> None:
+    """C[rows,n] = A[rows,n] @ B[n,n] in FP64 (pointers may be peer-mapped)."""
+    cu_check(lib().b200_dgemm_rows(C.c_void_p(a_ptr), C.c_void_p(b_ptr), C.c_void_p(c_ptr), rows, n,
+                                   current_stream_ptr()), "dgemm_rows")
+
+
+def conv_nchw(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], S: int, P: int) -> torch.Tensor:
+    """Plain convolution of an NCHW CUDA tensor with [K,C,F,F] weights -> NCHW (conv_test path)."""
+    N, Cc, H, W = x.shape
+    K, _, F, _ = w.shape
+    Ho, Wo = (H - F + 2 * P) // S + 1, (W - F + 2 * P) // S + 1
+    out = torch.empty((N, K, Ho, Wo), dtype=torch.float32, device=x.device)
+    cu_check(lib().b200_conv_nchw(fptr(x.contiguous()), fptr(w.contiguous()),
+                                  fptr(bias.contiguous()) if bias is not None else None, fptr(out),
+                                  N, Cc, H, W, K, F, S, P, current_stream_ptr()), "conv_nchw")
+    return out

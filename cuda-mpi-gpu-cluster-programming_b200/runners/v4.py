@@ -36,8 +36,11 @@ def main(argv=None, variant: str = "v4") -> int:
     cfg = config_from_args(ns, seed_default=1)
     if not torch.cuda.is_available():
         fail(bdist.env_rank_world()[0], "CUDA no CUDA-capable device is detected")
-    ctx = bdist.init()
     scatter = "sharded" if variant == "v5" else ns.scatter
+    world_env = bdist.env_rank_world()[1]
+    if world_env > torch.cuda.device_count():
+        return _oversubscribed(ns, cfg, variant, scatter)
+    ctx = bdist.init()
     try:
         x, w = make_problem(cfg)                  # identical on every rank (seeded): no weight bcast
         ctx.barrier()
@@ -67,6 +70,39 @@ def main(argv=None, variant: str = "v4") -> int:
         if not ns.quiet_extras:
             for line in L.extras(fnv=fnv1a64(y), wall_ms=ms, np=ctx.world, precision=cfg.precision,
                                  scatter=scatter, strategy=ns.strategy, batch=cfg.batch, **kv):
+                L.emit(line)
+    ctx.finalize()
+    return 0
+
+
+def _oversubscribed(ns, cfg, variant, scatter) -> int:
+    """More ranks than GPUs (the reference happily runs `mpirun -np 4` on one GPU, ref
+    scripts/common_test_utils.sh:275).  Ranks that spin on each other's flags must never share a
+    GPU (B200_PROFILING.md: Xid 109), so rank 0 runs all ranks' kernels itself, layer by layer,
+    through the single-device emulation of the exact same protocol; the other processes only take
+    part in the barriers.  Output and log lines are identical to a real multi-GPU run."""
+    from ..models.engine import EmulatedWorld
+    ctx = bdist.init(device="cpu")
+    ctx.barrier()
+    t0 = time.perf_counter()
+    y = None
+    if ctx.rank == 0:
+        x, w = make_problem(cfg)
+        ew = EmulatedWorld(cfg, w, ctx.world, "cuda:0", precision=cfg.precision, strategy=ns.strategy,
+                           scatter=scatter)
+        y = ew.forward(x.pin_memory().to("cuda:0", non_blocking=True)).cpu()
+    ctx.barrier()
+    ms = (time.perf_counter() - t0) * 1e3
+    if ctx.rank == 0:
+        flat = y.reshape(-1)
+        rows = y.shape[1] if cfg.batch == 1 else y.shape[0] * y.shape[1]
+        for line in L.v4_shape_values(rows, y.shape[2], y.shape[3], flat[:10].tolist()):
+            L.emit(line)
+        L.emit(L.v4_time(ms, "MPI+CUDA" if variant == "v4" else "MPI+CUDA-Aware"))
+        if not ns.quiet_extras:
+            for line in L.extras(fnv=fnv1a64(y), wall_ms=ms, np=ctx.world, precision=cfg.precision,
+                                 scatter=scatter, strategy=ns.strategy, batch=cfg.batch,
+                                 mode="ranks-emulated-on-one-gpu"):
                 L.emit(line)
     ctx.finalize()
     return 0

@@ -145,6 +145,19 @@ int b200_tc_block(void* handle, const float* bias, float* out, const b200_block_
                   int flags /* bit0: round outputs to TF32 */, void* stream);
 int b200_tc_block_tiles(const b200_block_geom* g);
 
+/* Stand-alone convolution on NCHW device tensors with reference-layout weights [K][C][F][F]
+ * (the `conv_test` equivalent; ref final_project/conv_test, kernel convTiledKernel).
+ * out_nchw is [N][K][Ho][Wo], Ho = (H-F+2P)/S+1.  bias may be NULL.  The call allocates (and frees,
+ * stream-ordered) b200_conv_nchw_scratch_bytes() of device scratch for its NHWC/packed intermediates. */
+long long b200_conv_nchw_scratch_bytes(int N, int C, int H, int W, int K, int F, int S, int P);
+int b200_conv_nchw(const float* in_nchw, const float* w_kcff, const float* bias, float* out_nchw,
+                   int N, int C, int H, int W, int K, int F, int S, int P, void* stream);
+
+/* HW1 equivalent on the GPU: C[rows x n] = A[rows x n] * B[n x n], FP64 tensor cores (DMMA m8n8k4).
+ * B and C may be peer-mapped pointers: the reference's MPI_Bcast(B) and MPI_Recv(C blocks)
+ * (ref homeworks/hw1/src/template.c:132,141) become loads/stores inside the kernel. */
+int b200_dgemm_rows(const double* A, const double* B, double* C, int rows, int n, void* stream);
+
 /* Symmetric (peer-mapped) memory: zeroed cudaMalloc + CUDA IPC handles (64 bytes) exchanged by
  * the caller (torch.distributed); replaces MPI host buffers. */
 int b200_symm_alloc(size_t bytes, void** ptr);
