@@ -10,6 +10,8 @@
 // b200_conv_nchw allocates the scratch on the stream for the duration of the call.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace {
 
 __global__ void nchw_to_nhwc(const float* __restrict__ in, float* __restrict__ out, int N, int C, int H, int W) {
@@ -119,4 +121,80 @@ extern "C" int b200_conv_nchw(const float* in_nchw, const float* w_kcff, const f
     int rc = run_with_scratch(d, in_nchw, w_kcff, bias, out_nchw, scratch, st);
     B200_CUDA_TRY(cudaFreeAsync(scratch, st));
     return rc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant.
+//
+// Who needs it: hosts that may not allocate device memory when they call us — an inference server
+// whose own pool has already reserved the whole GPU (a cudaMalloc here would fail or fragment it),
+// or a latency-bound loop that cannot afford the device-wide synchronisation cudaMalloc/cudaFree
+// imply.  b200_conv_nchw (above) needs scratch for its NHWC/packed intermediates and gets it from
+// cudaMallocAsync; this entry point runs the very same kernels but takes the scratch from a fixed
+// array that is part of the library image.
+//
+// Cost and limits.  The array is B200_CONV_NCHW_STATIC_SCRATCH_BYTES (8 MiB) and every GPU that
+// loads this library carries it until the process exits, used or not.  A problem whose scratch
+// (b200_conv_nchw_scratch_bytes) exceeds it is refused with B200_ERR_RANGE and a message — there is
+// no fallback to allocation.  8 MiB covers both AlexNet convolutions of this project for one image
+// (conv1: 0.62 + 0.14 + 1.16 MB, conv2: 0.28 + 2.46 + 0.75 MB).
+//
+// Sharing.  There is one array per GPU and every call on that GPU uses it.  It still holds the
+// previous call's data when the next call starts; that is harmless here because each call writes
+// every scratch element before reading it (nothing relies on zeros), but two calls that overlap on
+// the same GPU — different streams, or different host threads — would overwrite each other's
+// intermediates: callers must order them (same stream, or an event between them).
+//
+// Set-up.  Host code cannot use the array's name as a pointer (on the host that name is only a
+// handle for the runtime).  The device address is looked up with cudaGetSymbolAddress the first
+// time the entry point is called on a given device, with that device current, and cached per
+// device.  That first call therefore does a little extra runtime work; make it before any stream
+// capture you intend to do around later calls.
+#define B200_CONV_NCHW_STATIC_SCRATCH_BYTES (8u << 20)
+
+static __device__ __align__(256) unsigned char g_conv_nchw_static_scratch[B200_CONV_NCHW_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_static_scratch_addr[kMaxDevices] = {};      // per device, resolved on first use
+std::mutex g_static_scratch_mu;
+
+int static_scratch_for_current_device(float** out) {
+    int dev = -1;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) {
+        b200::set_error("b200_conv_nchw_noalloc: device ordinal %d outside [0,%d)", dev, kMaxDevices);
+        return B200_ERR_ARG;
+    }
+    std::lock_guard<std::mutex> lk(g_static_scratch_mu);
+    if (!g_static_scratch_addr[dev]) {
+        void* p = nullptr;
+        B200_CUDA_TRY(cudaGetSymbolAddress(&p, g_conv_nchw_static_scratch));   // device `dev` is current
+        g_static_scratch_addr[dev] = static_cast<float*>(p);
+    }
+    *out = g_static_scratch_addr[dev];
+    return B200_OK;
+}
+}  // namespace
+
+extern "C" long long b200_conv_nchw_noalloc_max_scratch_bytes(void) {
+    return (long long)B200_CONV_NCHW_STATIC_SCRATCH_BYTES;
+}
+
+extern "C" int b200_conv_nchw_noalloc(const float* in_nchw, const float* w_kcff, const float* bias,
+                                      float* out_nchw, int N, int C, int H, int W, int K, int F, int S,
+                                      int P, void* stream) {
+    ConvDims d;
+    if (!in_nchw || !w_kcff || !out_nchw || !make_dims(&d, N, C, H, W, K, F, S, P)) return B200_ERR_ARG;
+    const size_t need = (d.in_elems + d.w_elems + d.out_elems) * sizeof(float);
+    if (need > B200_CONV_NCHW_STATIC_SCRATCH_BYTES) {
+        b200::set_error("b200_conv_nchw_noalloc: this problem needs %zu bytes of scratch but the built-in "
+                        "scratch array holds %u bytes; use b200_conv_nchw (which allocates) or a smaller batch",
+                        need, (unsigned)B200_CONV_NCHW_STATIC_SCRATCH_BYTES);
+        return B200_ERR_RANGE;
+    }
+    float* scratch = nullptr;
+    int rc = static_scratch_for_current_device(&scratch);
+    if (rc != B200_OK) return rc;
+    return run_with_scratch(d, in_nchw, w_kcff, bias, out_nchw, scratch, (cudaStream_t)stream);
 }

@@ -153,6 +153,19 @@ long long b200_conv_nchw_scratch_bytes(int N, int C, int H, int W, int K, int F,
 int b200_conv_nchw(const float* in_nchw, const float* w_kcff, const float* bias, float* out_nchw,
                    int N, int C, int H, int W, int K, int F, int S, int P, void* stream);
 
+/* Allocation-free variant of b200_conv_nchw.  It has no counterpart in the reference (whose CUDA
+ * code allocates and frees on every call, ref v3_cuda_only/src/alexnet_cuda.cu:54-64,91-94).
+ * For callers that must not allocate device memory when they call in: a server whose memory pool
+ * already owns the whole GPU, or a latency-bound loop that cannot take cudaMalloc's device-wide
+ * synchronisation.  Same arguments and results as b200_conv_nchw; the scratch comes from an 8 MiB
+ * array built into the library (held by every GPU that loads it).  Problems needing more scratch
+ * than b200_conv_nchw_noalloc_max_scratch_bytes() are refused with B200_ERR_RANGE.  All calls on one
+ * GPU share that array: calls that overlap on the GPU race, so order them.  The first call on each
+ * device resolves the array's address; issue it before any stream capture. */
+long long b200_conv_nchw_noalloc_max_scratch_bytes(void);
+int b200_conv_nchw_noalloc(const float* in_nchw, const float* w_kcff, const float* bias, float* out_nchw,
+                           int N, int C, int H, int W, int K, int F, int S, int P, void* stream);
+
 /* HW1 equivalent on the GPU: C[rows x n] = A[rows x n] * B[n x n], FP64 tensor cores (DMMA m8n8k4).
  * B and C may be peer-mapped pointers: the reference's MPI_Bcast(B) and MPI_Recv(C blocks)
  * (ref homeworks/hw1/src/template.c:132,141) become loads/stores inside the kernel. */
