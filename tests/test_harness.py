@@ -72,3 +72,23 @@ def test_mpirun_fail_stop(tmp_path):
     p = subprocess.run([sys.executable, os.path.join(ROOT, "bin", "mpirun"), "--oversubscribe", "-np", "3",
                         sys.executable, str(prog)], capture_output=True, text=True, timeout=25)
     assert p.returncode == 3
+
+
+def test_multi_machine_dry_run_plan():
+    from b200cnn.harness import multi_machine as mm
+    hosts = mm.parse_hosts("alice@nodeA:100a:1,bob@nodeB:86:1")
+    assert [h.alias for h in hosts] == ["alice@nodeA", "bob@nodeB"] and hosts[1].arch == "86"
+    assert mm.combined_arch_flags(hosts) == "-gencode arch=compute_100a,code=sm_100a -gencode arch=compute_86,code=sm_86"
+    o = mm.Orchestrator(hosts, dry=True, shared_fs=False, verbose_rsync=False, iface="eth0")
+    o.setup()
+    o.run(max_np=4)
+    joined = "\n".join(o.cmds)
+    assert "rsync -az --delete --checksum --exclude .git/" in joined and "bob@nodeB" in joined
+    # np=2 over two 1-slot hosts: one torchrun agent per host, worker started over ssh
+    assert "--nnodes 2 --node-rank 1" in joined and "ssh bob@nodeB" in joined
+    assert "GLOO_SOCKET_IFNAME=eth0" in joined
+
+
+def test_hw_toolchain_test_and_package(tmp_path):
+    from b200cnn.harness import hw
+    assert hw.test(1, sizes=[128], counts=[1, 2, 3], timeout=120) == 0      # np=3 skipped (128 % 3)
