@@ -40,7 +40,8 @@ def parse():
     ap.add_argument("--height", type=int, default=227)
     ap.add_argument("--width", type=int, default=227)
     ap.add_argument("--precision", choices=["tf32", "simt"], default=None)
-    ap.add_argument("--strategy", choices=["halo", "recompute"], default="halo")
+    ap.add_argument("--strategy", choices=["auto", "halo", "recompute"], default="auto",
+                    help="auto: time both decompositions for a few warm steps and keep the faster")
     ap.add_argument("--scatter", choices=["p2p", "sharded"], default="p2p",
                     help="device-timed run: where the images live (p2p = all on rank 0, pulled by conv1)")
     ap.add_argument("--e2e-scatter", choices=["p2p", "sharded"], default="sharded",
@@ -133,6 +134,36 @@ def run_ours(a):
         e.check_status()
         return ctx.max_float(ms), sess.h2d_bytes, sess.d2h_bytes
 
+    def quick_ms(strategy, scatter):
+        s_ = Session(cfg, w, dist=ctx if N > 1 else None, device=dev, precision=precision,
+                     strategy=strategy, scatter=scatter)
+        e_ = s_.engine
+        if e_.in_rows > 0:
+            lo, hi = s_.input_rows
+            e_.input_view(0).copy_(x[:, lo:hi].to(dev))
+        for _ in range(3):
+            e_.forward_enqueue(0, 0)
+        torch.cuda.synchronize(dev)
+        ctx.barrier()
+        t0_, t1_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0_.record()
+        for _ in range(5):
+            e_.forward_enqueue(0, 0)
+        t1_.record()
+        t1_.synchronize()
+        ms_ = ctx.max_float(t0_.elapsed_time(t1_) / 5)
+        e_.check_status()
+        del s_, e_
+        torch.cuda.empty_cache()
+        return ms_
+
+    tuned = None
+    if a.strategy == "auto":
+        if N > 1:
+            tuned = {st: round(quick_ms(st, a.scatter), 4) for st in ("halo", "recompute")}
+            a.strategy = min(tuned, key=tuned.get)
+        else:
+            a.strategy = "halo"
     sess = Session(cfg, w, dist=ctx if N > 1 else None, device=dev, precision=precision,
                    strategy=a.strategy, scatter=a.scatter)
     total_ms, launches, clocks = measure_device(sess)
@@ -165,7 +196,8 @@ def run_ours(a):
         "config": {"model": "AlexNet blocks 1-2 (conv1-relu-pool1-conv2-relu-pool2-lrn2)",
                    "global_batch": a.batch, "input": f"{a.height}x{a.width}x3",
                    "parallelism": f"spatial-rows{N}" if N > 1 else "single-gpu",
-                   "strategy": a.strategy, "scatter": a.scatter if N > 1 else "local",
+                   "strategy": a.strategy, "strategy_autotune_ms": tuned,
+                   "scatter": a.scatter if N > 1 else "local",
                    "l2": "flushed between timed iterations (256 MiB fill, untimed)"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "impl": "ours",
     }
