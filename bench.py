@@ -42,8 +42,10 @@ def parse():
     ap.add_argument("--precision", choices=["tf32", "simt"], default=None)
     ap.add_argument("--strategy", choices=["auto", "halo", "recompute"], default="auto",
                     help="auto: time both decompositions for a few warm steps and keep the faster")
-    ap.add_argument("--scatter", choices=["p2p", "sharded"], default="p2p",
-                    help="device-timed run: where the images live (p2p = all on rank 0, pulled by conv1)")
+    ap.add_argument("--scatter", choices=["p2p", "sharded"], default="sharded",
+                    help="device-timed run: where the images live.  sharded = every rank holds the rows it "
+                         "needs (they arrive by its own H2D in the e2e run); p2p = all images on rank 0, "
+                         "pulled over NVLink inside conv1 (reported as config.p2p_scatter_images_per_s)")
     ap.add_argument("--e2e-scatter", choices=["p2p", "sharded"], default="sharded",
                     help="end-to-end run: p2p = rank 0 feeds everything; sharded = each rank feeds its slab")
     ap.add_argument("--no-e2e", action="store_true")
@@ -164,6 +166,9 @@ def run_ours(a):
             a.strategy = min(tuned, key=tuned.get)
         else:
             a.strategy = "halo"
+    p2p_alt = None
+    if N > 1 and a.scatter == "sharded":      # the reference's data placement, for the record
+        p2p_alt = round(a.batch / (quick_ms(a.strategy, "p2p") / 1e3), 1)
     sess = Session(cfg, w, dist=ctx if N > 1 else None, device=dev, precision=precision,
                    strategy=a.strategy, scatter=a.scatter)
     total_ms, launches, clocks = measure_device(sess)
@@ -197,7 +202,7 @@ def run_ours(a):
                    "global_batch": a.batch, "input": f"{a.height}x{a.width}x3",
                    "parallelism": f"spatial-rows{N}" if N > 1 else "single-gpu",
                    "strategy": a.strategy, "strategy_autotune_ms": tuned,
-                   "scatter": a.scatter if N > 1 else "local",
+                   "scatter": a.scatter if N > 1 else "local", "p2p_scatter_images_per_s": p2p_alt,
                    "l2": "flushed between timed iterations (256 MiB fill, untimed)"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "impl": "ours",
     }

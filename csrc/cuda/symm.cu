@@ -83,7 +83,31 @@ __global__ void flag_wait_kernel(WaitArgs a, int* status, unsigned long long tim
     __threadfence_system();
 }
 
+// Barrier in one launch: bump one counter on every peer, then wait for every peer's bump on ours.
+// Only for ranks that own a GPU each (the waits would deadlock if ranks shared a device).
+__global__ void flag_barrier_kernel(SignalArgs sig, WaitArgs w, int* status, unsigned long long timeout_ns) {
+    __threadfence_system();
+    if ((int)threadIdx.x < sig.n) red_release_sys_add(sig.target[threadIdx.x], 1);
+    if ((int)threadIdx.x < w.n) wait_flag_ge(w.flag[threadIdx.x], w.target[threadIdx.x], status, timeout_ns);
+    __syncthreads();
+    __threadfence_system();
+}
+
 }  // namespace
+
+extern "C" int b200_flag_barrier(int* const* signal_targets, const int* const* wait_flags,
+                                 const int* wait_target, int n, int* status, unsigned long long timeout_ns,
+                                 void* stream) {
+    if (n < 0 || n > 16 || (n && (!signal_targets || !wait_flags || !wait_target))) return B200_ERR_ARG;
+    if (n == 0) return B200_OK;
+    SignalArgs s;
+    WaitArgs w;
+    s.n = w.n = n;
+    for (int i = 0; i < n; ++i) { s.target[i] = signal_targets[i]; w.flag[i] = wait_flags[i]; w.target[i] = wait_target[i]; }
+    flag_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(s, w, status, timeout_ns);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
 
 // targets: up to 16 counters (local or peer); each gets += add
 extern "C" int b200_flag_signal(int* const* targets, int n, int add, void* stream) {

@@ -567,12 +567,20 @@ inline int num_kblocks(int F, int C) {
 
 constexpr int kMaxPatchBytes = 64 * 1024;
 
-// Tile planner: PR x PC pooled outputs per tile, (2PR+1)(2PC+1) <= 128*nacc pixel slots; minimise
-// tiles * nacc (MMA time), then slots.  Deterministic: peers call it to predict tile counts.
+// Tile planner: PR x PC pooled outputs per tile, (2PR+1)(2PC+1) <= 128*nacc pixel slots.
+// Cost = waves x cycles-per-tile, with cycles calibrated on B200 (profiles/tc_experiments_v4.log):
+// the tensor pipe runs ~1.3x above its floor, a tile carries ~14k cycles of fixed cost (setup, pipeline
+// fill/drain) plus an epilogue that grows with accumulators x channel chunks (+LRN), and the grid is
+// 148 persistent CTAs, so 1.7 waves cost 2.  Deterministic: peers call it to predict tile counts.
+constexpr int kPlanSms = 148;
+
 bool plan_tiles(const b200_block_geom* g, TcParams* p) {
     const int rows = g->p1 - g->p0;
     const bool patch = is_patch_mode(g->C);
-    long best = -1;
+    const int nkb = num_kblocks(g->F, g->C);
+    const double mma_kb = 4.0 * (128.0 * g->K / 256.0) * 1.3;         // cycles per k-block per accumulator
+    const double prod_kb = patch ? 450.0 : 0.0;                       // smem->smem im2col bound (conv1)
+    double best = -1;
     for (int nacc = 1; nacc <= 2; ++nacc)
         for (int PR = 1; PR <= rows && PR <= 63; ++PR)
             for (int PC = 1; PC <= g->Wp; ++PC) {
@@ -586,7 +594,12 @@ bool plan_tiles(const b200_block_geom* g, TcParams* p) {
                     const int pitch = ((TC - 1) * g->S * g->C + fcpad(g->F, g->C) + 3) & ~3;
                     if (prow * pitch * 4 > kMaxPatchBytes || prow > kRowTab) break;
                 }
-                const long cost = (long)cdiv(rows, PR) * cdiv(g->Wp, PC) * nacc * 1024 + slots;
+                const long tiles = (long)cdiv(rows, PR) * cdiv(g->Wp, PC);
+                const double per_kb = nacc * (mma_kb > prod_kb ? mma_kb : prod_kb);
+                const double tile_cycles = nkb * per_kb + 14000.0 + nacc * (g->K / 32) * 900.0 +
+                                           (g->lrn.N_lrn > 0 ? 20000.0 : 0.0);
+                const long waves = (tiles * (long)g->N + kPlanSms - 1) / kPlanSms;
+                const double cost = waves * tile_cycles + slots * 1e-3;
                 if (best < 0 || cost < best) {
                     best = cost;
                     p->PR = PR; p->PC = PC; p->TR = TR; p->TC = TC; p->nacc = nacc;

@@ -205,6 +205,16 @@ class Blocks12Engine:
                          self._flag_ptr(self.rank, self.lay.status_off), self.timeout_ns)
             self.launches += 1
 
+    def stage_barrier(self) -> None:
+        """signal + wait in ONE launch; only valid when every rank owns its GPU (real multi-GPU)."""
+        if self.world > 1:
+            W = range(self.world)
+            cu.flag_barrier([self._flag_ptr(r, self.lay.bar_off + self.rank) for r in W],
+                            [self._flag_ptr(self.rank, self.lay.bar_off + r) for r in W],
+                            [self.epoch] * self.world,
+                            self._flag_ptr(self.rank, self.lay.status_off), self.timeout_ns)
+            self.launches += 1
+
     def stage_block1(self, in_idx: int = 0) -> None:
         rp = self.rp
         if rp.pool1_own[1] <= rp.pool1_own[0]:
@@ -247,8 +257,7 @@ class Blocks12Engine:
         assert self._final, "call finalize() first"
         with torch.cuda.device(self.device):
             self.stage_begin()
-            self.stage_barrier_signal()
-            self.stage_barrier_wait()
+            self.stage_barrier()
             self.stage_block1(in_idx)
             self.stage_block2(out_idx)
             self.stage_done_signal()

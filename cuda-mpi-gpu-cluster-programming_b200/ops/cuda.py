@@ -55,6 +55,8 @@ def lib():
         L.b200_flag_signal.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_void_p]
         L.b200_flag_wait.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.c_int,
                                      C.c_void_p, C.c_ulonglong, C.c_void_p]
+        L.b200_flag_barrier.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_int),
+                                        C.c_int, C.c_void_p, C.c_ulonglong, C.c_void_p]
         L.b200_conv_nchw.argtypes = [C.c_void_p] * 4 + [C.c_int] * 8 + [C.c_void_p]
         L.b200_conv_nchw_scratch_bytes.argtypes = [C.c_int] * 8
         L.b200_conv_nchw_scratch_bytes.restype = C.c_longlong
@@ -150,3 +152,14 @@ def conv_nchw(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], S:
                                   fptr(bias.contiguous()) if bias is not None else None, fptr(out),
                                   N, Cc, H, W, K, F, S, P, current_stream_ptr()), "conv_nchw")
     return out
+
+
+def flag_barrier(signal_targets: Sequence[int], wait_flags: Sequence[int], wait_targets: Sequence[int],
+                 status_ptr: int = 0, timeout_ns: int = DEFAULT_TIMEOUT_NS) -> None:
+    """Cross-GPU barrier in one launch (ranks must own one GPU each)."""
+    n = len(signal_targets)
+    sa = (C.c_void_p * n)(*signal_targets)
+    fa = (C.c_void_p * n)(*wait_flags)
+    ta = (C.c_int * n)(*wait_targets)
+    cu_check(lib().b200_flag_barrier(sa, fa, ta, n, C.c_void_p(status_ptr or None), timeout_ns,
+                                     current_stream_ptr()), "flag_barrier")

@@ -187,6 +187,9 @@ int b200_enable_peer(int peer);
 int b200_flag_signal(int* const* targets, int n, int add, void* stream);
 int b200_flag_wait(const int* const* flags, const int* target, int n, int* status,
                    unsigned long long timeout_ns, void* stream);
+/* signal + wait in one launch (one GPU per rank only: the wait spins on peers' signals) */
+int b200_flag_barrier(int* const* signal_targets, const int* const* wait_flags, const int* wait_target,
+                      int n, int* status, unsigned long long timeout_ns, void* stream);
 
 #ifdef __cplusplus
 }
