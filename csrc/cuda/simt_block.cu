@@ -54,7 +54,7 @@ simt_block_kernel(const float* __restrict__ wt,    // [F][F*C][K]
         for (int s = 0; s < g.nseg; ++s) {
             const b200_row_seg& sg = g.seg[s];
             if (sg.flag && ir0 < sg.hi && ir0 + IR > sg.lo)
-                wait_flag_ge(sg.flag + n, sg.target, g.status, g.timeout_ns);
+                wait_flag_ge(sg.flag + n, sg.target * (g.epoch ? *g.epoch : 1), g.status, g.timeout_ns);
         }
     }
     __syncthreads();

@@ -76,19 +76,25 @@ __global__ void flag_signal_kernel(SignalArgs a, int add) {
 
 struct WaitArgs { int n; const int* flag[16]; int target[16]; };
 
-__global__ void flag_wait_kernel(WaitArgs a, int* status, unsigned long long timeout_ns) {
+__global__ void flag_wait_kernel(WaitArgs a, int* status, unsigned long long timeout_ns, const int* epoch) {
+    const int mult = epoch ? *epoch : 1;
     if ((int)threadIdx.x < a.n)
-        wait_flag_ge(a.flag[threadIdx.x], a.target[threadIdx.x], status, timeout_ns);
+        wait_flag_ge(a.flag[threadIdx.x], a.target[threadIdx.x] * mult, status, timeout_ns);
     __syncthreads();
     __threadfence_system();
 }
 
 // Barrier in one launch: bump one counter on every peer, then wait for every peer's bump on ours.
 // Only for ranks that own a GPU each (the waits would deadlock if ranks shared a device).
-__global__ void flag_barrier_kernel(SignalArgs sig, WaitArgs w, int* status, unsigned long long timeout_ns) {
+__global__ void flag_barrier_kernel(SignalArgs sig, WaitArgs w, int* status, unsigned long long timeout_ns,
+                                    int* epoch) {
+    __shared__ int s_epoch;
+    if (threadIdx.x == 0) s_epoch = epoch ? ++(*epoch) : 0;      // this kernel opens forward number *epoch
+    __syncthreads();
     __threadfence_system();
     if ((int)threadIdx.x < sig.n) red_release_sys_add(sig.target[threadIdx.x], 1);
-    if ((int)threadIdx.x < w.n) wait_flag_ge(w.flag[threadIdx.x], w.target[threadIdx.x], status, timeout_ns);
+    if ((int)threadIdx.x < w.n)
+        wait_flag_ge(w.flag[threadIdx.x], epoch ? s_epoch : w.target[threadIdx.x], status, timeout_ns);
     __syncthreads();
     __threadfence_system();
 }
@@ -97,14 +103,14 @@ __global__ void flag_barrier_kernel(SignalArgs sig, WaitArgs w, int* status, uns
 
 extern "C" int b200_flag_barrier(int* const* signal_targets, const int* const* wait_flags,
                                  const int* wait_target, int n, int* status, unsigned long long timeout_ns,
-                                 void* stream) {
+                                 int* epoch, void* stream) {
     if (n < 0 || n > 16 || (n && (!signal_targets || !wait_flags || !wait_target))) return B200_ERR_ARG;
     if (n == 0) return B200_OK;
     SignalArgs s;
     WaitArgs w;
     s.n = w.n = n;
     for (int i = 0; i < n; ++i) { s.target[i] = signal_targets[i]; w.flag[i] = wait_flags[i]; w.target[i] = wait_target[i]; }
-    flag_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(s, w, status, timeout_ns);
+    flag_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(s, w, status, timeout_ns, epoch);
     B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;
 }
@@ -123,13 +129,13 @@ extern "C" int b200_flag_signal(int* const* targets, int n, int add, void* strea
 
 // waits (on the stream) until flags[i] >= target[i] for all i; watchdog -> *status = TIMEOUT
 extern "C" int b200_flag_wait(const int* const* flags, const int* target, int n, int* status,
-                              unsigned long long timeout_ns, void* stream) {
+                              unsigned long long timeout_ns, const int* epoch, void* stream) {
     if (n < 0 || n > 16 || (n && (!flags || !target))) return B200_ERR_ARG;
     if (n == 0) return B200_OK;
     WaitArgs a;
     a.n = n;
     for (int i = 0; i < n; ++i) { a.flag[i] = flags[i]; a.target[i] = target[i]; }
-    flag_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(a, status, timeout_ns);
+    flag_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(a, status, timeout_ns, epoch);
     B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;
 }

@@ -295,7 +295,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                 if (tid == 0) {
                     for (int s = 0; s < g.nseg; ++s)
                         if (g.seg[s].flag && ir0 < g.seg[s].hi && ir0 + IRT > g.seg[s].lo)
-                            wait_flag_ge(g.seg[s].flag + n, g.seg[s].target, g.status, g.timeout_ns);
+                            wait_flag_ge(g.seg[s].flag + n, g.seg[s].target * (g.epoch ? *g.epoch : 1), g.status, g.timeout_ns);
                 }
                 bar_producers();
             }

@@ -57,6 +57,10 @@ class _Layout:
         return self.done_off + self.world
 
     @property
+    def epoch_off(self):    # device-side forward counter (bumped by the barrier kernel)
+        return self.status_off + 1
+
+    @property
     def count(self):
         return self.status_off + 16
 
@@ -64,7 +68,8 @@ class _Layout:
 class Blocks12Engine:
     def __init__(self, cfg: NetConfig, weights: Blocks12Weights, symm, rank: int = 0,
                  world: int = 1, *, precision: Optional[str] = None, strategy: str = "halo",
-                 scatter: str = "p2p", timeout_ns: int = cu.DEFAULT_TIMEOUT_NS):
+                 scatter: str = "p2p", timeout_ns: int = cu.DEFAULT_TIMEOUT_NS,
+                 device_epoch: Optional[bool] = None, use_graph: Optional[bool] = None):
         if scatter not in ("p2p", "sharded"):
             raise ValueError(scatter)
         self.cfg = cfg
@@ -79,6 +84,14 @@ class Blocks12Engine:
         self.sh = self.plan.shapes
         self.epoch = 0
         self.launches = 0            # kernels launched by this engine (bench reports it)
+        # device_epoch: flag targets are derived on the device from a forward counter, so launch
+        # arguments never change and a whole forward can be replayed as one CUDA graph.  The
+        # single-GPU emulation of several ranks launches barrier halves separately and keeps the
+        # host-side epoch instead.
+        self.device_epoch = (world > 1) if device_epoch is None else device_epoch
+        self.use_graph = True if use_graph is None else use_graph
+        self._graphs = {}            # (in_idx, out_idx) -> (torch.cuda.CUDAGraph, kernels per replay)
+        self._calls = {}
         self.lay = _Layout(world, cfg.batch)
         sh, rp, N = self.sh, self.rp, cfg.batch
 
@@ -180,13 +193,14 @@ class Blocks12Engine:
             segs.append(dict(ptr=self.symm.ptr(peer, "pool1"), base=po[0], slab=po[1] - po[0],
                              lo=lo, hi=hi,
                              flag=self._flag_ptr(self.rank, self.lay.arr_off + peer * self.lay.nmax),
-                             target=self.epoch * self._b1_tiles[peer]))
+                             target=(1 if self.device_epoch else self.epoch) * self._b1_tiles[peer]))
         lrn = LrnParams(p2.N_lrn, p2.alpha, p2.beta, p2.k_lrn, LRN_MODES[cfg.lrn_mode])
         return cu.make_block_geom(
             N=cfg.batch, H=sh.Hp1, W=sh.Wp1, Cin=sh.K1, K=p2.K, F=p2.F, S=p2.S, P=p2.P,
             Hc=sh.Hc2, Wc=sh.Wc2, Hp=sh.Hp2, Wp=sh.Wp2, rows=rp.out_rows,
             out_base=0, out_slab=sh.Hp2, lrn=lrn, segs=segs, signals=[],
-            status_ptr=self._flag_ptr(self.rank, self.lay.status_off), timeout_ns=self.timeout_ns)
+            status_ptr=self._flag_ptr(self.rank, self.lay.status_off), timeout_ns=self.timeout_ns,
+            epoch_ptr=self._flag_ptr(self.rank, self.lay.epoch_off) if self.device_epoch else 0)
 
     # ---- forward stages (each enqueues on the current stream) ----------------------------------
     def stage_begin(self) -> None:
@@ -212,7 +226,8 @@ class Blocks12Engine:
             cu.flag_barrier([self._flag_ptr(r, self.lay.bar_off + self.rank) for r in W],
                             [self._flag_ptr(self.rank, self.lay.bar_off + r) for r in W],
                             [self.epoch] * self.world,
-                            self._flag_ptr(self.rank, self.lay.status_off), self.timeout_ns)
+                            self._flag_ptr(self.rank, self.lay.status_off), self.timeout_ns,
+                            self._flag_ptr(self.rank, self.lay.epoch_off) if self.device_epoch else 0)
             self.launches += 1
 
     def stage_block1(self, in_idx: int = 0) -> None:
@@ -245,8 +260,9 @@ class Blocks12Engine:
     def stage_done_wait(self) -> None:
         if self.world > 1 and self.rank == 0:
             cu.flag_wait([self._flag_ptr(0, self.lay.done_off + r) for r in range(self.world)],
-                         [self.epoch] * self.world,
-                         self._flag_ptr(0, self.lay.status_off), self.timeout_ns)
+                         [1 if self.device_epoch else self.epoch] * self.world,
+                         self._flag_ptr(0, self.lay.status_off), self.timeout_ns,
+                         self._flag_ptr(0, self.lay.epoch_off) if self.device_epoch else 0)
             self.launches += 1
 
     def forward_enqueue(self, in_idx: int = 0, out_idx: int = 0) -> Optional[torch.Tensor]:
@@ -255,14 +271,41 @@ class Blocks12Engine:
         mode).  Returns rank 0's output tensor ``out_idx`` (valid once the stream gets here).
         Every rank must pass the same ``in_idx`` / ``out_idx`` for the same forward."""
         assert self._final, "call finalize() first"
+        key = (in_idx, out_idx)
         with torch.cuda.device(self.device):
-            self.stage_begin()
-            self.stage_barrier()
-            self.stage_block1(in_idx)
-            self.stage_block2(out_idx)
-            self.stage_done_signal()
-            self.stage_done_wait()
+            hit = self._graphs.get(key)
+            if hit is not None:
+                hit[0].replay()
+                self.epoch += 1
+                self.launches += hit[1]
+                return self.outs[out_idx]
+            n = self._calls.get(key, 0)
+            self._calls[key] = n + 1
+            graphable = self.use_graph and (self.world == 1 or self.device_epoch)
+            if graphable and n >= 1:                      # first call ran eagerly (warm-up); capture now
+                try:
+                    l0 = self.launches
+                    e0 = self.epoch
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g):
+                        self._enqueue_stages(in_idx, out_idx)
+                    self._graphs[key] = (g, self.launches - l0)
+                    self.launches, self.epoch = l0, e0    # capture launched nothing
+                    return self.forward_enqueue(in_idx, out_idx)
+                except Exception as ex:                   # capture unsupported: stay eager
+                    import warnings
+                    warnings.warn(f"CUDA graph capture failed ({ex}); running eagerly")
+                    self.use_graph = False
+            self._enqueue_stages(in_idx, out_idx)
         return self.outs[out_idx]
+
+    def _enqueue_stages(self, in_idx: int, out_idx: int) -> None:
+        self.stage_begin()
+        self.stage_barrier()
+        self.stage_block1(in_idx)
+        self.stage_block2(out_idx)
+        self.stage_done_signal()
+        self.stage_done_wait()
 
     def forward(self, x: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
         """Device-tensor API: copies ``x`` (this rank's input; whole batch on rank 0 in p2p mode)
@@ -303,7 +346,8 @@ class EmulatedWorld:
         self.symm = LocalSymm(world, device)
         self.engines: List[Blocks12Engine] = [
             Blocks12Engine(cfg, weights, self.symm.view(r), r, world, precision=precision,
-                           strategy=strategy, scatter=scatter) for r in range(world)]
+                           strategy=strategy, scatter=scatter, device_epoch=False, use_graph=False)
+            for r in range(world)]
         for e in self.engines:
             e.finalize()
         self.cfg = cfg

@@ -30,7 +30,7 @@ class BlockGeom(C.Structure):
         "out_base", "out_slab")] + [
         ("lrn", LrnParams), ("nseg", C.c_int), ("n_signal", C.c_int),
         ("seg", RowSeg * MAX_SEG), ("signal", C.c_void_p * MAX_SIGNAL),
-        ("status", C.c_void_p), ("timeout_ns", C.c_ulonglong)]
+        ("status", C.c_void_p), ("timeout_ns", C.c_ulonglong), ("epoch", C.c_void_p)]
 
 
 _lib = None
@@ -54,9 +54,9 @@ def lib():
         L.b200_enable_peer.argtypes = [C.c_int]
         L.b200_flag_signal.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_void_p]
         L.b200_flag_wait.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.c_int,
-                                     C.c_void_p, C.c_ulonglong, C.c_void_p]
+                                     C.c_void_p, C.c_ulonglong, C.c_void_p, C.c_void_p]
         L.b200_flag_barrier.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_int),
-                                        C.c_int, C.c_void_p, C.c_ulonglong, C.c_void_p]
+                                        C.c_int, C.c_void_p, C.c_ulonglong, C.c_void_p, C.c_void_p]
         L.b200_conv_nchw.argtypes = [C.c_void_p] * 4 + [C.c_int] * 8 + [C.c_void_p]
         L.b200_conv_nchw_scratch_bytes.argtypes = [C.c_int] * 8
         L.b200_conv_nchw_scratch_bytes.restype = C.c_longlong
@@ -86,7 +86,8 @@ def pack_weights_ffck(w: torch.Tensor) -> torch.Tensor:
 def make_block_geom(*, N, H, W, Cin, K, F, S, P, Hc, Wc, Hp, Wp, rows: Tuple[int, int],
                     out_base: int, out_slab: int, lrn: Optional[LrnParams],
                     segs: Sequence[dict], signals: Sequence[int] = (),
-                    status_ptr: int = 0, timeout_ns: int = DEFAULT_TIMEOUT_NS) -> BlockGeom:
+                    status_ptr: int = 0, timeout_ns: int = DEFAULT_TIMEOUT_NS,
+                    epoch_ptr: int = 0) -> BlockGeom:
     g = BlockGeom()
     g.N, g.H, g.W, g.C = N, H, W, Cin
     g.K, g.F, g.S, g.P = K, F, S, P
@@ -107,6 +108,7 @@ def make_block_geom(*, N, H, W, Cin, K, F, S, P, Hc, Wc, Hp, Wp, rows: Tuple[int
         g.signal[i] = p
     g.status = status_ptr or None
     g.timeout_ns = timeout_ns
+    g.epoch = epoch_ptr or None
     return g
 
 
@@ -127,13 +129,13 @@ def flag_signal(targets: Sequence[int], add: int = 1) -> None:
 
 
 def flag_wait(flags: Sequence[int], targets: Sequence[int], status_ptr: int = 0,
-              timeout_ns: int = DEFAULT_TIMEOUT_NS) -> None:
+              timeout_ns: int = DEFAULT_TIMEOUT_NS, epoch_ptr: int = 0) -> None:
     if not flags:
         return
     fa = (C.c_void_p * len(flags))(*flags)
     ta = (C.c_int * len(flags))(*targets)
     cu_check(lib().b200_flag_wait(fa, ta, len(flags), C.c_void_p(status_ptr or None),
-                                  timeout_ns, current_stream_ptr()), "flag_wait")
+                                  timeout_ns, C.c_void_p(epoch_ptr or None), current_stream_ptr()), "flag_wait")
 
 
 def dgemm_rows(a_ptr: int, b_ptr: int, c_ptr: int, rows: int, n: int) -> None:
@@ -155,11 +157,11 @@ def conv_nchw(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], S:
 
 
 def flag_barrier(signal_targets: Sequence[int], wait_flags: Sequence[int], wait_targets: Sequence[int],
-                 status_ptr: int = 0, timeout_ns: int = DEFAULT_TIMEOUT_NS) -> None:
+                 status_ptr: int = 0, timeout_ns: int = DEFAULT_TIMEOUT_NS, epoch_ptr: int = 0) -> None:
     """Cross-GPU barrier in one launch (ranks must own one GPU each)."""
     n = len(signal_targets)
     sa = (C.c_void_p * n)(*signal_targets)
     fa = (C.c_void_p * n)(*wait_flags)
     ta = (C.c_int * n)(*wait_targets)
     cu_check(lib().b200_flag_barrier(sa, fa, ta, n, C.c_void_p(status_ptr or None), timeout_ns,
-                                     current_stream_ptr()), "flag_barrier")
+                                     C.c_void_p(epoch_ptr or None), current_stream_ptr()), "flag_barrier")

@@ -125,6 +125,9 @@ typedef struct {
     int* signal[B200_MAX_SIGNAL];   /* per-image counters (usually on peers) bumped per finished tile */
     int* status;             /* device word: first error code of the launch (0 = ok)      */
     unsigned long long timeout_ns;
+    const int* epoch;        /* optional device counter of forwards: when set, seg[].target is a
+                                per-forward increment and the wait target is (*epoch) * target, so
+                                the launch arguments never change (CUDA-graph friendly)         */
 } b200_block_geom;
 
 /* host: [K][C][F][F] (reference layout) -> [F][F][C][K] used by the SIMT kernels */
@@ -186,10 +189,13 @@ int b200_enable_peer(int peer);
  * to 16 counters (local or peer); wait = spin until flags[i] >= target[i] with a watchdog. */
 int b200_flag_signal(int* const* targets, int n, int add, void* stream);
 int b200_flag_wait(const int* const* flags, const int* target, int n, int* status,
-                   unsigned long long timeout_ns, void* stream);
+                   unsigned long long timeout_ns, const int* epoch /* NULL or device counter: target *= *epoch */,
+                   void* stream);
 /* signal + wait in one launch (one GPU per rank only: the wait spins on peers' signals) */
 int b200_flag_barrier(int* const* signal_targets, const int* const* wait_flags, const int* wait_target,
-                      int n, int* status, unsigned long long timeout_ns, void* stream);
+                      int n, int* status, unsigned long long timeout_ns,
+                      int* epoch /* NULL, or device counter this kernel increments and waits for */,
+                      void* stream);
 
 #ifdef __cplusplus
 }

@@ -38,7 +38,7 @@ for scatter in ("p2p", "sharded"):
         t_b1 = timeit(lambda: e.stage_block1(0))
         t_b2 = timeit(lambda: e.stage_block2(0))         # flags already satisfied: no waiting
         def bar():
-            e.stage_begin(); e.stage_barrier_signal(); e.stage_barrier_wait()
+            e.stage_begin(); e.stage_barrier()
         t_bar = timeit(bar)
         rows = ctx.all_gather_object((ctx.rank, round(t_fwd, 1), round(t_b1, 1), round(t_b2, 1), round(t_bar, 1),
                                       e.rp.out_rows, e.rp.pool1_own, e.rp.in_rows))
