@@ -96,6 +96,7 @@ def run_ours(a):
         evs = []
         for i in range(a.steps):                 # enqueue everything, sync once: launch overhead of
             flush.fill_(i & 0xFF)                # the next step hides behind the (untimed) L2 flush
+            e.sync_ranks()                       # untimed: every rank has finished its flush
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             ev0.record()
             e.forward_enqueue(i % 2, i % 2)

@@ -57,12 +57,16 @@ class _Layout:
         return self.done_off + self.world
 
     @property
+    def sync_off(self):     # second barrier counter set [src_rank] for sync_ranks() (no epoch)
+        return self.status_off + 2
+
+    @property
     def epoch_off(self):    # device-side forward counter (bumped by the barrier kernel)
         return self.status_off + 1
 
     @property
     def count(self):
-        return self.status_off + 16
+        return self.status_off + 2 + self.world + 16
 
 
 class Blocks12Engine:
@@ -229,6 +233,18 @@ class Blocks12Engine:
                             self._flag_ptr(self.rank, self.lay.status_off), self.timeout_ns,
                             self._flag_ptr(self.rank, self.lay.epoch_off) if self.device_epoch else 0)
             self.launches += 1
+
+    def sync_ranks(self) -> None:
+        """Stream-ordered device-side barrier on its own counters (does not open a forward): used to
+        line the ranks up, e.g. right before a timed region.  One GPU per rank only."""
+        if self.world > 1:
+            self._sync_epoch = getattr(self, "_sync_epoch", 0) + 1
+            W = range(self.world)
+            with torch.cuda.device(self.device):
+                cu.flag_barrier([self._flag_ptr(r, self.lay.sync_off + self.rank) for r in W],
+                                [self._flag_ptr(self.rank, self.lay.sync_off + r) for r in W],
+                                [self._sync_epoch] * self.world,
+                                self._flag_ptr(self.rank, self.lay.status_off), self.timeout_ns, 0)
 
     def stage_block1(self, in_idx: int = 0) -> None:
         rp = self.rp
