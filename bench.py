@@ -48,6 +48,8 @@ def parse():
                          "pulled over NVLink inside conv1 (reported as config.p2p_scatter_images_per_s)")
     ap.add_argument("--e2e-scatter", choices=["p2p", "sharded"], default="sharded",
                     help="end-to-end run: p2p = rank 0 feeds everything; sharded = each rank feeds its slab")
+    ap.add_argument("--e2e-strategy", choices=["same", "halo", "recompute"], default="halo",
+                    help="decomposition for the end-to-end run (halo = smallest input slabs = fewest H2D bytes)")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
 
@@ -178,17 +180,20 @@ def run_ours(a):
     clocks.pop("samples", None)
     e2e = None
     if not a.no_e2e:
-        if a.e2e_scatter != a.scatter and N > 1:
+        e2e_strategy = a.strategy if a.e2e_strategy == "same" else a.e2e_strategy
+        if N > 1 and (a.e2e_scatter != a.scatter or e2e_strategy != a.strategy):
             del sess
             torch.cuda.empty_cache()
             sess = Session(cfg, w, dist=ctx, device=dev, precision=precision,
-                           strategy=a.strategy, scatter=a.e2e_scatter)
+                           strategy=e2e_strategy, scatter=a.e2e_scatter)
         e2e_ms, h2d, d2h = measure_e2e(sess)
         h2d_all = sum(ctx.all_gather_object(h2d))
         d2h_all = sum(ctx.all_gather_object(d2h))
         e2e = {"value": round(a.batch * a.steps / (e2e_ms / 1e3), 2), "unit": "images/s",
                "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": d2h_all,
-               "scatter": a.e2e_scatter if N > 1 else "local", "pipelined_steps_in_flight": 2}
+               "scatter": a.e2e_scatter if N > 1 else "local",
+               "strategy": (a.strategy if a.e2e_strategy == "same" else a.e2e_strategy) if N > 1 else "single-gpu",
+               "pipelined_steps_in_flight": 2}
     ms_per_step = total_ms / a.steps
     value = a.batch / (ms_per_step / 1e3)
     base = REF_V4_BEST_IMG_S.get(N)
