@@ -174,6 +174,11 @@ __device__ __forceinline__ void cp_async4(uint32_t dst, const void* src, uint32_
 __device__ __forceinline__ void cp_async_wait_all() {
     asm volatile("cp.async.wait_all;" ::: "memory");
 }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int kPending>
+__device__ __forceinline__ void cp_async_wait_group() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory");
+}
 // the mbarrier gets one arrival from this thread once all its earlier cp.async have landed
 __device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
     asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
@@ -243,7 +248,8 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.stages; ++s) {
-            mbar_init(full_bar + 8 * s, kProducerThreads + 1);    // every producer thread + TMA
+            // vec mode: every producer thread's cp.async group arrives (noinc); patch mode: one per warp
+            mbar_init(full_bar + 8 * s, (kPatch ? kProducerWarps : kProducerThreads) + 1);
             mbar_init(empty_bar + 8 * s, 1);
         }
         mbar_init(tmem_full_bar, 1);
@@ -354,7 +360,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
             int pfy = (4 * j) / p.FCpad, pt = (4 * j) - pfy * p.FCpad;   // patch: this thread's chunk
             const char* rp8[8];                                 // vec: row pointers for the current fy
             uint32_t vm[8];                                     // vec: xmask, or 0 when the row is padding
-            for (int kb = 0; kb < p.nkb; ++kb) {
+            for (int kb = 0; kb < ((p.dbg & 8) ? 0 : p.nkb); ++kb) {
                 if (!kPatch && fx == 0) {
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
@@ -366,7 +372,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                 const uint32_t a_dst = base + stage * kAStageBytes + dst0;
                 const uint32_t fb = full_bar + 8 * stage;
                 if (p.dbg & 1) {
-                    mbar_arrive(fb);
+                    if (kPatch) { __syncwarp(); if (lane == 0) mbar_arrive(fb); } else mbar_arrive(fb);
                 } else if (kPatch) {
                     const float* src = patch + pfy * p.patch_pitch + pt;
 #pragma unroll
@@ -378,7 +384,8 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                                      : "memory");
                     }
                     fence_proxy_async_smem();                  // generic stores -> async proxy (UMMA)
-                    mbar_arrive(fb);
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(fb);            // one arrival per warp (256 would serialise)
                     pt += kBlockK;
                     while (pt >= p.FCpad) { pt -= p.FCpad; ++pfy; }
                 } else {
@@ -395,7 +402,6 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                 }
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
-
             // ------------------------------ epilogue ------------------------------------
             mbar_wait(tmem_full_bar, (uint32_t)(it & 1));
             tc_fence_after();
@@ -405,6 +411,10 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
             const int PP = p.PR * p.PC;
             const int nchunk = N / 32;
             const bool do_lrn = g.lrn.N_lrn > 0;
+            const int NP = N + 4;                              // pbuf row: [2 zeros | N channels | 2 zeros]
+            if (do_lrn)
+                for (int i = tid; i < PP * 4; i += kProducerThreads)
+                    pbuf[(i >> 2) * NP + ((i & 3) < 2 ? (i & 3) : N + (i & 3))] = 0.f;
             for (int cc = 0; cc < ((p.dbg & 4) ? 0 : nchunk); ++cc) {
                 float* cb = cbuf0 + (cc & 1) * (kCbufBytes / 4);
                 if (has_acc) {
@@ -416,7 +426,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                 bar_producers();
                 // pool: lane = channel inside the chunk, warp strides over pooled pixels
                 const float bch = s_bias[cc * 32 + lane];
-                for (int pp = warp; pp < PP; pp += kProducerWarps) {
+                for (int pp = warp; pp < ((p.dbg & 32) ? 0 : PP); pp += kProducerWarps) {
                     const int2 e = ptab[pp];
                     const float* c0p = cb + e.x + lane;
                     float mx = -INFINITY;
@@ -427,7 +437,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                             mx = fmaxf(mx, c0p[(a * p.TC + b) * kCbufPitch]);
                     float val = fmaxf(mx + bch, 0.f);          // relu(max(x)+b) == max(relu(x+b))
                     if (do_lrn) {
-                        pbuf[pp * N + cc * 32 + lane] = val;
+                        pbuf[pp * NP + 2 + cc * 32 + lane] = val;
                     } else {
                         const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
                         if (p.round_out) val = to_tf32(val);
@@ -437,26 +447,46 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                     }
                 }
             }
-            if (do_lrn && !(p.dbg & 4)) {
+            if (do_lrn && !(p.dbg & (4 | 16))) {
                 bar_producers();
                 const int half = g.lrn.N_lrn / 2;
                 const float al = g.lrn.mode == B200_LRN_ALPHA_OVER_N
                                      ? g.lrn.alpha / (float)g.lrn.N_lrn : g.lrn.alpha;
                 const float nbeta = -g.lrn.beta;
-                for (int pp = 0; pp < PP; ++pp) {
-                    const int2 e = ptab[pp];
-                    const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
-                    if (pr >= g.p1 || pr >= g.Hp || pc >= g.Wp) continue;      // uniform
-                    const float* px = pbuf + pp * N;
-                    float* o = out + (((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N;
+                const bool win5 = g.lrn.N_lrn == 5;           // AlexNet's window: straight-line 5 taps
+                for (int pp0 = 0; pp0 < PP; pp0 += 4) {       // 4 independent pixels per trip (ILP)
+                    float* optr[4];
+                    const float* prow[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int pp = pp0 + u < PP ? pp0 + u : PP - 1;
+                        const int2 e = ptab[pp];
+                        const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
+                        const bool ok = pp0 + u < PP && pr < g.p1 && pr < g.Hp && pc < g.Wp;
+                        optr[u] = ok ? out + (((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N : nullptr;
+                        prow[u] = pbuf + pp * NP;              // channel c sits at prow[c + 2]; 2 zero pads each side
+                    }
                     for (int c = tid; c < N; c += kProducerThreads) {
-                        float ss = 0.f;
-                        const int c_lo = max(0, c - half), c_hi = min(N - 1, c + half);
-                        for (int q = c_lo; q <= c_hi; ++q) ss = fmaf(px[q], px[q], ss);
-                        // x / (k + a*ss)^beta; the base is >= k > 0, so exp2/log2 is safe and ~1 ulp-ish
-                        float val = px[c] * exp2f(nbeta * __log2f(g.lrn.k + al * ss));
-                        if (p.round_out) val = to_tf32(val);
-                        o[c] = val;
+                        float val[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const float* px = prow[u] + c;
+                            float ss;
+                            if (win5) {
+                                const float a0 = px[0], a1 = px[1], a2 = px[2], a3 = px[3], a4 = px[4];
+                                ss = fmaf(a0, a0, fmaf(a1, a1, fmaf(a2, a2, fmaf(a3, a3, a4 * a4))));
+                            } else {
+                                ss = 0.f;
+                                const int c_lo = max(0, c - half), c_hi = min(N - 1, c + half);
+                                for (int q = c_lo; q <= c_hi; ++q) ss = fmaf(prow[u][q + 2], prow[u][q + 2], ss);
+                            }
+                            // x / (k + a*ss)^beta; the base is >= k > 0, so exp2/log2 is safe
+                            val[u] = px[2] * exp2f(nbeta * __log2f(g.lrn.k + al * ss));
+                            if (p.round_out) val[u] = to_tf32(val[u]);
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            if (optr[u]) optr[u][c] = val[u];
                     }
                 }
             }
@@ -473,7 +503,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
         // ======================================= MMA issuer ==============================
         for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
             for (int kb = 0; kb < p.nkb; ++kb) {
-                mbar_wait(full_bar + 8 * stage, phase);
+                if (!(p.dbg & 8)) mbar_wait(full_bar + 8 * stage, phase);
                 tc_fence_after();
                 if (lane == 0) {
                     const uint32_t a_stage = base + stage * kAStageBytes;
@@ -487,7 +517,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                                       (kb | ks) != 0 ? 1u : 0u);
                         }
                     }
-                    umma_commit(empty_bar + 8 * stage);        // frees the stage when the MMAs retire
+                    if (!(p.dbg & 8)) umma_commit(empty_bar + 8 * stage);   // frees the stage when the MMAs retire
                     if (kb == p.nkb - 1) umma_commit(tmem_full_bar);
                 }
                 __syncwarp();
@@ -500,7 +530,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
         for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x, ++it) {
             // the previous tile's epilogue buffers alias the stages: wait until they are released
             if (it > 0) mbar_wait(tile_free_bar, (uint32_t)((it - 1) & 1));
-            for (int kb = 0; kb < p.nkb; ++kb) {
+            for (int kb = 0; kb < ((p.dbg & 8) ? 0 : p.nkb); ++kb) {
                 mbar_wait(empty_bar + 8 * stage, phase ^ 1);
                 if (lane == 0) {
                     const uint32_t fb = full_bar + 8 * stage;
@@ -628,7 +658,7 @@ int fill_params(const b200_block_geom* g, TcParams* p, int flags) {
         patch_bytes = (size_t)p->patch_rows * p->patch_pitch * 4;
     }
     const size_t ctl_bytes = 16 * 4 + 32 + kRowTab * 8 + kMaxPooled * 8 + (size_t)g->K * 4 + 64;
-    const size_t epi = 2 * (size_t)kCbufBytes + (g->lrn.N_lrn > 0 ? (size_t)kMaxPooled * g->K * 4 : 0);
+    const size_t epi = 2 * (size_t)kCbufBytes + (g->lrn.N_lrn > 0 ? (size_t)kMaxPooled * (g->K + 4) * 4 : 0);
     const int stage_bytes = kAStageBytes + p->b_stage_bytes;
     const long avail = 226 * 1024 - 1024 - (long)patch_bytes - (long)ctl_bytes;
     int stages = (int)(avail / stage_bytes);

@@ -24,10 +24,10 @@ def timeit(fn, n=10):
     e1.record(); e1.synchronize()
     return e0.elapsed_time(e1) / n * 1e3
 
-for dbg in (0, 1, 2, 3, 4, 5, 6, 7):
+for dbg in (0, 16, 4):
     os.environ["B200_TC_DBG"] = str(dbg)
     eng.epoch = 0
     t1 = timeit(lambda: eng.stage_block1(0))
     t2 = timeit(lambda: eng.stage_block2(0))
-    print(f"dbg={dbg} (A{'-' if dbg&1 else '+'} B{'-' if dbg&2 else '+'} epi{'-' if dbg&4 else '+'}): "
+    print(f"dbg={dbg} (A{'-' if dbg&1 else '+'} B{'-' if dbg&2 else '+'} epi{'-' if dbg&4 else '+'} {'MMA-free-run' if dbg&8 else ''}{' noLRN' if dbg&16 else ''}{' noPool' if dbg&32 else ''}{' noLRNstore' if dbg&64 else ''}{' noLRNmath' if dbg&128 else ''}): "
           f"block1 {t1:8.1f} us   block2 {t2:8.1f} us", flush=True)
