@@ -555,6 +555,260 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
     }
 }
 
+// ------------------------------------------------------- small-K_out kernel (conv1) ----
+// tc_block_kernel spends ~160 cycles per tcgen05.mma whatever N is (profiles/tc_experiments_v5.log:
+// with N=96 the tensor pipe is instruction-bound, not FLOP-bound), and its producer warps double as
+// epilogue warps, so staging, MMA and epilogue of a tile run one after the other.  For layers with
+// few output channels (K_out <= 128: conv1) this kernel turns the GEMM around and splits the roles:
+//   * A operand = weights [K_out -> 128 rows][K] (TMA), B operand = the im2col pixels, N = 128/256
+//     pixel slots per instruction: half as many tcgen05.mma per tile;
+//   * D is channels x pixels: 128 TMEM lanes x 256 columns = half of TMEM, so accumulators are
+//     double buffered and tile t's epilogue overlaps tile t+1's staging and MMAs;
+//   * warps 0-7 only stage the input patch and build B; warp 8 issues MMAs; warp 9 issues TMA;
+//     warps 10-13 are the epilogue: warp q owns TMEM lane quarter q = channels 32q..32q+31, drains
+//     three conv rows at a time through a private smem strip, max-pools and stores — no CTA-wide
+//     barrier anywhere in the epilogue.
+constexpr int kSwThreads = 448;
+constexpr int kSwEpiWarp0 = 10;
+constexpr int kSwStages = 2;
+constexpr int kSwWStageBytes = 128 * 128;            // weight stage: 128 rows (K_out rows valid) x 128 B
+
+struct SwParams {
+    TcParams t;
+    int nload;                                       // 32-column TMEM loads per pooled row (3*TC slots)
+    uint32_t strip_off, strip_bytes;                 // per-epilogue-warp smem strip
+    uint32_t sw_ctl_off;
+    uint32_t sw_idesc;
+};
+
+__global__ void __launch_bounds__(kSwThreads, 1)
+tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_constant__ SwParams sp,
+                        const float* __restrict__ bias, float* __restrict__ out) {
+    extern __shared__ uint8_t smem_raw[];
+    const TcParams& p = sp.t;
+    const b200_block_geom& g = p.g;
+    const int KO = g.K;                                       // output channels (<= 128)
+    const int slots = 128 * p.nacc;                           // GEMM N = pixel slots
+
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
+    const uint32_t w_off = kSwStages * kAStageBytes;          // pixel stages first, then weight stages
+    const uint32_t full_bar = base + sp.sw_ctl_off;           // [2]
+    const uint32_t empty_bar = full_bar + 16;                 // [2]
+    const uint32_t tfull_bar = full_bar + 32;                 // [2] accumulator ready
+    const uint32_t tempty_bar = full_bar + 48;                // [2] accumulator drained
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + sp.sw_ctl_off + 64);
+    const float** rowtab = reinterpret_cast<const float**>(gbase + sp.sw_ctl_off + 80);
+    float* s_bias = reinterpret_cast<float*>(gbase + sp.sw_ctl_off + 80 + kRowTab * 8);
+    float* patch = reinterpret_cast<float*>(gbase + p.patch_off);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kSwStages; ++s) {
+            mbar_init(full_bar + 8 * s, kProducerWarps + 1);
+            mbar_init(empty_bar + 8 * s, 1);
+            mbar_init(tfull_bar + 8 * s, 1);
+            mbar_init(tempty_bar + 8 * s, 4);
+        }
+        fence_mbar_init();
+    }
+    for (int i = threadIdx.x; i < 128; i += kSwThreads) s_bias[i] = i < KO ? bias[i] : 0.f;
+    if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_slot), 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int tiles_per_img = p.tiles_r * p.tiles_c;
+
+    if (warp < kProducerWarps) {
+        // ============================ producers: patch staging + im2col (B operand) ==========
+        const int tid = threadIdx.x;
+        const int j = tid & 7, m_base = tid >> 3;
+        const uint32_t row_sw = (uint32_t)(m_base & 7);
+        const uint32_t dst0 = (uint32_t)(m_base >> 3) * 1024u + row_sw * 128u + (((uint32_t)j ^ row_sw) << 4);
+        const int IRT = (p.TR - 1) * g.S + g.F;
+        int pij[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int m = m_base + 32 * i;
+            const int pi = m / p.TC;
+            pij[i] = m < p.TR * p.TC ? (pi << 16) | (m - pi * p.TC) : -1;
+        }
+        int stage = 0;
+        uint32_t phase = 0;
+        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
+            const int n = (int)(w / tiles_per_img);
+            const int rem = (int)(w - (long long)n * tiles_per_img);
+            const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
+            const int cr0 = 2 * (g.p0 + tr_i * p.PR), cc0 = 2 * (tc_i * p.PC);
+            const int ir0 = cr0 * g.S - g.P;
+            if (p.any_flag) {
+                if (tid == 0)
+                    for (int s = 0; s < g.nseg; ++s)
+                        if (g.seg[s].flag && ir0 < g.seg[s].hi && ir0 + IRT > g.seg[s].lo)
+                            wait_flag_ge(g.seg[s].flag + n, g.seg[s].target * (g.epoch ? *g.epoch : 1),
+                                         g.status, g.timeout_ns);
+            }
+            int rsel[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int pi = pij[i] >> 16, pj = pij[i] & 0xFFFF;
+                const bool ok = pij[i] >= 0 && (cr0 + pi) < g.Hc && (cc0 + pj) < g.Wc;
+                rsel[i] = ok ? pi * g.S * p.patch_pitch + pj * g.S * g.C : 0;
+            }
+            bar_producers();                                   // previous tile's im2col is finished
+            if (tid < p.patch_rows) {
+                const int h = ir0 + tid;
+                rowtab[tid] = (h >= 0 && h < g.H) ? seg_row_ptr(g, n, h) : nullptr;
+            }
+            bar_producers();
+            {
+                const int cf0 = (cc0 * g.S - g.P) * g.C, WC = g.W * g.C;
+                const uint32_t patch_s = smem_u32(patch);
+                for (int f = tid; f < p.patch_pitch; f += kProducerThreads) {
+                    const int cf = cf0 + f;
+                    const bool cv = cf >= 0 && cf < WC;
+                    uint32_t dst = patch_s + (uint32_t)f * 4u;
+                    for (int r = 0; r < p.patch_rows; ++r, dst += (uint32_t)p.patch_pitch * 4u) {
+                        const float* rp = rowtab[r];
+                        cp_async4(dst, rp + cf, (cv && rp != nullptr) ? 4u : 0u);
+                    }
+                }
+                cp_async_wait_all();
+                bar_producers();
+            }
+            int pfy = (4 * j) / p.FCpad, pt = (4 * j) - pfy * p.FCpad;
+            for (int kb = 0; kb < p.nkb; ++kb) {
+                mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+                const uint32_t a_dst = base + stage * kAStageBytes + dst0;
+                const float* src = patch + pfy * p.patch_pitch + pt;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    if (i >= 4 * p.nacc) break;                 // nacc == 1: only 128 pixel slots
+                    const float4 v = *reinterpret_cast<const float4*>(src + rsel[i]);
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a_dst + i * 4096u),
+                                 "f"(to_tf32(v.x)), "f"(to_tf32(v.y)), "f"(to_tf32(v.z)), "f"(to_tf32(v.w))
+                                 : "memory");
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(full_bar + 8 * stage);
+                pt += kBlockK;
+                while (pt >= p.FCpad) { pt -= p.FCpad; ++pfy; }
+                if (++stage == kSwStages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == kMmaWarp) {
+        // ======================================= MMA issuer ==============================
+        int stage = 0, buf = 0;
+        uint32_t phase = 0, bphase = 0;
+        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
+            mbar_wait(tempty_bar + 8 * buf, bphase ^ 1);        // epilogue has drained this accumulator
+            tc_fence_after();
+            for (int kb = 0; kb < p.nkb; ++kb) {
+                mbar_wait(full_bar + 8 * stage, phase);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint64_t dpix = make_smem_desc(base + stage * kAStageBytes);
+                    const uint64_t dwgt = make_smem_desc(base + w_off + stage * kSwWStageBytes);
+#pragma unroll
+                    for (int ks = 0; ks < kBlockK / 8; ++ks)
+                        umma_tf32(tmem_base + (uint32_t)(buf * 256), dwgt + 2 * ks, dpix + 2 * ks, sp.sw_idesc,
+                                  (kb | ks) != 0 ? 1u : 0u);
+                    umma_commit(empty_bar + 8 * stage);
+                    if (kb == p.nkb - 1) umma_commit(tfull_bar + 8 * buf);
+                }
+                __syncwarp();
+                if (++stage == kSwStages) { stage = 0; phase ^= 1; }
+            }
+            if (++buf == 2) { buf = 0; bphase ^= 1; }
+        }
+    } else if (warp == kTmaWarp) {
+        // ======================================= TMA issuer (weights) ====================
+        int stage = 0;
+        uint32_t phase = 0;
+        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
+            for (int kb = 0; kb < p.nkb; ++kb) {
+                mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+                if (lane == 0) {
+                    const uint32_t fb = full_bar + 8 * stage;
+                    mbar_arrive_expect_tx(fb, (uint32_t)(KO * 128));
+                    tma_load_2d(base + w_off + stage * kSwWStageBytes, &tmapW, kb * kBlockK, 0, fb);
+                }
+                __syncwarp();
+                if (++stage == kSwStages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else {
+        // ======================================= epilogue warps ==========================
+        const int q = warp & 3;                                // a warp can only touch TMEM lane quarter warp%4;
+                                                               // quarter q == channels 32q..32q+31
+        const bool live = q * 32 < KO;
+        const int ch = q * 32 + lane;
+        float* strip = reinterpret_cast<float*>(gbase + sp.strip_off + q * sp.strip_bytes);
+        const float bch = s_bias[ch];
+        int buf = 0;
+        uint32_t bphase = 0;
+        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
+            const int n = (int)(w / tiles_per_img);
+            const int rem = (int)(w - (long long)n * tiles_per_img);
+            const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
+            const int pr0 = g.p0 + tr_i * p.PR, pc0 = tc_i * p.PC;
+            mbar_wait(tfull_bar + 8 * buf, bphase);
+            tc_fence_after();
+            if (live) {
+                for (int pr = 0; pr < p.PR; ++pr) {
+                    // conv rows 2pr..2pr+2 = slots [col0, col0 + 3*TC); load whole 32-column groups
+                    const int col0 = 2 * pr * p.TC;
+                    int start = col0;
+                    if (start + 32 * sp.nload > slots) start = slots - 32 * sp.nload;
+                    const int shift = col0 - start;
+                    for (int l = 0; l < sp.nload; ++l) {
+                        uint32_t r[32];
+                        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * 256 + start + 32 * l), r);
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) strip[(32 * l + i) * kCbufPitch + lane] = __uint_as_float(r[i]);
+                    }
+                    __syncwarp();
+                    const int prg = pr0 + pr;
+                    for (int pc = 0; pc < p.PC; ++pc) {
+                        const float* c0p = strip + (shift + 2 * pc) * kCbufPitch + lane;
+                        float mx = -INFINITY;
+#pragma unroll
+                        for (int a = 0; a < 3; ++a)
+#pragma unroll
+                            for (int b = 0; b < 3; ++b) mx = fmaxf(mx, c0p[(a * p.TC + b) * kCbufPitch]);
+                        float val = fmaxf(mx + bch, 0.f);
+                        if (p.round_out) val = to_tf32(val);
+                        const int pcg = pc0 + pc;
+                        if (prg < g.p1 && prg < g.Hp && pcg < g.Wp && ch < KO)
+                            out[(((size_t)n * g.out_slab + (prg - g.out_base)) * g.Wp + pcg) * KO + ch] = val;
+                    }
+                    __syncwarp();
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar + 8 * buf);
+            if (g.n_signal > 0) {                              // all four warps' stores, then one signal
+                asm volatile("bar.sync 2, 128;" ::: "memory");
+                if (q == 0 && lane == 0) {
+                    __threadfence_system();
+                    for (int i = 0; i < g.n_signal; ++i) red_release_sys_add(g.signal[i] + n, 1);
+                }
+            }
+            if (++buf == 2) { buf = 0; bphase ^= 1; }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kMmaWarp) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
 // --------------------------------------------------------------------------- host ----
 struct TcConv {
     int K, C, F, Kpad, device, patch_mode, FCpad;
@@ -678,6 +932,31 @@ int fill_params(const b200_block_geom* g, TcParams* p, int flags) {
     return B200_OK;
 }
 
+// swapped kernel: layout [pixel stages | weight stages | patch | 4 epilogue strips | ctl]
+int fill_swapped(const b200_block_geom* g, SwParams* sp, int flags) {
+    int rc = fill_params(g, &sp->t, flags);
+    if (rc != B200_OK) return rc;
+    TcParams& p = sp->t;
+    if (!is_patch_mode(g->C) || g->K > 128 || g->lrn.N_lrn > 0) return B200_ERR_UNSUPPORTED;
+    sp->nload = cdiv(3 * p.TC, 32);
+    if (32 * sp->nload > 128 * p.nacc) return B200_ERR_UNSUPPORTED;
+    const size_t stages = (size_t)kSwStages * (kAStageBytes + kSwWStageBytes);
+    const size_t patch_bytes = (size_t)p.patch_rows * p.patch_pitch * 4;
+    p.patch_off = (uint32_t)stages;
+    sp->strip_off = (uint32_t)((stages + patch_bytes + 15) & ~(size_t)15);
+    sp->strip_bytes = (uint32_t)(32 * sp->nload * kCbufPitch * 4);
+    sp->sw_ctl_off = (uint32_t)((sp->strip_off + 4 * (size_t)sp->strip_bytes + 15) & ~(size_t)15);
+    // D = channels x pixels: M = 128 (K_out rows padded), N = pixel slots
+    sp->sw_idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)((128 * p.nacc) >> 3) << 17) | ((128u >> 4) << 24);
+    const size_t total = 1024 + sp->sw_ctl_off + 80 + kRowTab * 8 + 128 * 4 + 64;
+    if (total > 227 * 1024) return B200_ERR_UNSUPPORTED;
+    return B200_OK;
+}
+
+size_t smem_bytes_swapped(const SwParams& sp) {
+    return 1024 + (size_t)sp.sw_ctl_off + 80 + kRowTab * 8 + 128 * 4 + 64;
+}
+
 size_t smem_bytes(const TcParams& p) {
     return 1024 + (size_t)p.ctl_off + 16 * p.stages + 32 + kRowTab * 8 + kMaxPooled * 8 +
            (size_t)p.g.K * 4 + 64;
@@ -753,13 +1032,26 @@ extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const 
         return B200_ERR_ARG;
     if (g->K != t->K || g->C != t->C || g->F != t->F) return B200_ERR_ARG;
     if (g->p1 <= g->p0 || g->N <= 0) return B200_OK;
+    static int sms = 0;
+    if (!sms) B200_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, t->device));
+    if (t->patch_mode && g->K <= 128 && g->lrn.N_lrn == 0 && !getenv("B200_TC_NO_SWAP")) {
+        SwParams sp;
+        memset(&sp, 0, sizeof(sp));
+        if (fill_swapped(g, &sp, flags) == B200_OK) {       // else fall through to the generic kernel
+            const size_t smem = smem_bytes_swapped(sp);
+            B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_swapped_kernel,
+                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            const unsigned grid = (unsigned)(sp.t.total_tiles < sms ? sp.t.total_tiles : sms);
+            tc_block_swapped_kernel<<<grid, kSwThreads, smem, (cudaStream_t)stream>>>(t->tmap, sp, bias, out);
+            B200_CUDA_TRY(cudaGetLastError());
+            return B200_OK;
+        }
+    }
     TcParams p;
     int rc = fill_params(g, &p, flags);
     if (rc != B200_OK) return rc;
     const size_t smem = smem_bytes(p);
     if (smem > 227 * 1024) return B200_ERR_UNSUPPORTED;
-    static int sms = 0;
-    if (!sms) B200_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, t->device));
     const unsigned grid = (unsigned)(p.total_tiles < sms ? p.total_tiles : sms);
     if (t->patch_mode) {
         B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_kernel<true>,
