@@ -375,14 +375,15 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                     if (kPatch) { __syncwarp(); if (lane == 0) mbar_arrive(fb); } else mbar_arrive(fb);
                 } else if (kPatch) {
                     const float* src = patch + pfy * p.patch_pitch + pt;
+                    float4 v[8];
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const float4 v = *reinterpret_cast<const float4*>(src + rsel[i]);
+                    for (int i = 0; i < 8; ++i) v[i] = *reinterpret_cast<const float4*>(src + rsel[i]);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
                         asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a_dst + i * 4096u),
-                                     "f"(to_tf32(v.x)), "f"(to_tf32(v.y)), "f"(to_tf32(v.z)),
-                                     "f"(to_tf32(v.w))
+                                     "f"(to_tf32(v[i].x)), "f"(to_tf32(v[i].y)), "f"(to_tf32(v[i].z)),
+                                     "f"(to_tf32(v[i].w))
                                      : "memory");
-                    }
                     fence_proxy_async_smem();                  // generic stores -> async proxy (UMMA)
                     __syncwarp();
                     if (lane == 0) mbar_arrive(fb);            // one arrival per warp (256 would serialise)
@@ -682,12 +683,15 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                 mbar_wait(empty_bar + 8 * stage, phase ^ 1);
                 const uint32_t a_dst = base + stage * kAStageBytes + dst0;
                 const float* src = patch + pfy * p.patch_pitch + pt;
+                float4 v[8];                                    // all loads first: the stores are asm
+#pragma unroll                                                  // volatile and would fence each load
+                for (int i = 0; i < 8; ++i) v[i] = *reinterpret_cast<const float4*>(src + rsel[i]);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     if (i >= 4 * p.nacc) break;                 // nacc == 1: only 128 pixel slots
-                    const float4 v = *reinterpret_cast<const float4*>(src + rsel[i]);
                     asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a_dst + i * 4096u),
-                                 "f"(to_tf32(v.x)), "f"(to_tf32(v.y)), "f"(to_tf32(v.z)), "f"(to_tf32(v.w))
+                                 "f"(to_tf32(v[i].x)), "f"(to_tf32(v[i].y)), "f"(to_tf32(v[i].z)),
+                                 "f"(to_tf32(v[i].w))
                                  : "memory");
                 }
                 fence_proxy_async_smem();
