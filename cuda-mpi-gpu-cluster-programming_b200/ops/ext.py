@@ -1,0 +1,94 @@
+"""ctypes bindings for the full-AlexNet extension kernels (csrc/cuda/tc_gemm.cu, ext_ops.cu)."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import cuda as cu
+from ._ctypes import fptr
+
+_bound = False
+
+RELU, ROUND_TF32, ACCUMULATE, BIAS = 1, 2, 4, 8
+
+
+def _lib():
+    global _bound
+    L = cu.lib()
+    if not _bound:
+        L.b200_tc_gemm_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.b200_tc_gemm_destroy.argtypes = [C.c_void_p]
+        L.b200_tc_gemm.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                   C.c_int, C.c_void_p]
+        L.b200_im2col_nhwc.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 7 + [C.c_void_p]
+        L.b200_maxpool_nhwc.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 6 + [C.c_void_p]
+        L.b200_bias_act.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.b200_softmax_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        _bound = True
+    return L
+
+
+class TcLinear:
+    """Device-resident weights [N,K] (nn.Linear layout) for b200_tc_gemm."""
+
+    def __init__(self, w_nk: torch.Tensor, device):
+        w = w_nk.detach().cpu().contiguous().float()
+        self.N, self.K = w.shape
+        self.device = torch.device(device)
+        h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            cu.cu_check(_lib().b200_tc_gemm_create(fptr(w), self.N, self.K, C.byref(h)), "tc_gemm_create")
+        self._h = h
+
+    def run(self, a_ptr: int, lda: int, M: int, c_ptr: int, ldc: int, bias: Optional[torch.Tensor] = None,
+            flags: int = 0) -> None:
+        if bias is not None:
+            flags |= BIAS
+        cu.cu_check(_lib().b200_tc_gemm(self._h, C.c_void_p(a_ptr), lda, M,
+                                        fptr(bias) if bias is not None else None, C.c_void_p(c_ptr), ldc,
+                                        flags, cu.current_stream_ptr()), "tc_gemm")
+
+    def __call__(self, a: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
+                 round_out: bool = False) -> torch.Tensor:
+        assert a.dim() == 2 and a.shape[1] == self.K and a.is_contiguous()
+        out = torch.empty((a.shape[0], self.N), dtype=torch.float32, device=a.device)
+        self.run(a.data_ptr(), self.K, a.shape[0], out.data_ptr(), self.N, bias,
+                 (RELU if relu else 0) | (ROUND_TF32 if round_out else 0))
+        return out
+
+    def __del__(self):
+        try:
+            if self._h:
+                _lib().b200_tc_gemm_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+def im2col(x: torch.Tensor, F: int, S: int, P: int) -> torch.Tensor:
+    N, H, W, Cc = x.shape
+    Ho, Wo = (H - F + 2 * P) // S + 1, (W - F + 2 * P) // S + 1
+    col = torch.empty((N * Ho * Wo, F * F * Cc), dtype=torch.float32, device=x.device)
+    cu.cu_check(_lib().b200_im2col_nhwc(fptr(x), fptr(col), N, H, W, Cc, F, S, P, cu.current_stream_ptr()), "im2col")
+    return col
+
+
+def maxpool(x: torch.Tensor, F: int = 3, S: int = 2) -> torch.Tensor:
+    N, H, W, Cc = x.shape
+    out = torch.empty((N, (H - F) // S + 1, (W - F) // S + 1, Cc), dtype=torch.float32, device=x.device)
+    cu.cu_check(_lib().b200_maxpool_nhwc(fptr(x), fptr(out), N, H, W, Cc, F, S, cu.current_stream_ptr()), "maxpool")
+    return out
+
+
+def bias_act_(x_ptr: int, bias: Optional[torch.Tensor], rows: int, cols: int, ld: int, relu: bool) -> None:
+    cu.cu_check(_lib().b200_bias_act(C.c_void_p(x_ptr), fptr(bias) if bias is not None else None, rows, cols, ld,
+                                     1 if relu else 0, cu.current_stream_ptr()), "bias_act")
+
+
+def softmax(x: torch.Tensor) -> torch.Tensor:
+    y = torch.empty_like(x)
+    cu.cu_check(_lib().b200_softmax_rows(fptr(x), fptr(y), x.shape[0], x.shape[1], x.shape[1],
+                                         cu.current_stream_ptr()), "softmax")
+    return y

@@ -1,0 +1,90 @@
+"""Full AlexNet forward (extension; BASELINE.json config 5), one process per GPU.
+
+    mpirun -np N python -m b200cnn.runners.full --batch 256
+
+Blocks 1-2 run row-decomposed across the N GPUs with the fused peer-memory kernels (exactly as V4/V5);
+rank 0 then runs Conv3-5 + Pool5 (13x13 activations: too small to split), and FC6-8 run
+tensor-parallel over all N GPUs through peer memory (models/alexnet_full.py: TPClassifier).
+Prints V4-style lines; the "values" are the first 10 class probabilities of image 0."""
+from __future__ import annotations
+
+import sys
+import time
+
+import torch
+
+from ..config import INIT_RAND, LRN_V1, config_from_args
+from ..models.alexnet_full import ConvGemm, TPClassifier, make_full_weights
+from ..models.init import make_problem
+from ..models.session import Session
+from ..ops import ext
+from ..ops.cpu import fnv1a64
+from ..parallel import dist as bdist
+from ..utils import logfmt as L
+from .common import make_parser, fail
+
+
+def main(argv=None) -> int:
+    ap = make_parser("full_alexnet", init_default=INIT_RAND, lrn_default=LRN_V1)
+    ns = ap.parse_args(argv)
+    cfg = config_from_args(ns, seed_default=1)
+    if not torch.cuda.is_available():
+        fail(bdist.env_rank_world()[0], "CUDA no CUDA-capable device is detected")
+    if bdist.env_rank_world()[1] > torch.cuda.device_count():
+        fail(bdist.env_rank_world()[0], "the full-network runner needs one GPU per rank")
+    ctx = bdist.init()
+    x, w12 = make_problem(cfg)
+    sess = Session(cfg, w12, dist=ctx if ctx.world > 1 else None, device=ctx.device, precision=cfg.precision,
+                   strategy=ns.strategy, scatter="sharded")
+    sh = sess.engine.sh
+    feat = ((sh.Hp2 - 3) // 2 + 1) * ((sh.Wp2 - 3) // 2 + 1) * 256
+    w = make_full_weights(w12, seed=cfg.seed, feat=feat)
+    tp = TPClassifier(w, sess.symm, ctx.rank, ctx.world, cfg.batch, feat)
+    sess.symm.commit()
+    convs = [ConvGemm(w.w3, w.b3, ctx.device, 1), ConvGemm(w.w4, w.b4, ctx.device, 1),
+             ConvGemm(w.w5, w.b5, ctx.device, 1)] if ctx.rank == 0 else None
+    lo, hi = sess.input_rows
+    xin = x[:, lo:hi].contiguous().pin_memory() if hi > lo else None
+
+    def step():
+        e = sess.engine
+        if xin is not None:
+            e.input_view(0).copy_(xin, non_blocking=True)
+        y = e.forward_enqueue(0, 0)
+        if ctx.rank == 0:
+            for c in convs:
+                y = c(y)
+            tp.x5_view().copy_(ext.maxpool(y, 3, 2).reshape(cfg.batch, -1))
+        return tp.forward()
+
+    ctx.barrier()
+    t0 = time.perf_counter()
+    probs = step()
+    torch.cuda.synchronize(ctx.device)
+    ctx.barrier()
+    ms = (time.perf_counter() - t0) * 1e3
+    kv = {}
+    if ns.iters > 0:
+        torch.cuda.synchronize(ctx.device); ctx.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(ns.iters):
+            probs = step()
+        e1.record(); e1.synchronize()
+        dms = ctx.max_float(e0.elapsed_time(e1) / ns.iters)
+        kv = dict(device_forward_ms_warm=dms, images_per_s_warm=cfg.batch / (dms / 1e3))
+    sess.engine.check_status()
+    if ctx.rank == 0:
+        p = probs.cpu()
+        for line in L.v4_shape_values(cfg.batch, 1, 1000, p.reshape(-1)[:10].tolist()):
+            L.emit(line)
+        L.emit(L.v4_time(ms, "Full (spatial conv + TP FC)"))
+        for line in L.extras(fnv=fnv1a64(p), wall_ms=ms, np=ctx.world, batch=cfg.batch,
+                             prob_row_sum=float(p[0].sum()), argmax0=int(p[0].argmax()), **kv):
+            L.emit(line)
+    ctx.finalize()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -174,6 +174,21 @@ int b200_conv_nchw_noalloc(const float* in_nchw, const float* w_kcff, const floa
  * (ref homeworks/hw1/src/template.c:132,141) become loads/stores inside the kernel. */
 int b200_dgemm_rows(const double* A, const double* B, double* C, int rows, int n, void* stream);
 
+/* ---- full-AlexNet extension (no counterpart in the reference beyond its plans,
+ * ref final_project/PROBLEMS.txt:188-190, summary.md:37-43) ------------------------------------- */
+/* tcgen05 TF32 GEMM: C[M][N] (+)= act(A[M][K] * W[N][K]^T + bias).  W is given on the host in
+ * nn.Linear layout [N][K] (K % 32 == 0) and kept on the device TF32-rounded.  A and C may be peer
+ * pointers (all-gather fused into the loader, reduce fused into the epilogue).
+ * flags: 1 ReLU, 2 round outputs to TF32, 4 accumulate with red.add, 8 add bias. */
+int b200_tc_gemm_create(const float* w_nk, int N, int K, void** handle);
+int b200_tc_gemm_destroy(void* handle);
+int b200_tc_gemm(void* handle, const float* A, int lda, int M, const float* bias, float* C, int ldc,
+                 int flags, void* stream);
+int b200_im2col_nhwc(const float* in, float* col, int N, int H, int W, int C, int F, int S, int P, void* stream);
+int b200_maxpool_nhwc(const float* in, float* out, int N, int H, int W, int C, int F, int S, void* stream);
+int b200_bias_act(float* x, const float* bias, long long rows, int cols, int ld, int relu, void* stream);
+int b200_softmax_rows(const float* x, float* y, int rows, int cols, int ld, void* stream);
+
 /* Symmetric (peer-mapped) memory: zeroed cudaMalloc + CUDA IPC handles (64 bytes) exchanged by
  * the caller (torch.distributed); replaces MPI host buffers. */
 int b200_symm_alloc(size_t bytes, void** ptr);

@@ -1,0 +1,62 @@
+"""Full-AlexNet extension: tcgen05 GEMM, conv3-5 via im2col, tensor-parallel FC6-8 over peer memory
+(single-GPU emulation of the TP protocol here; the real multi-GPU run is in test_multigpu.py)."""
+import pytest
+import torch
+
+from b200cnn import default_config
+from b200cnn.config import INIT_RAND
+from b200cnn.models.init import make_problem
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    return ((a - b).abs().max() / b.abs().max()).item()
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 4096, 512), (300, 1000, 1024), (77, 125, 96), (128, 128, 32)])
+def test_tc_gemm_matches_torch(M, N, K):
+    from b200cnn.ops import ext
+    g = torch.Generator().manual_seed(3)
+    a = torch.randn((M, K), generator=g)
+    w = torch.randn((N, K), generator=g) * 0.05
+    b = torch.randn(N, generator=g)
+    lin = ext.TcLinear(w, "cuda:0")
+    ref = torch.relu(a @ w.t() + b)
+    out = lin(a.cuda(), b.cuda(), relu=True).cpu()
+    assert _rel(out, ref) < 4e-3
+    # accumulate mode (the reduce-scatter epilogue): C += A W^T twice on top of ones
+    c = torch.ones((M, N), device="cuda")
+    for _ in range(2):
+        lin.run(a.cuda().data_ptr(), K, M, c.data_ptr(), N, None, ext.ACCUMULATE)
+    torch.cuda.synchronize()
+    assert _rel(c.cpu(), 1 + 2 * (a @ w.t())) < 4e-3
+
+
+def test_im2col_pool_softmax_helpers():
+    from b200cnn.ops import ext
+    g = torch.Generator().manual_seed(4)
+    x = torch.randn((2, 13, 13, 8), generator=g)
+    col = ext.im2col(x.cuda(), 3, 1, 1).cpu().view(2, 13, 13, 3, 3, 8)
+    xp = torch.nn.functional.pad(x, (0, 0, 1, 1, 1, 1))
+    assert torch.equal(col[1, 4, 7], xp[1, 4:7, 7:10])
+    p = ext.maxpool(x.cuda(), 3, 2).cpu()
+    ref = torch.nn.functional.max_pool2d(x.permute(0, 3, 1, 2), 3, 2).permute(0, 2, 3, 1)
+    assert torch.equal(p, ref)
+    z = torch.randn((5, 1000), generator=g)
+    assert torch.allclose(ext.softmax(z.cuda()).cpu(), torch.softmax(z, 1), atol=1e-6)
+
+
+@pytest.mark.parametrize("tp_world", [1, 4, 8])
+def test_full_alexnet_matches_torch(tp_world):
+    from b200cnn.models.alexnet_full import FullAlexNet, make_full_weights, forward_torch_reference_full
+    cfg = default_config(batch=3, init=INIT_RAND, seed=2, precision="tf32")
+    x, w12 = make_problem(cfg)
+    w = make_full_weights(w12, seed=5)
+    ref = forward_torch_reference_full(x, w, cfg)
+    net = FullAlexNet(cfg, w, "cuda:0", tp_world=tp_world)
+    p = net.forward(x.cuda()).cpu()
+    assert p.shape == (3, 1000)
+    assert torch.allclose(p.sum(1), torch.ones(3), atol=1e-4)
+    assert (p - ref).abs().max().item() < 2e-3 * ref.max().item() + 1e-6
+    assert torch.equal(p.argmax(1), ref.argmax(1))

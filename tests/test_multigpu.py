@@ -37,3 +37,20 @@ def test_all_gpus_equal_np1():
     f1, _, _ = _run(1, "v4")
     fn, _, out = _run(n, "v4")
     assert f1 == fn, out
+
+
+def test_full_network_tp_np2_equals_np1():
+    """Full AlexNet: spatial blocks 1-2 + tensor-parallel FC over real peer memory."""
+    outs = []
+    for np_ in (1, 2):
+        cmd = [sys.executable, os.path.join(ROOT, "bin", "mpirun"), "--oversubscribe", "-np", str(np_),
+               sys.executable, "-m", "b200cnn.runners.full", "--batch", "4", "--seed", "3"]
+        p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, PYTHONPATH=ROOT),
+                           cwd=ROOT)
+        assert p.returncode == 0, p.stdout + p.stderr
+        vals = re.search(r"^Final Output \(first 10 values\): (.*)$", p.stdout, re.M).group(1).split()
+        am = re.search(r"argmax0=(\d+)", p.stdout).group(1)
+        outs.append(([float(v) for v in vals], am))
+    assert outs[0][1] == outs[1][1]
+    for a, b in zip(outs[0][0], outs[1][0]):
+        assert abs(a - b) <= 2e-3 * max(abs(a), 1e-6) + 1e-7      # atomic-add order differs across np
