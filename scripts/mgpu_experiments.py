@@ -10,7 +10,8 @@ from b200cnn.parallel import dist as bdist
 
 ctx = bdist.init()
 B = int(os.environ.get("BATCH", "128"))
-cfg = default_config(batch=B, init=INIT_RAND, seed=1, precision="tf32")
+HW = int(os.environ.get("HW", "227"))
+cfg = default_config(H=HW, W=HW, batch=B, init=INIT_RAND, seed=1, precision="tf32")
 x, w = make_problem(cfg)
 
 
@@ -25,7 +26,7 @@ def timeit(fn, n=10, sync_all=True):
     return e0.elapsed_time(e1) / n * 1e3
 
 
-for scatter in ("p2p", "sharded"):
+for scatter in os.environ.get("SCATTERS", "p2p,sharded").split(","):
     for strategy in ("halo", "recompute"):
         sess = Session(cfg, w, dist=ctx if ctx.world > 1 else None, device=ctx.device,
                        scatter=scatter, strategy=strategy)
@@ -43,7 +44,7 @@ for scatter in ("p2p", "sharded"):
         rows = ctx.all_gather_object((ctx.rank, round(t_fwd, 1), round(t_b1, 1), round(t_b2, 1), round(t_bar, 1),
                                       e.rp.out_rows, e.rp.pool1_own, e.rp.in_rows))
         if ctx.is_root:
-            print(f"--- world={ctx.world} scatter={scatter} strategy={strategy} batch={B}", flush=True)
+            print(f"--- world={ctx.world} scatter={scatter} strategy={strategy} batch={B} input={HW}x{HW}", flush=True)
             for r in rows:
                 print(f"  rank {r[0]}: forward {r[1]} us  block1 {r[2]} us  block2 {r[3]} us  barrier {r[4]} us  "
                       f"out{r[5]} pool1{r[6]} in{r[7]}", flush=True)
