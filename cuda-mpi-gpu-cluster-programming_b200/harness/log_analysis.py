@@ -207,6 +207,18 @@ class Warehouse:
         return n
 
 
+def loc_vs_perf(wh: "Warehouse") -> pd.DataFrame:
+    src = wh.df("SELECT relpath, loc, cuda_kernel_cnt FROM source_stats")
+    if src.empty:
+        return pd.DataFrame(columns=["version", "loc", "kernels", "best_s"])
+    src["version"] = src.relpath.map(lambda r: canonical_version_name(r) if re.search(r"v\d|serial|cuda|mpi", r.lower()) else None)
+    loc = src.dropna(subset=["version"]).groupby("version").agg(loc=("loc", "sum"), kernels=("cuda_kernel_cnt", "sum")).reset_index()
+    best = wh.df("SELECT version, MIN(total_time_s) AS best_s FROM perf_runs GROUP BY version")
+    best["version"] = best.version.map(canonical_version_name)
+    best = best.groupby("version").best_s.min().reset_index()
+    return loc.merge(best, on="version", how="outer").sort_values("version")
+
+
 def time_from_log(text: str) -> Optional[float]:
     """Seconds from a run log using the full pattern ladder (ref analysis.md:311-322)."""
     for pat, scale in TIME_PATTERNS:
@@ -273,6 +285,8 @@ def main(argv=None) -> int:
     sub.add_parser("stats")
     a = sub.add_parser("speedup"); a.add_argument("--stat", choices=["best", "median"], default="best")
     a = sub.add_parser("scorecard")
+    sub.add_parser("locperf")
+    a = sub.add_parser("legacy-graphs"); a.add_argument("csv"); a.add_argument("--outdir", default=str(PLOTS_DIR))
     a = sub.add_parser("plot"); a.add_argument("plots", nargs="+", choices=["speedup", "efficiency"])
     a.add_argument("--outdir", default=str(PLOTS_DIR))
     a = sub.add_parser("export"); a.add_argument("view"); a.add_argument("outfile")
@@ -298,6 +312,21 @@ def main(argv=None) -> int:
         st = wh.run_stats()
         sp = wh.speedup("median")[["version", "np", "S", "E"]]
         print(st.merge(sp, on=["version", "np"], how="left").sort_values(["version", "np"]).to_string(index=False))
+    elif ns.cmd == "locperf":
+        # lines of code per version directory vs its best time (ref analysis.md "LOC vs performance")
+        print(loc_vs_perf(wh).to_string(index=False))
+    elif ns.cmd == "legacy-graphs":
+        # ref final_project/old_logs/generate_graphs.py: bar chart of time per (version, np) from a
+        # run_summary_*.csv in any accepted schema
+        nd = normalise_summary(pd.read_csv(ns.csv))
+        if nd.empty:
+            print("unrecognised CSV schema", file=sys.stderr)
+            return 1
+        g = nd.groupby(["version", "np"])["total_time_s"].min().reset_index()
+        out = Path(ns.outdir); out.mkdir(parents=True, exist_ok=True)
+        svg_bars(out / "legacy_times.svg", [f"{_label(v)} np={int(n)}" for v, n in zip(g.version, g.np)],
+                 list(g.total_time_s), "Best time per version / np", "seconds", ymax=max(g.total_time_s) * 1.1)
+        print(f"plot -> {out}/legacy_times.svg")
     elif ns.cmd == "plot":
         out = Path(ns.outdir); out.mkdir(parents=True, exist_ok=True)
         sp = wh.speedup("best")

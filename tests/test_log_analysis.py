@@ -76,3 +76,32 @@ def test_canonical_names_and_time_ladder():
     assert la.canonical_version_name("V5 MPI+CUDA-Aware") == "V5 MPI+CUDA-Aware"
     assert la.time_from_log("Execution Time: 286.9 ms") == pytest.approx(0.2869)
     assert la.time_from_log("pid=0: Total PARALLEL time: 1.5 seconds.") == pytest.approx(1.5)
+
+
+def test_locperf_and_legacy_graphs(tmp_path):
+    root = _make_tree(tmp_path)
+    (tmp_path / "final_project").mkdir(exist_ok=True)
+    v3 = tmp_path / "final_project" / "v3_cuda_only"
+    v3.mkdir()
+    (v3 / "layers_cuda.cu").write_text("__global__ void a(){}\n__global__ void b(){}\n")
+    db = str(tmp_path / "w2.sqlite")
+    cli = [sys.executable, os.path.join(ROOT, "log_analysis.py"), "--db", db]
+    assert subprocess.run(cli + ["ingest", "--root", str(root)], capture_output=True).returncode == 0
+    out = subprocess.run(cli + ["locperf"], capture_output=True, text=True)
+    assert out.returncode == 0 and "V3 CUDA" in out.stdout
+    r = subprocess.run(cli + ["legacy-graphs", str(tmp_path / "legacy.csv"), "--outdir", str(tmp_path / "lg")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0 and (tmp_path / "lg" / "legacy_times.svg").exists()
+
+
+def test_v1_python_runner_equals_native_binary(tmp_path):
+    """Same seed -> same FNV digest from the Python V1 runner and the native V1 `template`."""
+    import re
+    vdir = os.path.join(ROOT, "final_project", "v1_serial")
+    assert subprocess.run(["make"], cwd=vdir, capture_output=True).returncode == 0
+    nat = subprocess.run(["./template", "--seed", "77"], cwd=vdir, capture_output=True, text=True).stdout
+    py = subprocess.run([sys.executable, "-m", "b200cnn.runners.v1", "--seed", "77"], cwd=ROOT, capture_output=True,
+                        text=True, env=dict(os.environ, PYTHONPATH=ROOT)).stdout
+    f = lambda t: re.search(r"Output FNV1a64: (0x[0-9a-f]+)", t).group(1)
+    assert f(nat) == f(py)
+    assert nat.splitlines()[0] == py.splitlines()[0] == "--- AlexNet Serial CPU Version (V1) ---"
