@@ -67,6 +67,29 @@ __global__ void softmax_rows(const float* __restrict__ x, float* __restrict__ y,
     for (int c = lane; c < cols; c += 32) y[(size_t)row * cols + c] = __expf(xr[c] - m) * inv;
 }
 
+// Space-to-depth by S of an NHWC row slab: out[n][Y][X][(dy*S+dx)*C + c] = in[n][S*Y+dy][S*X+dx][c],
+// zeros outside the image or the slab.  Turns a stride-S FxF convolution (conv1: 11x11/4 on 3
+// channels) into a stride-1 ceil(F/S)^2 convolution on S*S*C channels whose im2col rows are aligned
+// 16 B chunks of the tensor itself, which the tcgen05 loader can cp.async without staging.
+__global__ void space_to_depth(const float* __restrict__ in, float* __restrict__ out, int N, int H, int W, int C,
+                               int S, int in_base, int in_slab, int y0, int ys, int Ws) {
+    const int Cs = S * S * C;
+    const size_t total = (size_t)N * ys * Ws * Cs;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int cs = (int)(i % Cs); size_t t = i / Cs;
+        const int X = (int)(t % Ws); t /= Ws;
+        const int Yl = (int)(t % ys); const int n = (int)(t / ys);
+        const int c = cs % C, d = cs / C, dx = d % S, dy = d / S;
+        const int h = S * (y0 + Yl) + dy, w = S * X + dx;
+        float v = 0.f;
+        if (h < H && w < W && h >= in_base && h < in_base + in_slab)
+            v = in[(((size_t)n * in_slab + (h - in_base)) * W + w) * C + c];
+        uint32_t u;                                   // feeds a TF32 tensor-core operand: round once here
+        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
+        out[i] = __uint_as_float(u);
+    }
+}
+
 inline unsigned nblocks(size_t n) {
     size_t b = (n + 255) / 256;
     return (unsigned)(b > 148 * 16 ? 148 * 16 : (b ? b : 1));
@@ -104,6 +127,17 @@ extern "C" int b200_bias_act(float* x, const float* bias, long long rows, int co
 extern "C" int b200_softmax_rows(const float* x, float* y, int rows, int cols, int ld, void* stream) {
     if (!x || !y || rows <= 0 || cols <= 0 || ld < cols) return B200_ERR_ARG;
     softmax_rows<<<(rows + 7) / 8, 256, 0, (cudaStream_t)stream>>>(x, y, rows, cols, ld);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+extern "C" int b200_space_to_depth(const float* in, float* out, int N, int H, int W, int C, int S, int in_base,
+                                   int in_slab, int y0, int ys, void* stream) {
+    if (!in || !out || N <= 0 || S <= 0 || ys < 0) return B200_ERR_ARG;
+    if (ys == 0) return B200_OK;
+    const int Ws = (W + S - 1) / S;
+    space_to_depth<<<nblocks((size_t)N * ys * Ws * S * S * C), 256, 0, (cudaStream_t)stream>>>(
+        in, out, N, H, W, C, S, in_base, in_slab, y0, ys, Ws);
     B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;
 }

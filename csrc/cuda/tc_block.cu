@@ -440,7 +440,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
 //     barrier anywhere in the epilogue.
 constexpr int kSwThreads = 448;
 constexpr int kSwEpiWarp0 = 10;
-constexpr int kSwStages = 2;
+constexpr int kSwMaxStages = 4;
 constexpr int kSwWStageBytes = 128 * 128;            // weight stage: 128 rows (K_out rows valid) x 128 B
 
 struct SwParams {
@@ -449,6 +449,9 @@ struct SwParams {
     uint32_t strip_off, strip_bytes;                 // per-epilogue-warp smem strip
     uint32_t sw_ctl_off;
     uint32_t sw_idesc;
+    int direct;                                      // 1: B rows are cp.async'd straight from global memory
+    int nstages;                                     // 2 (patch) or 3 (direct)
+    int cpr;                                         // direct: 16 B chunks per filter row run (F*C/4)
 };
 
 __global__ void __launch_bounds__(kSwThreads, 1)
@@ -462,23 +465,26 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
 
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
-    const uint32_t w_off = kSwStages * kAStageBytes;          // pixel stages first, then weight stages
-    const uint32_t full_bar = base + sp.sw_ctl_off;           // [2]
-    const uint32_t empty_bar = full_bar + 16;                 // [2]
-    const uint32_t tfull_bar = full_bar + 32;                 // [2] accumulator ready
-    const uint32_t tempty_bar = full_bar + 48;                // [2] accumulator drained
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + sp.sw_ctl_off + 64);
-    const float** rowtab = reinterpret_cast<const float**>(gbase + sp.sw_ctl_off + 80);
-    float* s_bias = reinterpret_cast<float*>(gbase + sp.sw_ctl_off + 80 + kRowTab * 8);
+    const int NS = sp.nstages;
+    const uint32_t w_off = NS * kAStageBytes;                 // pixel stages first, then weight stages
+    const uint32_t full_bar = base + sp.sw_ctl_off;           // [4]
+    const uint32_t empty_bar = full_bar + 32;                 // [4]
+    const uint32_t tfull_bar = full_bar + 64;                 // [2] accumulator ready
+    const uint32_t tempty_bar = full_bar + 80;                // [2] accumulator drained
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + sp.sw_ctl_off + 96);
+    const float** rowtab = reinterpret_cast<const float**>(gbase + sp.sw_ctl_off + 112);
+    float* s_bias = reinterpret_cast<float*>(gbase + sp.sw_ctl_off + 112 + kRowTab * 8);
     float* patch = reinterpret_cast<float*>(gbase + p.patch_off);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kSwStages; ++s) {
-            mbar_init(full_bar + 8 * s, kProducerWarps + 1);
+        for (int s = 0; s < NS; ++s) {
+            mbar_init(full_bar + 8 * s, (sp.direct ? kProducerThreads : kProducerWarps) + 1);
             mbar_init(empty_bar + 8 * s, 1);
-            mbar_init(tfull_bar + 8 * s, 1);
-            mbar_init(tempty_bar + 8 * s, 4);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(tfull_bar + 8 * b, 1);
+            mbar_init(tempty_bar + 8 * b, 4);
         }
         fence_mbar_init();
     }
@@ -526,7 +532,42 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                 const bool ok = pij[i] >= 0 && (cr0 + pi) < g.Hc && (cc0 + pj) < g.Wc;
                 rsel[i] = ok ? pi * g.S * p.patch_pitch + pj * g.S * g.C : 0;
             }
-            bar_producers();                                   // previous tile's im2col is finished
+            bar_producers();                                   // previous tile's loads/im2col are issued
+            if (sp.direct) {
+                // ---- direct mode: rows of B are 16 B chunks of the activation itself ----
+                if (tid < IRT) {
+                    const int h = ir0 + tid;
+                    rowtab[tid] = (h >= 0 && h < g.H) ? seg_row_ptr(g, n, h) : nullptr;
+                }
+                bar_producers();
+                int hsel[8], xb[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int pi = pij[i] >> 16, pj = pij[i] & 0xFFFF;
+                    const bool ok = pij[i] >= 0 && (cr0 + pi) < g.Hc && (cc0 + pj) < g.Wc;
+                    hsel[i] = ok ? pi * g.S : -1;
+                    xb[i] = ((cc0 + pj) * g.S - g.P) * g.C * 4;
+                }
+                int fy = 0, ch = j;                             // this thread's chunk: run fy, chunk ch in run
+                while (ch >= sp.cpr) { ch -= sp.cpr; ++fy; }
+                for (int kb = 0; kb < p.nkb; ++kb) {
+                    mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+                    const uint32_t a_dst = base + stage * kAStageBytes + dst0;
+                    const bool kv = fy < g.F;                   // beyond F*F*C: zero columns of the K padding
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        if (i >= 4 * p.nacc) break;
+                        const char* rp = (kv && hsel[i] >= 0) ? reinterpret_cast<const char*>(rowtab[hsel[i] + fy])
+                                                              : nullptr;
+                        cp_async16(a_dst + i * 4096u, rp + (xb[i] + ch * 16), rp ? 16u : 0u);
+                    }
+                    cp_async_mbar_arrive_noinc(full_bar + 8 * stage);
+                    ch += 8;
+                    while (ch >= sp.cpr) { ch -= sp.cpr; ++fy; }
+                    if (++stage == NS) { stage = 0; phase ^= 1; }
+                }
+                continue;
+            }
             if (tid < p.patch_rows) {
                 const int h = ir0 + tid;
                 rowtab[tid] = (h >= 0 && h < g.H) ? seg_row_ptr(g, n, h) : nullptr;
@@ -568,7 +609,7 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                 if (lane == 0) mbar_arrive(full_bar + 8 * stage);
                 pt += kBlockK;
                 while (pt >= p.FCpad) { pt -= p.FCpad; ++pfy; }
-                if (++stage == kSwStages) { stage = 0; phase ^= 1; }
+                if (++stage == NS) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == kMmaWarp) {
@@ -592,7 +633,7 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                     if (kb == p.nkb - 1) umma_commit(tfull_bar + 8 * buf);
                 }
                 __syncwarp();
-                if (++stage == kSwStages) { stage = 0; phase ^= 1; }
+                if (++stage == NS) { stage = 0; phase ^= 1; }
             }
             if (++buf == 2) { buf = 0; bphase ^= 1; }
         }
@@ -609,7 +650,7 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                     tma_load_2d(base + w_off + stage * kSwWStageBytes, &tmapW, kb * kBlockK, 0, fb);
                 }
                 __syncwarp();
-                if (++stage == kSwStages) { stage = 0; phase ^= 1; }
+                if (++stage == NS) { stage = 0; phase ^= 1; }
             }
         }
     } else {
@@ -731,9 +772,15 @@ constexpr int kMaxPatchBytes = 64 * 1024;
 // 148 persistent CTAs, so 1.7 waves cost 2.  Deterministic: peers call it to predict tile counts.
 constexpr int kPlanSms = 148;
 
+// small-K_out layers whose B rows can be cp.async'd straight from the activation (see SwParams::direct)
+inline bool direct_eligible(const b200_block_geom* g) {
+    return is_patch_mode(g->C) && g->K <= 128 && g->lrn.N_lrn == 0 && g->P == 0 && g->C % 4 == 0 &&
+           (g->F * g->C) % 4 == 0 && (g->W * g->C) % 4 == 0 && !getenv("B200_TC_NO_DIRECT");
+}
+
 bool plan_tiles(const b200_block_geom* g, TcParams* p) {
     const int rows = g->p1 - g->p0;
-    const bool patch = is_patch_mode(g->C);
+    const bool patch = is_patch_mode(g->C) && !direct_eligible(g);
     const int nkb = num_kblocks(g->F, g->C);
     const double mma_kb = 4.0 * (128.0 * g->K / 256.0) * 1.3;         // cycles per k-block per accumulator
     const double prod_kb = patch ? 450.0 : 0.0;                       // smem->smem im2col bound (conv1)
@@ -813,21 +860,26 @@ int fill_swapped(const b200_block_geom* g, SwParams* sp, int flags) {
     if (!is_patch_mode(g->C) || g->K > 128 || g->lrn.N_lrn > 0) return B200_ERR_UNSUPPORTED;
     sp->nload = cdiv(3 * p.TC, 32);
     if (32 * sp->nload > 128 * p.nacc) return B200_ERR_UNSUPPORTED;
-    const size_t stages = (size_t)kSwStages * (kAStageBytes + kSwWStageBytes);
-    const size_t patch_bytes = (size_t)p.patch_rows * p.patch_pitch * 4;
+    // direct mode: every 16 B chunk of a B row is an aligned piece of the activation (no padding, channel
+    // and row sizes multiples of 4 floats): cp.async from global, no smem patch, no smem->smem im2col
+    sp->direct = (direct_eligible(g) && (p.TR - 1) * g->S + g->F <= kRowTab) ? 1 : 0;
+    sp->cpr = g->F * g->C / 4;
+    sp->nstages = sp->direct ? 3 : 2;
+    const size_t stages = (size_t)sp->nstages * (kAStageBytes + kSwWStageBytes);
+    const size_t patch_bytes = sp->direct ? 0 : (size_t)p.patch_rows * p.patch_pitch * 4;
     p.patch_off = (uint32_t)stages;
     sp->strip_off = (uint32_t)((stages + patch_bytes + 15) & ~(size_t)15);
     sp->strip_bytes = (uint32_t)(32 * sp->nload * kCbufPitch * 4);
     sp->sw_ctl_off = (uint32_t)((sp->strip_off + 4 * (size_t)sp->strip_bytes + 15) & ~(size_t)15);
     // D = channels x pixels: M = 128 (K_out rows padded), N = pixel slots
     sp->sw_idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)((128 * p.nacc) >> 3) << 17) | ((128u >> 4) << 24);
-    const size_t total = 1024 + sp->sw_ctl_off + 80 + kRowTab * 8 + 128 * 4 + 64;
+    const size_t total = 1024 + sp->sw_ctl_off + 112 + kRowTab * 8 + 128 * 4 + 64;
     if (total > 227 * 1024) return B200_ERR_UNSUPPORTED;
     return B200_OK;
 }
 
 size_t smem_bytes_swapped(const SwParams& sp) {
-    return 1024 + (size_t)sp.sw_ctl_off + 80 + kRowTab * 8 + 128 * 4 + 64;
+    return 1024 + (size_t)sp.sw_ctl_off + 112 + kRowTab * 8 + 128 * 4 + 64;
 }
 
 size_t smem_bytes(const TcParams& p) {

@@ -88,6 +88,7 @@ class Blocks12Engine:
         self.sh = self.plan.shapes
         self.epoch = 0
         self.launches = 0            # kernels launched by this engine (bench reports it)
+        self.s2d = False
         # device_epoch: flag targets are derived on the device from a forward counter, so launch
         # arguments never change and a whole forward can be replayed as one CUDA graph.  The
         # single-GPU emulation of several ranks launches barrier halves separately and keeps the
@@ -107,8 +108,15 @@ class Blocks12Engine:
                 self.w1p = cu.pack_weights_ffck(weights.w1).to(self.device)
                 self.w2p = cu.pack_weights_ffck(weights.w2).to(self.device)
             elif self.precision == "tf32":
-                from ..ops import tc
-                self.tc1 = tc.TcConv(weights.w1, self.device)
+                import os
+                from ..ops import tc, ext
+                p1 = cfg.conv1
+                # stride-S conv1 on C=3 -> stride-1 conv on the space-to-depth tensor (S*S*C channels):
+                # its im2col rows are aligned 16 B pieces of the tensor, which the loader cp.async's
+                # straight into the MMA stage (no shared-memory patch, no smem->smem expansion).
+                self.s2d = (p1.S > 1 and p1.P == 0 and (p1.S * p1.S * cfg.C) % 4 == 0
+                            and not os.environ.get("B200_NO_S2D"))
+                self.tc1 = tc.TcConv(ext.s2d_weights(weights.w1, p1.S) if self.s2d else weights.w1, self.device)
                 self.tc2 = tc.TcConv(weights.w2, self.device)
             else:
                 raise ValueError(self.precision)
@@ -125,6 +133,18 @@ class Blocks12Engine:
         self.in_rows = in_rows
         self.in_bytes = N * in_rows * sh.W * sh.C * f4
         self.buf_in = [symm.alloc(f"in{i}", self.in_bytes) for i in range(self.n_in_buf)]
+        if self.s2d:
+            S1 = cfg.conv1.S
+            self.s2d_ws = -(-sh.W // S1)
+            self.s2d_hs = -(-sh.H // S1)
+            self.s2d_c = S1 * S1 * sh.C
+            if in_rows > 0:
+                self.s2d_y0 = self.in_base // S1
+                self.s2d_ys = -(-(self.in_base + in_rows) // S1) - self.s2d_y0
+            else:
+                self.s2d_y0, self.s2d_ys = 0, 0
+            self.buf_s2d = [symm.alloc(f"s2d{i}", N * self.s2d_ys * self.s2d_ws * self.s2d_c * f4)
+                            for i in range(self.n_in_buf)]
         own = rp.pool1_own[1] - rp.pool1_own[0]
         self.buf_pool1 = symm.alloc("pool1", N * own * sh.Wp1 * sh.K1 * f4)
         out_rows = sh.Hp2 if rank == 0 else 0
@@ -166,19 +186,28 @@ class Blocks12Engine:
     def _geom_block1(self, r: int, probe: bool = False, in_idx: int = 0):
         cfg, sh, p1 = self.cfg, self.sh, self.cfg.conv1
         rp = self.plan.ranks[r]
+        s2d = self.s2d
+        S1 = p1.S
+        Hin = self.s2d_hs if s2d else sh.H
         if probe:
-            segs = [dict(ptr=1, base=0, slab=sh.H, lo=0, hi=sh.H)]
+            segs = [dict(ptr=1, base=0, slab=Hin, lo=0, hi=Hin)]
             signals, out_ptr = [], 0
         else:
             if self.scatter == "p2p":
-                segs = [dict(ptr=self.symm.ptr(0, f"in{in_idx}"), base=0, slab=sh.H, lo=0, hi=sh.H)]
+                name = f"s2d{in_idx}" if s2d else f"in{in_idx}"
+                segs = [dict(ptr=self.symm.ptr(0, name), base=0, slab=Hin, lo=0, hi=Hin)]
+            elif s2d:
+                segs = [dict(ptr=self.buf_s2d[in_idx].ptr, base=self.s2d_y0, slab=self.s2d_ys,
+                             lo=self.s2d_y0, hi=self.s2d_y0 + self.s2d_ys)]
             else:
                 segs = [dict(ptr=self.buf_in[in_idx].ptr, base=self.in_base, slab=self.in_rows,
                              lo=rp.in_rows[0], hi=rp.in_rows[1])]
             signals = [self._flag_ptr(peer, self.lay.arr_off + r * self.lay.nmax)
                        for peer in sorted({p for p, _, _ in rp.serves})]
+        conv = dict(H=Hin, W=self.s2d_ws, Cin=self.s2d_c, F=-(-p1.F // S1), S=1, P=0) if s2d else \
+            dict(H=sh.H, W=sh.W, Cin=sh.C, F=p1.F, S=p1.S, P=p1.P)
         g = cu.make_block_geom(
-            N=cfg.batch, H=sh.H, W=sh.W, Cin=sh.C, K=p1.K, F=p1.F, S=p1.S, P=p1.P,
+            N=cfg.batch, K=p1.K, **conv,
             Hc=sh.Hc1, Wc=sh.Wc1, Hp=sh.Hp1, Wp=sh.Wp1, rows=rp.pool1_own,
             out_base=rp.pool1_own[0], out_slab=rp.pool1_own[1] - rp.pool1_own[0], lrn=None,
             segs=segs, signals=signals,
@@ -245,6 +274,16 @@ class Blocks12Engine:
                                 [self._flag_ptr(self.rank, self.lay.sync_off + r) for r in W],
                                 [self._sync_epoch] * self.world,
                                 self._flag_ptr(self.rank, self.lay.status_off), self.timeout_ns, 0)
+
+    def stage_s2d(self, in_idx: int = 0) -> None:
+        """Space-to-depth of this rank's input slab (rank 0's whole batch in p2p-scatter mode).  Runs
+        before the opening barrier, so peers only ever read a finished tensor."""
+        if self.s2d and self.in_rows > 0:
+            from ..ops import ext
+            sh = self.sh
+            ext.space_to_depth_(self.buf_in[in_idx].ptr, self.buf_s2d[in_idx].ptr, self.cfg.batch, sh.H, sh.W,
+                                sh.C, self.cfg.conv1.S, self.in_base, self.in_rows, self.s2d_y0, self.s2d_ys)
+            self.launches += 1
 
     def stage_block1(self, in_idx: int = 0) -> None:
         rp = self.rp
@@ -317,6 +356,7 @@ class Blocks12Engine:
 
     def _enqueue_stages(self, in_idx: int, out_idx: int) -> None:
         self.stage_begin()
+        self.stage_s2d(in_idx)
         self.stage_barrier()
         self.stage_block1(in_idx)
         self.stage_block2(out_idx)
@@ -381,6 +421,7 @@ class EmulatedWorld:
         self.load_input(x)
         E = self.engines
         for e in E: e.stage_begin()
+        for e in E: e.stage_s2d(0)
         for e in E: e.stage_barrier_signal()
         for e in E: e.stage_barrier_wait()
         for e in E: e.stage_block1(0)

@@ -26,6 +26,7 @@ def _lib():
         L.b200_maxpool_nhwc.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 6 + [C.c_void_p]
         L.b200_bias_act.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.b200_softmax_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.b200_space_to_depth.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 9 + [C.c_void_p]
         _bound = True
     return L
 
@@ -92,3 +93,21 @@ def softmax(x: torch.Tensor) -> torch.Tensor:
     cu.cu_check(_lib().b200_softmax_rows(fptr(x), fptr(y), x.shape[0], x.shape[1], x.shape[1],
                                          cu.current_stream_ptr()), "softmax")
     return y
+
+
+def space_to_depth_(in_ptr: int, out_ptr: int, N: int, H: int, W: int, Cc: int, S: int, in_base: int,
+                    in_slab: int, y0: int, ys: int) -> None:
+    cu.cu_check(_lib().b200_space_to_depth(C.c_void_p(in_ptr), C.c_void_p(out_ptr), N, H, W, Cc, S, in_base,
+                                           in_slab, y0, ys, cu.current_stream_ptr()), "space_to_depth")
+
+
+def s2d_weights(w: torch.Tensor, S: int) -> torch.Tensor:
+    """[K,C,F,F] stride-S filter -> [K, S*S*C, Ft, Ft] stride-1 filter on the space-to-depth tensor
+    (Ft = ceil(F/S); taps that fall outside the original FxF window are zero)."""
+    K, Cc, F, _ = w.shape
+    Ft = (F + S - 1) // S
+    wp = torch.zeros((K, Cc, Ft * S, Ft * S), dtype=w.dtype)
+    wp[:, :, :F, :F] = w
+    # wp[k][c][ty*S+dy][tx*S+dx] -> out[k][(dy*S+dx)*C + c][ty][tx]
+    wp = wp.view(K, Cc, Ft, S, Ft, S).permute(0, 3, 5, 1, 2, 4).reshape(K, S * S * Cc, Ft, Ft)
+    return wp.contiguous()
