@@ -73,20 +73,64 @@ __global__ void softmax_rows(const float* __restrict__ x, float* __restrict__ y,
 // 16 B chunks of the tensor itself, which the tcgen05 loader can cp.async without staging.
 __global__ void space_to_depth(const float* __restrict__ in, float* __restrict__ out, int N, int H, int W, int C,
                                int S, int in_base, int in_slab, int y0, int ys, int Ws) {
-    const int Cs = S * S * C;
-    const size_t total = (size_t)N * ys * Ws * Cs;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-        const int cs = (int)(i % Cs); size_t t = i / Cs;
-        const int X = (int)(t % Ws); t /= Ws;
-        const int Yl = (int)(t % ys); const int n = (int)(t / ys);
-        const int c = cs % C, d = cs / C, dx = d % S, dy = d / S;
-        const int h = S * (y0 + Yl) + dy, w = S * X + dx;
-        float v = 0.f;
-        if (h < H && w < W && h >= in_base && h < in_base + in_slab)
-            v = in[(((size_t)n * in_slab + (h - in_base)) * W + w) * C + c];
-        uint32_t u;                                   // feeds a TF32 tensor-core operand: round once here
-        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
-        out[i] = __uint_as_float(u);
+    // One block per (image, s2d row): the S input rows are read coalesced into shared memory, then the
+    // s2d row (Ws pixels x S*S*C floats, contiguous) is written coalesced — whole 128 B lines both ways.
+    extern __shared__ float tile[];                               // [S][rowf]
+    const int SC = S * C, Cs = S * SC, rowf = Ws * SC, WC = W * C;
+    const int nrows = N * ys;
+    for (int row = blockIdx.x; row < nrows; row += gridDim.x) {
+        const int Yl = row % ys, n = row / ys;
+        for (int i = threadIdx.x; i < S * rowf; i += blockDim.x) {
+            const int dy = i / rowf, f = i - dy * rowf;
+            const int h = S * (y0 + Yl) + dy;
+            float v = 0.f;
+            if (h < H && h >= in_base && h < in_base + in_slab && f < WC)
+                v = in[((size_t)n * in_slab + (h - in_base)) * WC + f];
+            uint32_t u;                               // feeds a TF32 tensor-core operand: round once here
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
+            tile[i] = __uint_as_float(u);
+        }
+        __syncthreads();
+        float* dst = out + (size_t)row * Ws * Cs;
+        for (int o = threadIdx.x; o < Ws * Cs; o += blockDim.x) {
+            const int X = o / Cs, cs = o - X * Cs;
+            const int dy = cs / SC, r = cs - dy * SC;
+            dst[o] = tile[dy * rowf + X * SC + r];
+        }
+        __syncthreads();
+    }
+}
+
+// Fast path with compile-time S and C (conv1: S=4, C=3): constant divisions, 128-bit smem reads and
+// global writes, one block per (image, s2d row).
+template <int S, int C>
+__global__ void __launch_bounds__(256)
+space_to_depth_fixed(const float* __restrict__ in, float* __restrict__ out, int H, int W, int in_base, int in_slab,
+                     int y0, int ys, int Ws) {
+    constexpr int SC = S * C, Cs = S * SC;
+    static_assert(SC % 4 == 0, "a dy-run must be whole float4s");
+    extern __shared__ __align__(16) float tile[];                 // [S][rowf]
+    const int rowf = Ws * SC, WC = W * C;
+    const int row = blockIdx.x, Yl = row % ys, n = row / ys;
+#pragma unroll
+    for (int dy = 0; dy < S; ++dy) {
+        const int h = S * (y0 + Yl) + dy;
+        const bool rv = h < H && h >= in_base && h < in_base + in_slab;
+        const float* src = in + ((size_t)n * in_slab + (rv ? h - in_base : 0)) * WC;
+        for (int f = threadIdx.x; f < rowf; f += 256) {
+            const float v = (rv && f < WC) ? __ldg(src + f) : 0.f;
+            uint32_t u;
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
+            tile[dy * rowf + f] = __uint_as_float(u);
+        }
+    }
+    __syncthreads();
+    float4* dst = reinterpret_cast<float4*>(out + (size_t)row * Ws * Cs);
+    constexpr int Q = Cs / 4, QR = SC / 4;                        // float4 per pixel / per dy-run
+    for (int o = threadIdx.x; o < Ws * Q; o += 256) {
+        const int X = o / Q, q = o - X * Q;
+        const int dy = q / QR, r4 = q - dy * QR;
+        dst[o] = *reinterpret_cast<const float4*>(tile + dy * rowf + X * SC + r4 * 4);
     }
 }
 
@@ -136,7 +180,17 @@ extern "C" int b200_space_to_depth(const float* in, float* out, int N, int H, in
     if (!in || !out || N <= 0 || S <= 0 || ys < 0) return B200_ERR_ARG;
     if (ys == 0) return B200_OK;
     const int Ws = (W + S - 1) / S;
-    space_to_depth<<<nblocks((size_t)N * ys * Ws * S * S * C), 256, 0, (cudaStream_t)stream>>>(
+    const int rowf = Ws * S * C, nrows = N * ys;
+    const size_t smem = (size_t)S * rowf * sizeof(float);
+    if (S == 4 && C == 3 && smem <= 48 * 1024) {
+        space_to_depth_fixed<4, 3><<<nrows, 256, smem, (cudaStream_t)stream>>>(in, out, H, W, in_base, in_slab,
+                                                                             y0, ys, Ws);
+        B200_CUDA_TRY(cudaGetLastError());
+        return B200_OK;
+    }
+    if (smem > 200 * 1024) return B200_ERR_UNSUPPORTED;
+    B200_CUDA_TRY(cudaFuncSetAttribute(space_to_depth, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    space_to_depth<<<nrows < 148 * 8 ? nrows : 148 * 8, 256, smem, (cudaStream_t)stream>>>(
         in, out, N, H, W, C, S, in_base, in_slab, y0, ys, Ws);
     B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;

@@ -68,7 +68,7 @@ simt_block_kernel(const float* __restrict__ wt,    // [F][F*C][K]
             for (int s = 0; s < g.nseg; ++s) {
                 const b200_row_seg& sg = g.seg[s];
                 if (h >= sg.lo && h < sg.hi) {
-                    src = sg.ptr + ((size_t)n * sg.slab + (h - sg.base)) * g.W * C;
+                    src = sg.ptr + ((size_t)n * sg.slab + (h - sg.base)) * (g.in_pitch ? g.in_pitch : g.W * C);
                     break;
                 }
             }

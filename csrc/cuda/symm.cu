@@ -49,6 +49,15 @@ extern "C" int b200_ipc_close(void* ptr) {
     return B200_OK;
 }
 
+extern "C" int b200_memcpy2d_h2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width,
+                                 size_t height, void* stream) {
+    if (!dst || !src) return B200_ERR_ARG;
+    if (width == 0 || height == 0) return B200_OK;
+    B200_CUDA_TRY(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, height, cudaMemcpyHostToDevice,
+                                    (cudaStream_t)stream));
+    return B200_OK;
+}
+
 extern "C" int b200_can_access_peer(int dev, int peer) {
     int ok = 0;
     if (cudaDeviceCanAccessPeer(&ok, dev, peer) != cudaSuccess) { cudaGetLastError(); return 0; }

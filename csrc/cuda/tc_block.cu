@@ -73,7 +73,7 @@ __device__ __forceinline__ const float* seg_row_ptr(const b200_block_geom& g, in
 #pragma unroll
     for (int s = 0; s < B200_MAX_SEG; ++s) {
         if (s < g.nseg && h >= g.seg[s].lo && h < g.seg[s].hi)
-            return g.seg[s].ptr + ((size_t)n * g.seg[s].slab + (h - g.seg[s].base)) * g.W * g.C;
+            return g.seg[s].ptr + ((size_t)n * g.seg[s].slab + (h - g.seg[s].base)) * (g.in_pitch ? g.in_pitch : g.W * g.C);
     }
     return nullptr;
 }
@@ -773,9 +773,14 @@ constexpr int kMaxPatchBytes = 64 * 1024;
 constexpr int kPlanSms = 148;
 
 // small-K_out layers whose B rows can be cp.async'd straight from the activation (see SwParams::direct)
+// A filter-row run = fcpad(F,C) floats starting at column x*S*C of an input row; it is made of aligned
+// 16 B chunks when S*C and the row pitch are multiples of 4 floats, and it stays inside the row when the
+// pitch covers the last pixel's run (the floats past W*C only ever meet zero weights).
 inline bool direct_eligible(const b200_block_geom* g) {
-    return is_patch_mode(g->C) && g->K <= 128 && g->lrn.N_lrn == 0 && g->P == 0 && g->C % 4 == 0 &&
-           (g->F * g->C) % 4 == 0 && (g->W * g->C) % 4 == 0 && !getenv("B200_TC_NO_DIRECT");
+    const int pitch = g->in_pitch ? g->in_pitch : g->W * g->C;
+    return is_patch_mode(g->C) && g->K <= 128 && g->lrn.N_lrn == 0 && g->P == 0 && (g->S * g->C) % 4 == 0 &&
+           pitch % 4 == 0 && pitch >= (g->Wc - 1) * g->S * g->C + fcpad(g->F, g->C) &&
+           !getenv("B200_TC_NO_DIRECT");
 }
 
 bool plan_tiles(const b200_block_geom* g, TcParams* p) {
@@ -863,7 +868,7 @@ int fill_swapped(const b200_block_geom* g, SwParams* sp, int flags) {
     // direct mode: every 16 B chunk of a B row is an aligned piece of the activation (no padding, channel
     // and row sizes multiples of 4 floats): cp.async from global, no smem patch, no smem->smem im2col
     sp->direct = (direct_eligible(g) && (p.TR - 1) * g->S + g->F <= kRowTab) ? 1 : 0;
-    sp->cpr = g->F * g->C / 4;
+    sp->cpr = fcpad(g->F, g->C) / 4;
     sp->nstages = sp->direct ? 3 : 2;
     const size_t stages = (size_t)sp->nstages * (kAStageBytes + kSwWStageBytes);
     const size_t patch_bytes = sp->direct ? 0 : (size_t)p.patch_rows * p.patch_pitch * 4;

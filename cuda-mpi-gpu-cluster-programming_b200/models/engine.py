@@ -114,8 +114,9 @@ class Blocks12Engine:
                 # stride-S conv1 on C=3 -> stride-1 conv on the space-to-depth tensor (S*S*C channels):
                 # its im2col rows are aligned 16 B pieces of the tensor, which the loader cp.async's
                 # straight into the MMA stage (no shared-memory patch, no smem->smem expansion).
+                # (kept as an option, B200_S2D=1: the pitched-row direct loader below needs no extra pass)
                 self.s2d = (p1.S > 1 and p1.P == 0 and (p1.S * p1.S * cfg.C) % 4 == 0
-                            and not os.environ.get("B200_NO_S2D"))
+                            and bool(os.environ.get("B200_S2D")))
                 self.tc1 = tc.TcConv(ext.s2d_weights(weights.w1, p1.S) if self.s2d else weights.w1, self.device)
                 self.tc2 = tc.TcConv(weights.w2, self.device)
             else:
@@ -131,8 +132,17 @@ class Blocks12Engine:
             in_rows = rp.in_rows[1] - rp.in_rows[0]
             self.in_base = rp.in_rows[0]
         self.in_rows = in_rows
-        self.in_bytes = N * in_rows * sh.W * sh.C * f4
-        self.buf_in = [symm.alloc(f"in{i}", self.in_bytes) for i in range(self.n_in_buf)]
+        # Row pitch of the resident input: padded to a multiple of 4 floats (and long enough for the last
+        # pixel's filter-row run) so conv1's loader can cp.async 16 B chunks straight from it; the H2D
+        # copy is a pitched DMA (cudaMemcpy2DAsync), so the padding costs nothing.
+        p1 = cfg.conv1
+        self.in_pitch = sh.W * sh.C
+        if self.precision == "tf32" and not self.s2d and p1.P == 0 and (p1.S * sh.C) % 4 == 0:
+            run = (p1.F * sh.C + 3) // 4 * 4
+            self.in_pitch = (max(sh.W * sh.C, (sh.Wc1 - 1) * p1.S * sh.C + run) + 3) // 4 * 4
+        self.in_bytes = N * in_rows * sh.W * sh.C * f4          # payload bytes per step (H2D accounting)
+        self.in_alloc = N * in_rows * self.in_pitch * f4 + 256
+        self.buf_in = [symm.alloc(f"in{i}", self.in_alloc) for i in range(self.n_in_buf)]
         if self.s2d:
             S1 = cfg.conv1.S
             self.s2d_ws = -(-sh.W // S1)
@@ -179,9 +189,20 @@ class Blocks12Engine:
 
     # ---- geometry ------------------------------------------------------------------------------
     def input_view(self, i: int = 0) -> torch.Tensor:
-        """This rank's input buffer ``i`` (rank 0 holds the whole batch in p2p-scatter mode)."""
+        """This rank's input buffer ``i`` as an [N, rows, W, C] view (rows are ``in_pitch`` floats apart;
+        rank 0 holds the whole batch in p2p-scatter mode)."""
         sh = self.sh
-        return self.buf_in[i].tensor((self.cfg.batch, self.in_rows, sh.W, sh.C))
+        n, rows, pitch = self.cfg.batch, self.in_rows, self.in_pitch
+        flat = self.buf_in[i].tensor((max(n * rows * pitch, 1),))
+        return flat.as_strided((n, rows, sh.W, sh.C), (rows * pitch, pitch, sh.C, 1))
+
+    def h2d(self, i: int, x_host: torch.Tensor) -> None:
+        """Pinned host [N, rows, W, C] -> input buffer ``i`` on the current stream (pitched DMA)."""
+        sh = self.sh
+        assert x_host.is_contiguous() and tuple(x_host.shape) == (self.cfg.batch, self.in_rows, sh.W, sh.C)
+        with torch.cuda.device(self.device):
+            cu.memcpy2d_h2d(self.buf_in[i].ptr, self.in_pitch * 4, x_host, sh.W * sh.C * 4, sh.W * sh.C * 4,
+                            self.cfg.batch * self.in_rows)
 
     def _geom_block1(self, r: int, probe: bool = False, in_idx: int = 0):
         cfg, sh, p1 = self.cfg, self.sh, self.cfg.conv1
@@ -205,7 +226,7 @@ class Blocks12Engine:
             signals = [self._flag_ptr(peer, self.lay.arr_off + r * self.lay.nmax)
                        for peer in sorted({p for p, _, _ in rp.serves})]
         conv = dict(H=Hin, W=self.s2d_ws, Cin=self.s2d_c, F=-(-p1.F // S1), S=1, P=0) if s2d else \
-            dict(H=sh.H, W=sh.W, Cin=sh.C, F=p1.F, S=p1.S, P=p1.P)
+            dict(H=sh.H, W=sh.W, Cin=sh.C, F=p1.F, S=p1.S, P=p1.P, in_pitch=self.in_pitch)
         g = cu.make_block_geom(
             N=cfg.batch, K=p1.K, **conv,
             Hc=sh.Hc1, Wc=sh.Wc1, Hp=sh.Hp1, Wp=sh.Wp1, rows=rp.pool1_own,
@@ -281,6 +302,7 @@ class Blocks12Engine:
         if self.s2d and self.in_rows > 0:
             from ..ops import ext
             sh = self.sh
+            assert self.in_pitch == sh.W * sh.C, "the s2d pre-pass reads an unpadded input"
             ext.space_to_depth_(self.buf_in[in_idx].ptr, self.buf_s2d[in_idx].ptr, self.cfg.batch, sh.H, sh.W,
                                 sh.C, self.cfg.conv1.S, self.in_base, self.in_rows, self.s2d_y0, self.s2d_ys)
             self.launches += 1

@@ -80,7 +80,7 @@ class Session:
                 # slot i is free once the forward that last read it has finished
                 self.s_in.wait_event(self.ev_compute[i])
                 with torch.cuda.stream(self.s_in):
-                    e.input_view(i).copy_(x_host, non_blocking=True)
+                    e.h2d(i, x_host)
                     self.ev_h2d[i].record(self.s_in)
                 self.s_compute.wait_event(self.ev_h2d[i])
             # output slot i must have been drained by its previous D2H

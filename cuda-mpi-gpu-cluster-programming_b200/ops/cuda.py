@@ -28,7 +28,7 @@ class BlockGeom(C.Structure):
     _fields_ = [(n, C.c_int) for n in (
         "N", "H", "W", "C", "K", "F", "S", "P", "Hc", "Wc", "Hp", "Wp", "p0", "p1",
         "out_base", "out_slab")] + [
-        ("lrn", LrnParams), ("nseg", C.c_int), ("n_signal", C.c_int),
+        ("lrn", LrnParams), ("nseg", C.c_int), ("n_signal", C.c_int), ("in_pitch", C.c_int),
         ("seg", RowSeg * MAX_SEG), ("signal", C.c_void_p * MAX_SIGNAL),
         ("status", C.c_void_p), ("timeout_ns", C.c_ulonglong), ("epoch", C.c_void_p)]
 
@@ -52,6 +52,8 @@ def lib():
         L.b200_ipc_close.argtypes = [C.c_void_p]
         L.b200_can_access_peer.argtypes = [C.c_int, C.c_int]
         L.b200_enable_peer.argtypes = [C.c_int]
+        L.b200_memcpy2d_h2d.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
+                                        C.c_void_p]
         L.b200_flag_signal.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_void_p]
         L.b200_flag_wait.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.c_int,
                                      C.c_void_p, C.c_ulonglong, C.c_void_p, C.c_void_p]
@@ -87,7 +89,7 @@ def make_block_geom(*, N, H, W, Cin, K, F, S, P, Hc, Wc, Hp, Wp, rows: Tuple[int
                     out_base: int, out_slab: int, lrn: Optional[LrnParams],
                     segs: Sequence[dict], signals: Sequence[int] = (),
                     status_ptr: int = 0, timeout_ns: int = DEFAULT_TIMEOUT_NS,
-                    epoch_ptr: int = 0) -> BlockGeom:
+                    epoch_ptr: int = 0, in_pitch: int = 0) -> BlockGeom:
     g = BlockGeom()
     g.N, g.H, g.W, g.C = N, H, W, Cin
     g.K, g.F, g.S, g.P = K, F, S, P
@@ -109,6 +111,7 @@ def make_block_geom(*, N, H, W, Cin, K, F, S, P, Hc, Wc, Hp, Wp, rows: Tuple[int
     g.status = status_ptr or None
     g.timeout_ns = timeout_ns
     g.epoch = epoch_ptr or None
+    g.in_pitch = in_pitch
     return g
 
 
@@ -165,3 +168,9 @@ def flag_barrier(signal_targets: Sequence[int], wait_flags: Sequence[int], wait_
     ta = (C.c_int * n)(*wait_targets)
     cu_check(lib().b200_flag_barrier(sa, fa, ta, n, C.c_void_p(status_ptr or None), timeout_ns,
                                      C.c_void_p(epoch_ptr or None), current_stream_ptr()), "flag_barrier")
+
+
+def memcpy2d_h2d(dst_ptr: int, dpitch: int, src: torch.Tensor, spitch: int, width: int, height: int) -> None:
+    """Pitched pinned-host -> device copy on the current stream (bytes)."""
+    cu_check(lib().b200_memcpy2d_h2d(C.c_void_p(dst_ptr), dpitch, C.c_void_p(src.data_ptr()), spitch, width,
+                                     height, current_stream_ptr()), "memcpy2d_h2d")

@@ -121,6 +121,8 @@ typedef struct {
     b200_lrn_params lrn;     /* N_lrn == 0 => no LRN                                      */
     int nseg;
     int n_signal;
+    int in_pitch;            /* floats between consecutive input rows of every segment; 0 => W*C.  A
+                                pitch that is a multiple of 4 lets conv1 (C=3) cp.async 16 B chunks  */
     b200_row_seg seg[B200_MAX_SEG];
     int* signal[B200_MAX_SIGNAL];   /* per-image counters (usually on peers) bumped per finished tile */
     int* status;             /* device word: first error code of the launch (0 = ok)      */
@@ -206,6 +208,9 @@ int b200_enable_peer(int peer);
 /* Stream-ordered device flag ops (MPI_Barrier / completion notification equivalents,
  * ref v4_mpi_cuda/src/main_mpi_cuda.cpp:151,154): signal = fence.sys + red.release.sys add on up
  * to 16 counters (local or peer); wait = spin until flags[i] >= target[i] with a watchdog. */
+/* pinned host -> device copy of `height` rows of `width` bytes with different pitches (cudaMemcpy2DAsync) */
+int b200_memcpy2d_h2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width, size_t height,
+                      void* stream);
 int b200_flag_signal(int* const* targets, int n, int add, void* stream);
 int b200_flag_wait(const int* const* flags, const int* target, int n, int* status,
                    unsigned long long timeout_ns, const int* epoch /* NULL or device counter: target *= *epoch */,
