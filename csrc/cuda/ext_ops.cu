@@ -134,6 +134,16 @@ space_to_depth_fixed(const float* __restrict__ in, float* __restrict__ out, int 
     }
 }
 
+// contiguous rows (width floats) -> rows at a larger pitch; coalesced both ways
+__global__ void repitch_rows(const float* __restrict__ src, float* __restrict__ dst, long long rows, int width,
+                             int dpitch) {
+    for (long long r = blockIdx.y; r < rows; r += gridDim.y) {
+        const float* s = src + r * width;
+        float* d = dst + r * dpitch;
+        for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < width; f += gridDim.x * blockDim.x) d[f] = s[f];
+    }
+}
+
 inline unsigned nblocks(size_t n) {
     size_t b = (n + 255) / 256;
     return (unsigned)(b > 148 * 16 ? 148 * 16 : (b ? b : 1));
@@ -192,6 +202,15 @@ extern "C" int b200_space_to_depth(const float* in, float* out, int N, int H, in
     B200_CUDA_TRY(cudaFuncSetAttribute(space_to_depth, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     space_to_depth<<<nrows < 148 * 8 ? nrows : 148 * 8, 256, smem, (cudaStream_t)stream>>>(
         in, out, N, H, W, C, S, in_base, in_slab, y0, ys, Ws);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+extern "C" int b200_repitch_rows(const float* src, float* dst, long long rows, int width, int dpitch, void* stream) {
+    if (!src || !dst || rows < 0 || width <= 0 || dpitch < width) return B200_ERR_ARG;
+    if (rows == 0) return B200_OK;
+    dim3 grid((width + 255) / 256, (unsigned)(rows < 65535 ? rows : 65535));
+    repitch_rows<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst, rows, width, dpitch);
     B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;
 }

@@ -26,6 +26,7 @@ def _lib():
         L.b200_maxpool_nhwc.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 6 + [C.c_void_p]
         L.b200_bias_act.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.b200_softmax_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.b200_repitch_rows.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_void_p]
         L.b200_space_to_depth.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 9 + [C.c_void_p]
         _bound = True
     return L
@@ -111,3 +112,8 @@ def s2d_weights(w: torch.Tensor, S: int) -> torch.Tensor:
     # wp[k][c][ty*S+dy][tx*S+dx] -> out[k][(dy*S+dx)*C + c][ty][tx]
     wp = wp.view(K, Cc, Ft, S, Ft, S).permute(0, 3, 5, 1, 2, 4).reshape(K, S * S * Cc, Ft, Ft)
     return wp.contiguous()
+
+
+def repitch_rows_(src_ptr: int, dst_ptr: int, rows: int, width: int, dpitch: int) -> None:
+    cu.cu_check(_lib().b200_repitch_rows(C.c_void_p(src_ptr), C.c_void_p(dst_ptr), rows, width, dpitch,
+                                         cu.current_stream_ptr()), "repitch_rows")

@@ -190,6 +190,8 @@ int b200_im2col_nhwc(const float* in, float* col, int N, int H, int W, int C, in
 int b200_maxpool_nhwc(const float* in, float* out, int N, int H, int W, int C, int F, int S, void* stream);
 int b200_bias_act(float* x, const float* bias, long long rows, int cols, int ld, int relu, void* stream);
 int b200_softmax_rows(const float* x, float* y, int rows, int cols, int ld, void* stream);
+/* contiguous rows of `width` floats -> rows `dpitch` floats apart (device to device) */
+int b200_repitch_rows(const float* src, float* dst, long long rows, int width, int dpitch, void* stream);
 /* space-to-depth by S of an NHWC row slab (rows [in_base,in_base+in_slab) of an H x W image) into s2d
  * rows [y0, y0+ys): out[n][Y-y0][X][(dy*S+dx)*C+c] = in[n][S*Y+dy][S*X+dx][c], zero outside. */
 int b200_space_to_depth(const float* in, float* out, int N, int H, int W, int C, int S, int in_base,
