@@ -88,8 +88,8 @@ def run_ours(a):
             for i in range(2):
                 e.input_view(i).copy_(x[:, lo:hi].to(dev))
         flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
-        for _ in range(a.warmup):
-            e.forward_enqueue(0, 0)
+        for i in range(max(a.warmup, 4)):          # >= 2 calls per buffer parity: both CUDA graphs are
+            e.forward_enqueue(i % 2, i % 2)        # captured here, never inside the timed region
         torch.cuda.synchronize(dev)
         ctx.barrier()
         torch.cuda.synchronize(dev)
@@ -120,7 +120,7 @@ def run_ours(a):
         hx = None
         if e.in_rows > 0:
             hx = [x[:, lo:hi].contiguous().pin_memory() for _ in range(2)]
-        for i in range(max(a.warmup, 3)):
+        for i in range(max(a.warmup, 4)):
             sess.submit(hx[i % 2] if hx else None)
         sess.drain()
         ctx.barrier()
