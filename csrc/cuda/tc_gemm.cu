@@ -35,8 +35,15 @@ struct GemmParams {
     int flags;                                                   // 1 relu, 2 round to tf32, 4 atomic add, 8 bias
     int tiles_m, tiles_n, nkb;
     uint32_t idesc;
+    // implicit-GEMM convolution (kConv): A is an NHWC activation [cN][cH][cW][cC], row m of the GEMM is
+    // output pixel m = (n*cHo + oy)*cWo + ox and k-block kb is 32 channels of filter tap (fy, fx):
+    // kb = (fy*cF + fx)*(cC/32) + chunk.  Taps outside the image are zero-filled by cp.async (size 0).
+    int cH, cW, cC, cF, cS, cP, cHo, cWo;
 };
 
+// kConv = false: A[M][lda] row-major.  kConv = true: A rows are gathered from the NHWC activation, so the
+// im2col matrix of conv3-5 never exists in memory.
+template <bool kConv>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_constant__ GemmParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -74,18 +81,48 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_constant_
         uint32_t phase = 0;
         for (long long t = blockIdx.x; t < total; t += gridDim.x) {
             const int m0 = (int)(t / p.tiles_n) * kBM;
+            // kConv: per-row pixel origin (float offset of input (n, oy*S-P, ox*S-P, 4j)) and tap validity
+            long long poff[8];
+            uint32_t ymask[8], xmask[8];
+            if (kConv) {
+                const int hw = p.cHo * p.cWo;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int m = m0 + r0 + 16 * i;
+                    const int mm = m < p.M ? m : 0;
+                    const int n = mm / hw, rem = mm - n * hw;
+                    const int oy = rem / p.cWo, ox = rem - oy * p.cWo;
+                    const int y0 = oy * p.cS - p.cP, x0 = ox * p.cS - p.cP;
+                    poff[i] = (((long long)n * p.cH + y0) * p.cW + x0) * p.cC + 4 * j;
+                    const int ylo = max(0, -y0), yhi = min(p.cF, p.cH - y0);
+                    const int xlo = max(0, -x0), xhi = min(p.cF, p.cW - x0);
+                    ymask[i] = (m < p.M && yhi > ylo) ? (((1u << yhi) - 1u) & ~((1u << ylo) - 1u)) : 0u;
+                    xmask[i] = xhi > xlo ? (((1u << xhi) - 1u) & ~((1u << xlo) - 1u)) : 0u;
+                }
+            }
+            int fy = 0, fx = 0, cch = 0;                                  // kConv: tap + channel chunk of kb
+            const int nch = kConv ? p.cC / kBK : 1;
             for (int kb = 0; kb < p.nkb; ++kb) {
                 mbar_wait(empty_bar + 8 * stage, phase ^ 1);
                 const uint32_t a_stage = base + stage * kAStage;
+                const int tap_off = kConv ? (fy * p.cW + fx) * p.cC + cch * kBK : 0;
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     const int r = r0 + 16 * i, m = m0 + r;
                     const uint32_t sw = (uint32_t)(r & 7);
                     const uint32_t dst = a_stage + (uint32_t)(r >> 3) * 1024u + sw * 128u + (((uint32_t)j ^ sw) << 4);
-                    const float* src = p.A + (size_t)(m < p.M ? m : 0) * p.lda + kb * kBK + 4 * j;
-                    cp_async16(dst, src, m < p.M ? 16u : 0u);
+                    if (kConv) {
+                        const bool v = ((ymask[i] >> fy) & (xmask[i] >> fx) & 1u) != 0u;
+                        cp_async16(dst, p.A + (v ? poff[i] + tap_off : 0), v ? 16u : 0u);
+                    } else {
+                        const float* src = p.A + (size_t)(m < p.M ? m : 0) * p.lda + kb * kBK + 4 * j;
+                        cp_async16(dst, src, m < p.M ? 16u : 0u);
+                    }
                 }
                 cp_async_mbar_arrive_noinc(full_bar + 8 * stage);
+                if (kConv) {
+                    if (++cch == nch) { cch = 0; if (++fx == p.cF) { fx = 0; ++fy; } }
+                }
                 if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
         }
@@ -266,10 +303,45 @@ extern "C" int b200_tc_gemm(void* handle, const float* A, int lda, int M, const 
     const size_t smem = 1024 + (size_t)kStages * (kAStage + kBStage) + 16 * kStages + 32 + 64;
     static int sms = 0;
     if (!sms) B200_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, t->device));
-    B200_CUDA_TRY(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200_CUDA_TRY(cudaFuncSetAttribute(tc_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long total = (long long)p.tiles_m * p.tiles_n;
     const unsigned grid = (unsigned)(total < sms ? total : sms);
-    tc_gemm_kernel<<<grid, kGemmThreads, smem, (cudaStream_t)stream>>>(t->tmap, p);
+    tc_gemm_kernel<false><<<grid, kGemmThreads, smem, (cudaStream_t)stream>>>(t->tmap, p);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+// Convolution as an implicit GEMM on the same kernel: x is NHWC [N][H][W][C] (C a multiple of 32, may be a
+// peer pointer), the handle holds weights [K_out][F*F*C] in (fy, fx, c) order, out is [N*Ho*Wo][ldc].
+// Same flags as b200_tc_gemm.  No im2col buffer is written or read.
+extern "C" int b200_tc_conv_gemm(void* handle, const float* x, int N, int H, int W, int C, int F, int S, int P,
+                                 const float* bias, float* out, int ldc, int flags, void* stream) {
+    TcGemm* t = (TcGemm*)handle;
+    if (!t || !x || !out || N < 0 || H <= 0 || W <= 0 || C <= 0 || F <= 0 || S <= 0 || P < 0) return B200_ERR_ARG;
+    if (C % kBK != 0 || F > 16) return B200_ERR_UNSUPPORTED;
+    if (t->K != F * F * C || ldc < t->N) return B200_ERR_ARG;
+    if ((flags & 8) && !bias) return B200_ERR_ARG;
+    const int Ho = (H - F + 2 * P) / S + 1, Wo = (W - F + 2 * P) / S + 1;
+    if (Ho <= 0 || Wo <= 0) return B200_ERR_ARG;
+    const long long M = (long long)N * Ho * Wo;
+    if (M == 0) return B200_OK;
+    if (M > 0x7fffffffLL - kBM) return B200_ERR_RANGE;
+    GemmParams p;
+    memset(&p, 0, sizeof(p));
+    p.A = x; p.C = out; p.bias = bias;
+    p.M = (int)M; p.N = t->N; p.K = t->K; p.lda = 0; p.ldc = ldc; p.flags = flags;
+    p.tiles_m = (int)((M + kBM - 1) / kBM);
+    p.tiles_n = (t->N + kBN - 1) / kBN;
+    p.nkb = t->K / kBK;
+    p.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kBN >> 3) << 17) | ((128u >> 4) << 24);
+    p.cH = H; p.cW = W; p.cC = C; p.cF = F; p.cS = S; p.cP = P; p.cHo = Ho; p.cWo = Wo;
+    const size_t smem = 1024 + (size_t)kStages * (kAStage + kBStage) + 16 * kStages + 32 + 64;
+    static int sms = 0;
+    if (!sms) B200_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, t->device));
+    B200_CUDA_TRY(cudaFuncSetAttribute(tc_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long long total = (long long)p.tiles_m * p.tiles_n;
+    const unsigned grid = (unsigned)(total < sms ? total : sms);
+    tc_gemm_kernel<true><<<grid, kGemmThreads, smem, (cudaStream_t)stream>>>(t->tmap, p);
     B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;
 }

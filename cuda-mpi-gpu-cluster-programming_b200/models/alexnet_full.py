@@ -5,7 +5,9 @@ The reference implements blocks 1-2 only; the rest exists there as a plan
 FC 9216 -> 4096 -> 4096 -> 1000).  Layer order keeps the reference's block structure (LRN after pool 2).
 
 * blocks 1-2: the fused tcgen05 kernels of :mod:`b200cnn.models.engine` (spatially decomposable);
-* Conv3-5: im2col + the tcgen05 GEMM (``csrc/cuda/tc_gemm.cu``), bias+ReLU in its epilogue, Pool5;
+* Conv3-5: the tcgen05 GEMM (``csrc/cuda/tc_gemm.cu``) as an implicit GEMM: its loader gathers the im2col
+  rows straight from the NHWC activation (B200_CONV_IMPLICIT=0 materialises them instead), bias+ReLU in
+  its epilogue, Pool5;
 * FC6-8: the same GEMM, tensor-parallel across ranks over peer memory (:class:`TPClassifier`):
     FC6 column-parallel, its loader pulls the features out of rank 0's buffer (all-gather fused);
     FC7 row-parallel, partial sums go straight into the owning rank's shard with red.add over NVLink
@@ -14,6 +16,7 @@ FC 9216 -> 4096 -> 4096 -> 1000).  Layer order keeps the reference's block struc
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 from typing import List, Optional
 
@@ -67,15 +70,24 @@ def forward_torch_reference_full(x: torch.Tensor, w: FullWeights, cfg: NetConfig
 
 
 class ConvGemm:
-    """3x3 (or FxF) convolution as im2col + tcgen05 GEMM with bias+ReLU in the epilogue."""
+    """3x3 (or FxF) convolution on the tcgen05 GEMM with bias+ReLU in the epilogue.  ``implicit``: the
+    GEMM's loader gathers the im2col rows straight from the NHWC activation (b200_tc_conv_gemm);
+    otherwise the col matrix is materialised first (b200_im2col_nhwc), which costs a write and a read
+    of F*F times the activation."""
 
-    def __init__(self, w_kcff: torch.Tensor, bias: torch.Tensor, device, pad: int):
+    def __init__(self, w_kcff: torch.Tensor, bias: torch.Tensor, device, pad: int,
+                 implicit: Optional[bool] = None):
         K, Cc, F, _ = w_kcff.shape
         self.K, self.C, self.F, self.P = K, Cc, F, pad
         self.lin = ext.TcLinear(w_kcff.permute(0, 2, 3, 1).reshape(K, F * F * Cc), device)
         self.bias = bias.to(device).contiguous()
+        if implicit is None:
+            implicit = os.environ.get("B200_CONV_IMPLICIT", "1") == "1"
+        self.implicit = bool(implicit) and Cc % 32 == 0
 
     def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        if self.implicit:
+            return self.lin.conv(x, self.F, 1, self.P, self.bias, relu=True, round_out=True)
         N, H, W, _ = x.shape
         col = ext.im2col(x, self.F, 1, self.P)
         Ho, Wo = H - self.F + 2 * self.P + 1, W - self.F + 2 * self.P + 1

@@ -22,6 +22,8 @@ def _lib():
         L.b200_tc_gemm_destroy.argtypes = [C.c_void_p]
         L.b200_tc_gemm.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                    C.c_int, C.c_void_p]
+        L.b200_tc_conv_gemm.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 7 + [C.c_void_p, C.c_void_p, C.c_int,
+                                                                                 C.c_int, C.c_void_p]
         L.b200_im2col_nhwc.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 7 + [C.c_void_p]
         L.b200_maxpool_nhwc.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 6 + [C.c_void_p]
         L.b200_bias_act.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_void_p]
@@ -58,6 +60,20 @@ class TcLinear:
         out = torch.empty((a.shape[0], self.N), dtype=torch.float32, device=a.device)
         self.run(a.data_ptr(), self.K, a.shape[0], out.data_ptr(), self.N, bias,
                  (RELU if relu else 0) | (ROUND_TF32 if round_out else 0))
+        return out
+
+    def conv(self, x: torch.Tensor, F: int, S: int, P: int, bias: Optional[torch.Tensor] = None,
+             relu: bool = False, round_out: bool = False) -> torch.Tensor:
+        """NHWC convolution as an implicit GEMM (weights [K_out, F*F*C] in (fy, fx, c) order): the loader
+        gathers the im2col rows itself, nothing is materialised."""
+        N, H, W, Cc = x.shape
+        assert x.is_contiguous() and F * F * Cc == self.K and Cc % 32 == 0
+        Ho, Wo = (H - F + 2 * P) // S + 1, (W - F + 2 * P) // S + 1
+        out = torch.empty((N, Ho, Wo, self.N), dtype=torch.float32, device=x.device)
+        flags = (RELU if relu else 0) | (ROUND_TF32 if round_out else 0) | (BIAS if bias is not None else 0)
+        cu.cu_check(_lib().b200_tc_conv_gemm(self._h, fptr(x), N, H, W, Cc, F, S, P,
+                                             fptr(bias) if bias is not None else None, fptr(out), self.N,
+                                             flags, cu.current_stream_ptr()), "tc_conv_gemm")
         return out
 
     def __del__(self):

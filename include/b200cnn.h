@@ -186,6 +186,11 @@ int b200_tc_gemm_create(const float* w_nk, int N, int K, void** handle);
 int b200_tc_gemm_destroy(void* handle);
 int b200_tc_gemm(void* handle, const float* A, int lda, int M, const float* bias, float* C, int ldc,
                  int flags, void* stream);
+/* Convolution as an implicit GEMM on the same kernel: x is NHWC [N][H][W][C] with C % 32 == 0 (may be a
+ * peer pointer); the handle holds [K_out][F*F*C] weights in (fy, fx, c) order; out is [N*Ho*Wo][ldc].
+ * The producer warps gather the im2col rows on the fly (zero fill outside the image); no col buffer. */
+int b200_tc_conv_gemm(void* handle, const float* x, int N, int H, int W, int C, int F, int S, int P,
+                      const float* bias, float* out, int ldc, int flags, void* stream);
 int b200_im2col_nhwc(const float* in, float* col, int N, int H, int W, int C, int F, int S, int P, void* stream);
 int b200_maxpool_nhwc(const float* in, float* out, int N, int H, int W, int C, int F, int S, void* stream);
 int b200_bias_act(float* x, const float* bias, long long rows, int cols, int ld, int relu, void* stream);

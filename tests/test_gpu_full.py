@@ -60,3 +60,38 @@ def test_full_alexnet_matches_torch(tp_world):
     assert torch.allclose(p.sum(1), torch.ones(3), atol=1e-4)
     assert (p - ref).abs().max().item() < 2e-3 * ref.max().item() + 1e-6
     assert torch.equal(p.argmax(1), ref.argmax(1))
+
+
+@pytest.mark.parametrize("N,H,W,C,K,F,S,P", [(3, 13, 13, 64, 96, 3, 1, 1), (2, 9, 11, 32, 40, 5, 2, 2),
+                                             (5, 6, 6, 128, 130, 3, 1, 0), (1, 13, 13, 384, 256, 3, 1, 1)])
+def test_tc_conv_gemm_matches_torch(N, H, W, C, K, F, S, P):
+    """Implicit-GEMM convolution (loader gathers im2col rows on the fly) vs conv2d in fp32 on the CPU."""
+    from b200cnn.ops import ext
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn((N, H, W, C), generator=g)
+    w = torch.randn((K, C, F, F), generator=g) * 0.05
+    b = torch.randn(K, generator=g)
+    lin = ext.TcLinear(w.permute(0, 2, 3, 1).reshape(K, F * F * C), "cuda:0")
+    ref = torch.relu(torch.nn.functional.conv2d(x.permute(0, 3, 1, 2), w, b, stride=S, padding=P)).permute(0, 2, 3, 1)
+    for _ in range(2):                                   # second call: stage/phase state starts clean again
+        out = lin.conv(x.cuda(), F, S, P, b.cuda(), relu=True).cpu()
+        assert out.shape == ref.shape
+        assert _rel(out, ref) < 4e-3
+    # same numbers as the materialised-im2col route (same kernel, same K order)
+    col = ext.im2col(x.cuda(), F, S, P)
+    out2 = lin(col, b.cuda(), relu=True).view(ref.shape).cpu()
+    assert torch.equal(out, out2)
+
+
+def test_full_alexnet_implicit_conv_equals_im2col(monkeypatch):
+    from b200cnn.models.alexnet_full import FullAlexNet, make_full_weights
+    cfg = default_config(batch=2, init=INIT_RAND, seed=2, precision="tf32")
+    x, w12 = make_problem(cfg)
+    w = make_full_weights(w12, seed=5)
+    monkeypatch.setenv("B200_CONV_IMPLICIT", "0")
+    p0 = FullAlexNet(cfg, w, "cuda:0").forward(x.cuda()).cpu()
+    monkeypatch.setenv("B200_CONV_IMPLICIT", "1")
+    net = FullAlexNet(cfg, w, "cuda:0")
+    assert net.c3.implicit and net.c4.implicit and net.c5.implicit
+    p1 = net.forward(x.cuda()).cpu()
+    assert torch.equal(p0, p1)
