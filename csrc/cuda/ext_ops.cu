@@ -52,6 +52,25 @@ __global__ void bias_act(float* __restrict__ x, const float* __restrict__ bias, 
     }
 }
 
+// out[r][c] = act(sum_k ws[k*stride + r*cols + c] + bias[c]), summed in k order (deterministic split-K finish)
+__global__ void splitk_reduce(const float* __restrict__ ws, int ksplit, size_t stride, size_t rows, int cols,
+                              const float* __restrict__ bias, float* __restrict__ out, int ld, int flags) {
+    const size_t total = rows * (size_t)cols;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t r = i / cols; const int c = (int)(i % cols);
+        float v = 0.f;
+        for (int k = 0; k < ksplit; ++k) v += ws[k * stride + i];
+        if (flags & 8) v += bias[c];
+        if (flags & 1) v = fmaxf(v, 0.f);
+        if (flags & 2) {
+            unsigned u;
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
+            v = __uint_as_float(u);
+        }
+        out[r * ld + c] = v;
+    }
+}
+
 // one warp per row
 __global__ void softmax_rows(const float* __restrict__ x, float* __restrict__ y, int rows, int cols, int ld) {
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
@@ -174,6 +193,19 @@ extern "C" int b200_bias_act(float* x, const float* bias, long long rows, int co
     if (!x || rows < 0 || cols <= 0 || ld < cols) return B200_ERR_ARG;
     if (rows == 0) return B200_OK;
     bias_act<<<nblocks((size_t)rows * cols), 256, 0, (cudaStream_t)stream>>>(x, bias, (size_t)rows, cols, ld, relu);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+// finish of b200_tc_gemm_splitk: ws holds ksplit partial [rows][cols] matrices `stride` floats apart.
+// flags: 1 ReLU, 2 round to TF32, 8 add bias (same bits as b200_tc_gemm).
+extern "C" int b200_splitk_reduce(const float* ws, int ksplit, long long stride, long long rows, int cols,
+                                  const float* bias, float* out, int ld, int flags, void* stream) {
+    if (!ws || !out || ksplit < 1 || rows < 0 || cols <= 0 || ld < cols || stride < rows * cols) return B200_ERR_ARG;
+    if ((flags & 8) && !bias) return B200_ERR_ARG;
+    if (rows == 0) return B200_OK;
+    splitk_reduce<<<nblocks((size_t)rows * cols), 256, 0, (cudaStream_t)stream>>>(ws, ksplit, (size_t)stride,
+                                                                               (size_t)rows, cols, bias, out, ld, flags);
     B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;
 }

@@ -137,18 +137,25 @@ class TPClassifier:
 
     # -- phases (a real rank runs them back to back with barriers; the emulation interleaves ranks) --
     def phase_zero(self) -> None:
-        self.buf_y7.tensor((self.B, self.hs)).zero_()
+        if self.world > 1:
+            self.buf_y7.tensor((self.B, self.hs)).zero_()
 
     def phase_fc6(self) -> None:         # all-gather fused: A is rank 0's feature buffer
         self.fc6.run(self.symm.ptr(0, "tp_x5"), self.feat, self.B, self.buf_y6.ptr, self.hs, self.b6,
                      ext.RELU | ext.ROUND_TF32)
 
     def phase_fc7(self) -> None:         # reduce-scatter fused: red.add into the owner's shard
+        if self.world == 1:              # nothing to reduce: bias + ReLU in the GEMM epilogue
+            self.fc7[0].run(self.buf_y6.ptr, self.hs, self.B, self.buf_y7.ptr, self.hs, self.b7,
+                            ext.RELU | ext.ROUND_TF32)
+            return
         for s in range(self.world):
             self.fc7[s].run(self.buf_y6.ptr, self.hs, self.B, self.symm.ptr(s, "tp_y7"), self.hs, None,
                             ext.ACCUMULATE)
 
     def phase_fc7_finish(self) -> None:
+        if self.world == 1:
+            return
         ext.bias_act_(self.buf_y7.ptr, self.b7, self.B, self.hs, self.hs, relu=True)
 
     def phase_fc8(self) -> None:         # pulls every peer's shard; writes its logits columns on rank 0

@@ -2,6 +2,7 @@
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import torch
@@ -22,6 +23,11 @@ def _lib():
         L.b200_tc_gemm_destroy.argtypes = [C.c_void_p]
         L.b200_tc_gemm.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
                                    C.c_int, C.c_void_p]
+        L.b200_tc_gemm_splitk.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int,
+                                          C.c_int, C.c_int, C.c_longlong, C.c_void_p]
+        L.b200_splitk_reduce.argtypes = [C.c_void_p, C.c_int, C.c_longlong, C.c_longlong, C.c_int, C.c_void_p,
+                                         C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.b200_tc_gemm_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.b200_tc_conv_gemm.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 7 + [C.c_void_p, C.c_void_p, C.c_int,
                                                                                  C.c_int, C.c_void_p]
         L.b200_im2col_nhwc.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 7 + [C.c_void_p]
@@ -45,11 +51,38 @@ class TcLinear:
         with torch.cuda.device(self.device):
             cu.cu_check(_lib().b200_tc_gemm_create(fptr(w), self.N, self.K, C.byref(h)), "tc_gemm_create")
         self._h = h
+        nkb, bn = C.c_int(), C.c_int()
+        cu.cu_check(_lib().b200_tc_gemm_info(h, C.byref(nkb), C.byref(bn)), "tc_gemm_info")
+        self.nkb, self.bn = nkb.value, bn.value
+        self._sms = torch.cuda.get_device_properties(self.device).multi_processor_count
+        self._ws: Optional[torch.Tensor] = None
+
+    def splitk_for(self, M: int) -> int:
+        """K splits for an M-row call: layers whose tiles fill less than half of the SMs (FC at batch <= 256)
+        are split along K until they do; each split keeps >= 8 k-blocks.  B200_GEMM_SPLITK=0 disables."""
+        if os.environ.get("B200_GEMM_SPLITK", "1") != "1":
+            return 1
+        tiles = ((M + 127) // 128) * ((self.N + self.bn - 1) // self.bn)
+        if tiles * 2 > self._sms or self.nkb < 16:
+            return 1
+        return max(1, min(self._sms // tiles, self.nkb // 8))
 
     def run(self, a_ptr: int, lda: int, M: int, c_ptr: int, ldc: int, bias: Optional[torch.Tensor] = None,
             flags: int = 0) -> None:
         if bias is not None:
             flags |= BIAS
+        ks = 1 if (flags & ACCUMULATE) else self.splitk_for(M)
+        if ks > 1:                       # partial sums into a workspace, then a deterministic reduce + epilogue
+            need = ks * M * self.N
+            if self._ws is None or self._ws.numel() < need:
+                self._ws = torch.empty(need, dtype=torch.float32, device=self.device)
+            st = cu.current_stream_ptr()
+            cu.cu_check(_lib().b200_tc_gemm_splitk(self._h, C.c_void_p(a_ptr), lda, M, None, fptr(self._ws), self.N,
+                                                   0, ks, M * self.N, st), "tc_gemm_splitk")
+            cu.cu_check(_lib().b200_splitk_reduce(fptr(self._ws), ks, M * self.N, M, self.N,
+                                                  fptr(bias) if bias is not None else None, C.c_void_p(c_ptr), ldc,
+                                                  flags, st), "splitk_reduce")
+            return
         cu.cu_check(_lib().b200_tc_gemm(self._h, C.c_void_p(a_ptr), lda, M,
                                         fptr(bias) if bias is not None else None, C.c_void_p(c_ptr), ldc,
                                         flags, cu.current_stream_ptr()), "tc_gemm")

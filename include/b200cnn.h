@@ -186,6 +186,15 @@ int b200_tc_gemm_create(const float* w_nk, int N, int K, void** handle);
 int b200_tc_gemm_destroy(void* handle);
 int b200_tc_gemm(void* handle, const float* A, int lda, int M, const float* bias, float* C, int ldc,
                  int flags, void* stream);
+/* Split-K form for small-M layers: split ks of every tile covers a slice of K and stores its partial sums
+ * at C + ks * split_stride floats (flags must be 0 when ksplit > 1); b200_splitk_reduce adds the partials in
+ * a fixed order and applies bias / ReLU / TF32 rounding (flags 8 / 1 / 2).  b200_tc_gemm_info returns the
+ * number of 32-wide k-blocks and the N tile (128 or 256) the kernel uses for this handle. */
+int b200_tc_gemm_splitk(void* handle, const float* A, int lda, int M, const float* bias, float* C, int ldc,
+                        int flags, int ksplit, long long split_stride, void* stream);
+int b200_splitk_reduce(const float* ws, int ksplit, long long stride, long long rows, int cols,
+                       const float* bias, float* out, int ld, int flags, void* stream);
+int b200_tc_gemm_info(void* handle, int* nkb, int* bn);
 /* Convolution as an implicit GEMM on the same kernel: x is NHWC [N][H][W][C] with C % 32 == 0 (may be a
  * peer pointer); the handle holds [K_out][F*F*C] weights in (fy, fx, c) order; out is [N*Ho*Wo][ldc].
  * The producer warps gather the im2col rows on the fly (zero fill outside the image); no col buffer. */

@@ -64,9 +64,10 @@ def test_full_alexnet_matches_torch(tp_world):
 
 @pytest.mark.parametrize("N,H,W,C,K,F,S,P", [(3, 13, 13, 64, 96, 3, 1, 1), (2, 9, 11, 32, 40, 5, 2, 2),
                                              (5, 6, 6, 128, 130, 3, 1, 0), (1, 13, 13, 384, 256, 3, 1, 1)])
-def test_tc_conv_gemm_matches_torch(N, H, W, C, K, F, S, P):
+def test_tc_conv_gemm_matches_torch(N, H, W, C, K, F, S, P, monkeypatch):
     """Implicit-GEMM convolution (loader gathers im2col rows on the fly) vs conv2d in fp32 on the CPU."""
     from b200cnn.ops import ext
+    monkeypatch.setenv("B200_GEMM_SPLITK", "0")          # bit-equality below needs the same summation order
     g = torch.Generator().manual_seed(11)
     x = torch.randn((N, H, W, C), generator=g)
     w = torch.randn((K, C, F, F), generator=g) * 0.05
@@ -88,6 +89,7 @@ def test_full_alexnet_implicit_conv_equals_im2col(monkeypatch):
     cfg = default_config(batch=2, init=INIT_RAND, seed=2, precision="tf32")
     x, w12 = make_problem(cfg)
     w = make_full_weights(w12, seed=5)
+    monkeypatch.setenv("B200_GEMM_SPLITK", "0")          # the im2col route would split K at this tiny batch
     monkeypatch.setenv("B200_CONV_IMPLICIT", "0")
     p0 = FullAlexNet(cfg, w, "cuda:0").forward(x.cuda()).cpu()
     monkeypatch.setenv("B200_CONV_IMPLICIT", "1")
@@ -95,3 +97,25 @@ def test_full_alexnet_implicit_conv_equals_im2col(monkeypatch):
     assert net.c3.implicit and net.c4.implicit and net.c5.implicit
     p1 = net.forward(x.cuda()).cpu()
     assert torch.equal(p0, p1)
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 1000, 4096), (64, 512, 9216), (130, 4096, 1024)])
+def test_tc_gemm_splitk_matches_plain_and_is_deterministic(M, N, K, monkeypatch):
+    """Split-K (partials + fixed-order reduce) vs the unsplit kernel and vs fp32 matmul; two runs bit-equal."""
+    from b200cnn.ops import ext
+    g = torch.Generator().manual_seed(7)
+    a = torch.randn((M, K), generator=g)
+    w = torch.randn((N, K), generator=g) * 0.02
+    b = torch.randn(N, generator=g)
+    ref = torch.relu(a @ w.t() + b)
+    lin = ext.TcLinear(w, "cuda:0")
+    monkeypatch.setenv("B200_GEMM_SPLITK", "1")
+    assert lin.splitk_for(M) > 1
+    o1 = lin(a.cuda(), b.cuda(), relu=True).cpu()
+    o2 = lin(a.cuda(), b.cuda(), relu=True).cpu()
+    assert torch.equal(o1, o2)
+    monkeypatch.setenv("B200_GEMM_SPLITK", "0")
+    assert lin.splitk_for(M) == 1
+    o0 = lin(a.cuda(), b.cuda(), relu=True).cpu()
+    assert _rel(o1, ref) < 4e-3 and _rel(o0, ref) < 4e-3
+    assert _rel(o1, o0) < 1e-4                          # fp32 summation order differs, nothing else
