@@ -2,12 +2,17 @@
 
     mpirun -np N python -m b200cnn.runners.full --batch 256
 
-Blocks 1-2 run row-decomposed across the N GPUs with the fused peer-memory kernels (exactly as V4/V5);
-rank 0 then runs Conv3-5 + Pool5 (13x13 activations: too small to split), and FC6-8 run
+Blocks 1-2 run row-decomposed across the N GPUs with the fused peer-memory kernels (exactly as V4/V5).
+Conv3-5 + Pool5 work on 13x13 maps, too small to split by rows, so they are sharded by BATCH: after a
+device-side barrier every rank copies its images of the gathered LRN2 tensor out of rank 0's buffer over
+NVLink (one pass; the implicit-GEMM loader would otherwise re-read each pixel nine times over the link),
+runs the three implicit-GEMM convolutions and the pool locally and stores its feature rows straight into rank
+0's FC input buffer (B200_FULL_CONV_SHARD=rank0: rank 0 does all of it, the round-1 baseline).  FC6-8 run
 tensor-parallel over all N GPUs through peer memory (models/alexnet_full.py: TPClassifier).
 Prints V4-style lines; the "values" are the first 10 class probabilities of image 0."""
 from __future__ import annotations
 
+import os
 import sys
 import time
 
@@ -20,6 +25,7 @@ from ..models.session import Session
 from ..ops import ext
 from ..ops.cpu import fnv1a64
 from ..parallel import dist as bdist
+from ..parallel.symm import DevBuf
 from ..utils import logfmt as L
 from .common import make_parser, fail
 
@@ -41,21 +47,55 @@ def main(argv=None) -> int:
     w = make_full_weights(w12, seed=cfg.seed, feat=feat)
     tp = TPClassifier(w, sess.symm, ctx.rank, ctx.world, cfg.batch, feat)
     sess.symm.commit()
+    shard = ctx.world > 1 and os.environ.get("B200_FULL_CONV_SHARD", "batch") == "batch"
+    per = -(-cfg.batch // ctx.world)
+    b0 = min(cfg.batch, ctx.rank * per) if shard else 0
+    b1 = min(cfg.batch, b0 + per) if shard else (cfg.batch if ctx.rank == 0 else 0)
     convs = [ConvGemm(w.w3, w.b3, ctx.device, 1), ConvGemm(w.w4, w.b4, ctx.device, 1),
-             ConvGemm(w.w5, w.b5, ctx.device, 1)] if ctx.rank == 0 else None
+             ConvGemm(w.w5, w.b5, ctx.device, 1)] if b1 > b0 else None
+    if shard:
+        with torch.cuda.device(ctx.device):
+            # rank 0's gathered LRN2 tensor and FC input, addressed through their peer mappings
+            y_all = DevBuf(sess.symm.ptr(0, "out0"), cfg.batch * sh.Hp2 * sh.Wp2 * 256 * 4,
+                           ctx.device).tensor((cfg.batch, sh.Hp2, sh.Wp2, 256))
+            x5_all = DevBuf(sess.symm.ptr(0, "tp_x5"), cfg.batch * feat * 4, ctx.device).tensor((cfg.batch, feat))
+            y_loc = torch.empty((max(b1 - b0, 1), sh.Hp2, sh.Wp2, 256), dtype=torch.float32, device=ctx.device)
     lo, hi = sess.input_rows
     xin = x[:, lo:hi].contiguous().pin_memory() if hi > lo else None
 
-    def step():
-        e = sess.engine
+    def load():                              # this rank's input rows: pinned host -> resident device buffer
         if xin is not None:
-            e.input_view(0).copy_(xin, non_blocking=True)
+            sess.engine.h2d(0, xin)
+
+    def compute():
+        e = sess.engine
         y = e.forward_enqueue(0, 0)
-        if ctx.rank == 0:
+        if shard:
+            tp.barrier()                     # rank 0 is past its completion wait: the gathered tensor is whole
+            if b1 > b0:
+                z = y_loc[:b1 - b0]
+                z.copy_(y_all[b0:b1])
+                for c in convs:
+                    z = c(z)
+                x5_all[b0:b1].copy_(ext.maxpool(z, 3, 2).reshape(b1 - b0, -1))
+        elif ctx.rank == 0:
             for c in convs:
                 y = c(y)
             tp.x5_view().copy_(ext.maxpool(y, 3, 2).reshape(cfg.batch, -1))
-        return tp.forward()
+        return tp.forward()              # opens with a barrier: every rank's feature rows have landed
+
+    def timed(fn, iters):
+        torch.cuda.synchronize(ctx.device); ctx.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            out = fn()
+        e1.record(); e1.synchronize()
+        return out, ctx.max_float(e0.elapsed_time(e1) / iters)
+
+    def step():
+        load()
+        return compute()
 
     ctx.barrier()
     t0 = time.perf_counter()
@@ -65,14 +105,12 @@ def main(argv=None) -> int:
     ms = (time.perf_counter() - t0) * 1e3
     kv = {}
     if ns.iters > 0:
-        torch.cuda.synchronize(ctx.device); ctx.barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(ns.iters):
+        for _ in range(2):                   # second call captures the blocks 1-2 CUDA graph: keep it untimed
             probs = step()
-        e1.record(); e1.synchronize()
-        dms = ctx.max_float(e0.elapsed_time(e1) / ns.iters)
-        kv = dict(device_forward_ms_warm=dms, images_per_s_warm=cfg.batch / (dms / 1e3))
+        probs, dms = timed(compute, ns.iters)            # input resident on the device
+        _, ems = timed(step, ns.iters)                   # plus the pinned H2D of the inputs every step
+        kv = dict(device_forward_ms_warm=dms, images_per_s_warm=cfg.batch / (dms / 1e3),
+                  with_h2d_forward_ms_warm=ems, with_h2d_images_per_s_warm=cfg.batch / (ems / 1e3))
     sess.engine.check_status()
     if ctx.rank == 0:
         p = probs.cpu()
@@ -80,7 +118,8 @@ def main(argv=None) -> int:
             L.emit(line)
         L.emit(L.v4_time(ms, "Full (spatial conv + TP FC)"))
         for line in L.extras(fnv=fnv1a64(p), wall_ms=ms, np=ctx.world, batch=cfg.batch,
-                             prob_row_sum=float(p[0].sum()), argmax0=int(p[0].argmax()), **kv):
+                             prob_row_sum=float(p[0].sum()), argmax0=int(p[0].argmax()),
+                             conv_shard="batch" if shard else "rank0", **kv):
             L.emit(line)
     ctx.finalize()
     return 0
