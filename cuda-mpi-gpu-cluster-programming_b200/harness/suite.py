@@ -243,7 +243,67 @@ def run_suite(prefix: str, cases: List[Case], timeout: int = 600, extra_args: Op
     return csv_path, rows
 
 
+# ---- single-case entry points for scripts/common_test_utils.sh --------------------------------
+def run_one_case(name: str, np_: int, subdir: str, tag: str, session_dir: str, csv_path: str,
+                 timeout: int = 600, extra_args: Optional[List[str]] = None) -> dict:
+    """One build-run-parse case appended to ``csv_path`` (created with the header when missing): what the
+    reference's ``setup_test_case`` + ``execute_single_test_case`` pair does (ref
+    scripts/common_test_utils.sh:187-346).  A missing variant directory is logged as a failed row."""
+    up = name.upper()
+    c = Case(name, subdir, tag, np_, cuda=any(k in up for k in ("V3", "V4", "V5", "CUDA")),
+             mpi=any(k in up for k in ("V2", "V4", "V5", "MPI")))
+    os.makedirs(session_dir, exist_ok=True)
+    session_id = os.path.basename(os.path.normpath(session_dir))
+    if not os.path.isdir(os.path.join(FINAL, subdir)):
+        row = {h: "" for h in CSV_HEADER}
+        row.update(SessionID=session_id, MachineID=socket.gethostname(), GitCommit=git_commit(),
+                   EntryTimestamp=datetime.datetime.now().isoformat(timespec="seconds"), ProjectVariant=name,
+                   NumProcesses=np_, MakeLogFile="N/A", BuildSucceeded="false", BuildMessage="Dir not found",
+                   RunLogFile="N/A", RunCommandSucceeded="false", RunEnvironmentWarning="false",
+                   RunMessage="Skipped", ParseSucceeded="false", ParseMessage="Skipped",
+                   OverallStatusSymbol="✘", OverallStatusMessage="✘ Dir Missing")
+    else:
+        flags = os.environ.get("DETECTED_GPU_ARCH_FLAGS") or detect_gpu_arch_flags()[0]
+        row = execute_case(c, session_dir, session_id, flags, timeout, extra_args or [])
+    new = not os.path.exists(csv_path)
+    with open(csv_path, "a", newline="") as f:
+        wtr = csv.DictWriter(f, fieldnames=CSV_HEADER)
+        if new:
+            wtr.writeheader()
+        wtr.writerow(row)
+    return row
+
+
+def _sub_main(argv: List[str]) -> Optional[int]:
+    """``arch`` | ``case ...`` | ``table <csv>``: the pieces a bash caller composes itself."""
+    if not argv or argv[0] not in ("arch", "case", "table"):
+        return None
+    if argv[0] == "arch":
+        flags, how = detect_gpu_arch_flags()
+        print(flags)
+        print(f"[ARCH_DETECT] {how}", file=sys.stderr)
+        return 0
+    if argv[0] == "table":
+        with open(argv[1], newline="") as f:
+            print(summary_table(list(csv.DictReader(f))))
+        return 0
+    ap = argparse.ArgumentParser(prog="suite case")
+    ap.add_argument("--name", required=True); ap.add_argument("--np", type=int, default=1)
+    ap.add_argument("--subdir", required=True); ap.add_argument("--tag", required=True)
+    ap.add_argument("--session-dir", required=True); ap.add_argument("--csv", required=True)
+    ap.add_argument("--timeout", type=int, default=600)
+    ap.add_argument("rest", nargs="*")
+    ns = ap.parse_args(argv[1:])
+    row = run_one_case(ns.name, ns.np, ns.subdir, ns.tag, ns.session_dir, ns.csv, ns.timeout, ns.rest)
+    print(f"  [{row['OverallStatusSymbol']}] {ns.name} np={ns.np}: {row['OverallStatusMessage']}"
+          f"  time={row['ExecutionTime_ms'] or '-'} ms  shape={row['OutputShape'] or '-'}")
+    return 0 if row["OverallStatusSymbol"] != "✘" else 1
+
+
 def main(argv=None) -> int:
+    sub = _sub_main(list(sys.argv[1:] if argv is None else argv))
+    if sub is not None:
+        return sub
     ap = argparse.ArgumentParser(description=__doc__.split("\n")[0])
     ap.add_argument("--session-prefix", default="script1")
     ap.add_argument("--np", default="1,2,4", help="process counts for the MPI variants")

@@ -1,5 +1,6 @@
 """Log-line contract and harness parser round trips."""
 import os
+import re
 import subprocess
 import sys
 
@@ -92,3 +93,31 @@ def test_multi_machine_dry_run_plan():
 def test_hw_toolchain_test_and_package(tmp_path):
     from b200cnn.harness import hw
     assert hw.test(1, sizes=[128], counts=[1, 2, 3], timeout=120) == 0      # np=3 skipped (128 % 3)
+
+
+def test_bash_library_functions(tmp_path):
+    """scripts/common_test_utils.sh: the reference's sourceable function names (setup_test_case,
+    execute_single_test_case, _log_to_csv, _print_summary_table) on top of the Python harness."""
+    script = f'''
+set -e
+source "{ROOT}/scripts/common_test_utils.sh"
+LOGS_BASE_DIR="{tmp_path}"
+init_test_session unit
+_detect_and_set_cuda_arch_flags
+setup_test_case "V1 Serial" 1 v1_serial v1_serial && execute_single_test_case
+setup_test_case "V9 Missing" 2 v9_nope v9 || true
+_log_to_csv "Manual" 1 m.log true ok r.log true false ok true ok OK fine 1.5 1x1x1 "1 2 3"
+_print_summary_table
+echo "CSV=$CSV_SUMMARY_FILE FLAGS=$DETECTED_GPU_ARCH_FLAGS"
+'''
+    p = subprocess.run(["bash", "-c", script], capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout + p.stderr
+    csv_path = re.search(r"CSV=(\S+)", p.stdout).group(1)
+    assert "compute_100a" in p.stdout or "sm_" in p.stdout
+    import csv as _csv
+    rows = list(_csv.DictReader(open(csv_path)))
+    assert [r["ProjectVariant"] for r in rows] == ["V1 Serial", "V9 Missing", "Manual"]
+    assert rows[0]["OverallStatusSymbol"] == "✔" and rows[0]["OutputShape"] == "13x13x256"
+    assert rows[1]["BuildMessage"] == "Dir not found" and rows[1]["OverallStatusSymbol"] == "✘"
+    assert rows[2]["ExecutionTime_ms"] == "1.5" and rows[2]["OutputFirst5Values"] == "1 2 3"
+    assert os.path.exists(os.path.join(os.path.dirname(csv_path), "run_v1_serial_np1.log"))
