@@ -63,6 +63,10 @@ def run_ours(a):
     from b200cnn.parallel import dist as bdist
     from b200cnn.utils.clocks import ClockSampler, rejected
 
+    if not torch.cuda.is_available():       # never a silent CPU fallback: the metric is a GPU metric
+        print(json.dumps({"impl": "ours", "error": "no CUDA device visible: bench.py measures the sm_100a kernels "
+                                                   "and has no CPU path", "gpu_launches": 0}))
+        sys.exit(2)
     ctx = bdist.init()
     if ctx.world != a.gpus:
         if ctx.is_root:
