@@ -50,6 +50,10 @@ def parse():
                     help="end-to-end run: p2p = rank 0 feeds everything; sharded = each rank feeds its slab")
     ap.add_argument("--e2e-strategy", choices=["same", "halo", "recompute"], default="halo",
                     help="decomposition for the end-to-end run (halo = smallest input slabs = fewest H2D bytes)")
+    ap.add_argument("--conv2-kernel", choices=["auto", "single", "double"], default="auto",
+                    help="1 GPU: conv2 through tc_block_kernel (one 256-pixel tile fills TMEM) or tc_block_db_kernel "
+                         "(128-pixel tiles, double-buffered TMEM, own epilogue warps).  auto runs both on the bench "
+                         "input, requires bit-identical outputs and keeps the faster")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
 
@@ -166,6 +170,53 @@ def run_ours(a):
         torch.cuda.empty_cache()
         return ms_
 
+    # conv2 kernel variant (single GPU): both kernels run the bench input untimed; the double-buffered one is
+    # used only if its output is bit-identical to the single-buffered kernel's and it is faster
+    conv2_info = None
+    os.environ.pop("B200_TC_DB", None)
+    if N == 1 and precision == "tf32" and a.conv2_kernel != "single":
+        def probe(db):
+            if db:
+                os.environ["B200_TC_DB"] = "1"
+            else:
+                os.environ.pop("B200_TC_DB", None)
+            s_ = Session(cfg, w, device=dev, precision=precision, strategy="halo", scatter=a.scatter)
+            e_ = s_.engine
+            lo_, hi_ = s_.input_rows
+            e_.input_view(0).copy_(x[:, lo_:hi_].to(dev))
+            y_ = e_.forward_enqueue(0, 0).clone()
+            for _ in range(3):
+                e_.forward_enqueue(0, 0)
+            torch.cuda.synchronize(dev)
+            t0_, t1_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0_.record()
+            for _ in range(5):
+                e_.forward_enqueue(0, 0)
+            t1_.record()
+            t1_.synchronize()
+            y2_ = e_.forward_enqueue(0, 0).clone()          # graph replay, several tiles per CTA behind it
+            e_.check_status()
+            ok_ = bool(torch.equal(y_, y2_))
+            del s_, e_
+            return y_, t0_.elapsed_time(t1_) / 5, ok_
+        try:
+            y_s, ms_s, _ = probe(False)
+            y_d, ms_d, stable = probe(True)
+            same = bool(torch.equal(y_s, y_d)) and stable
+            use_db = same and (a.conv2_kernel == "double" or ms_d < ms_s)
+            conv2_info = {"single_buffered_forward_ms": round(ms_s, 4),
+                          "double_buffered_forward_ms": round(ms_d, 4), "bit_identical": same,
+                          "used": "double_buffered" if use_db else "single_buffered"}
+            del y_s, y_d
+        except Exception as ex:                   # any host-side problem: stay on the validated kernel
+            use_db = False
+            conv2_info = {"used": "single_buffered", "error": str(ex)[:200]}
+        if use_db:
+            os.environ["B200_TC_DB"] = "1"
+        else:
+            os.environ.pop("B200_TC_DB", None)
+        torch.cuda.empty_cache()
+
     tuned = None
     if a.strategy == "auto":
         if N > 1:
@@ -213,6 +264,7 @@ def run_ours(a):
                    "parallelism": f"spatial-rows{N}" if N > 1 else "single-gpu",
                    "strategy": a.strategy, "strategy_autotune_ms": tuned,
                    "scatter": a.scatter if N > 1 else "local", "p2p_scatter_images_per_s": p2p_alt,
+                   "conv2_kernel": conv2_info,
                    "l2": "flushed between timed iterations (256 MiB fill, untimed)"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "impl": "ours",
     }

@@ -723,6 +723,299 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
     }
 }
 
+
+// ------------------------------------------ double-buffered kernel (C % 32 == 0 layers) ----
+// DRAFT, off by default (B200_TC_DB=1), not yet run on a GPU: DESIGN.md §6 step 1.
+// tc_block_kernel<false> fills all of TMEM with one 256-pixel tile and its producer warps are its
+// epilogue warps, so drain, max-pool and LRN (55 us of conv2's 282 us) never overlap an MMA.  Here a
+// tile is 128 pixel slots (one M=128 accumulator of N <= 256 columns), TMEM holds two of them, and
+// the roles are split as in tc_block_swapped_kernel:
+//   warps 0-7  im2col producers (cp.async 16 B chunks straight into the swizzled A stage, 4 rows each)
+//   warp  8    MMA issuer + TMEM owner;   warp 9  TMA issuer (weight k-blocks)
+//   warps 10-13 epilogue: TMEM lane quarter warp%4, 32 columns at a time -> cbuf -> pool -> pbuf -> LRN
+//               -> store; the accumulator is handed back to the MMA warp BEFORE the LRN pass.
+// The epilogue buffers do not alias the stages, so the TMA warp never waits for an epilogue.
+constexpr int kDbThreads = 448;
+constexpr int kDbEpiWarp0 = 10;
+constexpr int kDbTileM = 128;
+constexpr int kDbAStageBytes = kDbTileM * 128;            // 16 KB
+constexpr int kDbCbufBytes = kDbTileM * kCbufPitch * 4;   // one 32-channel chunk of the tile
+
+struct DbParams {
+    TcParams t;                                          // nacc == 1 tiling
+    uint32_t cbuf_off, pbuf_off, db_ctl_off;
+};
+
+__device__ __forceinline__ void bar_epilogue() { asm volatile("bar.sync 2, 128;" ::: "memory"); }
+
+__global__ void __launch_bounds__(kDbThreads, 1)
+tc_block_db_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant__ DbParams dp,
+                   const float* __restrict__ bias, float* __restrict__ out) {
+    extern __shared__ uint8_t smem_raw[];
+    const TcParams& p = dp.t;
+    const b200_block_geom& g = p.g;
+    const int N = g.K;
+
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
+    const int NS = p.stages;
+    const uint32_t b_off = NS * kDbAStageBytes;
+    const uint32_t full_bar = base + dp.db_ctl_off;           // [4]
+    const uint32_t empty_bar = full_bar + 32;                 // [4]
+    const uint32_t tfull_bar = full_bar + 64;                 // [2] accumulator ready
+    const uint32_t tempty_bar = full_bar + 80;                // [2] accumulator drained
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + dp.db_ctl_off + 96);
+    const float** rowtab = reinterpret_cast<const float**>(gbase + dp.db_ctl_off + 112);
+    int2* ptab = reinterpret_cast<int2*>(gbase + dp.db_ctl_off + 112 + kRowTab * 8);
+    float* s_bias = reinterpret_cast<float*>(gbase + dp.db_ctl_off + 112 + kRowTab * 8 + kMaxPooled * 8);
+    float* cbuf0 = reinterpret_cast<float*>(gbase + dp.cbuf_off);
+    float* pbuf = reinterpret_cast<float*>(gbase + dp.pbuf_off);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NS; ++s) {
+            mbar_init(full_bar + 8 * s, kProducerThreads + 1);
+            mbar_init(empty_bar + 8 * s, 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(tfull_bar + 8 * b, 1);
+            mbar_init(tempty_bar + 8 * b, 4);
+        }
+        fence_mbar_init();
+    }
+    for (int i = threadIdx.x; i < N; i += kDbThreads) s_bias[i] = bias[i];
+    if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int tiles_per_img = p.tiles_r * p.tiles_c;
+
+    if (warp < kProducerWarps) {
+        // =============================== im2col producers (A operand) =====================
+        const int tid = threadIdx.x;
+        const int j = tid & 7, m_base = tid >> 3;             // rows m_base + 32*i, i < 4
+        const uint32_t row_sw = (uint32_t)(m_base & 7);
+        const uint32_t dst0 = (uint32_t)(m_base >> 3) * 1024u + row_sw * 128u + (((uint32_t)j ^ row_sw) << 4);
+        const int IRT = (p.TR - 1) * g.S + g.F;
+        int pij[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int m = m_base + 32 * i;
+            const int pi = m / p.TC;
+            pij[i] = m < p.TR * p.TC ? (pi << 16) | (m - pi * p.TC) : -1;
+        }
+        int stage = 0;
+        uint32_t phase = 0;
+        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
+            const int n = (int)(w / tiles_per_img);
+            const int rem = (int)(w - (long long)n * tiles_per_img);
+            const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
+            const int cr0 = 2 * (g.p0 + tr_i * p.PR), cc0 = 2 * (tc_i * p.PC);
+            const int ir0 = cr0 * g.S - g.P;
+            if (p.any_flag && tid == 0) {                       // consumer side of the halo flags
+                for (int s = 0; s < g.nseg; ++s)
+                    if (g.seg[s].flag && ir0 < g.seg[s].hi && ir0 + IRT > g.seg[s].lo)
+                        wait_flag_ge(g.seg[s].flag + n, g.seg[s].target * (g.epoch ? *g.epoch : 1), g.status,
+                                     g.timeout_ns);
+            }
+            bar_producers();                                    // previous tile's row-table reads are over
+            int rsel[4], cbyte[4];
+            uint32_t xmask[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int pi = pij[i] >> 16, pj = pij[i] & 0xFFFF;
+                const bool ok = pij[i] >= 0 && (cr0 + pi) < g.Hc && (cc0 + pj) < g.Wc;
+                const int x0 = (cc0 + pj) * g.S - g.P;
+                rsel[i] = ok ? pi * g.S : IRT;                  // IRT.. = null rows -> zero fill
+                cbyte[i] = (x0 * g.C + 4 * j) * 4;
+                const int lo = max(0, -x0), hi = min(g.F, g.W - x0);
+                xmask[i] = hi > lo ? (((1u << hi) - 1u) & ~((1u << lo) - 1u)) : 0u;
+            }
+            if (tid < IRT + g.F) {
+                const int h = ir0 + tid;
+                rowtab[tid] = (tid < IRT && h >= 0 && h < g.H) ? seg_row_ptr(g, n, h) : nullptr;
+            }
+            bar_producers();
+            int fy = 0, fx = 0, cch = 0;
+            const char* rp4[4];
+            uint32_t vm[4];
+            for (int kb = 0; kb < p.nkb; ++kb) {
+                if (fx == 0) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        rp4[i] = reinterpret_cast<const char*>(rowtab[rsel[i] + fy]);
+                        vm[i] = rp4[i] ? xmask[i] : 0u;
+                    }
+                }
+                mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+                const uint32_t a_dst = base + stage * kDbAStageBytes + dst0;
+                const int off = (fx * g.C + cch * kBlockK) * 4;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t nb = ((vm[i] >> fx) & 1u) ? 16u : 0u;
+                    cp_async16(a_dst + i * 4096u, rp4[i] + (cbyte[i] + off), nb);
+                }
+                cp_async_mbar_arrive_noinc(full_bar + 8 * stage);
+                if (++fx == g.F) { fx = 0; if (++fy == g.F) { fy = 0; ++cch; } }
+                if (++stage == NS) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == kMmaWarp) {
+        // ======================================= MMA issuer ==============================
+        int stage = 0, buf = 0;
+        uint32_t phase = 0, bphase = 0;
+        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
+            mbar_wait(tempty_bar + 8 * buf, bphase ^ 1);        // epilogue has drained this accumulator
+            tc_fence_after();
+            for (int kb = 0; kb < p.nkb; ++kb) {
+                mbar_wait(full_bar + 8 * stage, phase);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint64_t da = make_smem_desc(base + stage * kDbAStageBytes);
+                    const uint64_t db = make_smem_desc(base + b_off + stage * p.b_stage_bytes);
+#pragma unroll
+                    for (int ks = 0; ks < kBlockK / 8; ++ks)
+                        umma_tf32(tmem_base + (uint32_t)(buf * N), da + 2 * ks, db + 2 * ks, p.idesc,
+                                  (kb | ks) != 0 ? 1u : 0u);
+                    umma_commit(empty_bar + 8 * stage);
+                    if (kb == p.nkb - 1) umma_commit(tfull_bar + 8 * buf);
+                }
+                __syncwarp();
+                if (++stage == NS) { stage = 0; phase ^= 1; }
+            }
+            if (++buf == 2) { buf = 0; bphase ^= 1; }
+        }
+    } else if (warp == kTmaWarp) {
+        // ======================================= TMA issuer (weights) ====================
+        int stage = 0;
+        uint32_t phase = 0;
+        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
+            for (int kb = 0; kb < p.nkb; ++kb) {
+                mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+                if (lane == 0) {
+                    const uint32_t fb = full_bar + 8 * stage;
+                    mbar_arrive_expect_tx(fb, (uint32_t)p.b_stage_bytes);
+                    tma_load_2d(base + b_off + stage * p.b_stage_bytes, &tmapB, kb * kBlockK, 0, fb);
+                }
+                __syncwarp();
+                if (++stage == NS) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else {
+        // ======================================= epilogue warps ==========================
+        const int q = warp & 3;                                // TMEM lane quarter this warp may read
+        const int we = warp - kDbEpiWarp0, te = we * 32 + lane; // warp / thread index inside the epilogue group
+        const int row = q * 32 + lane;                         // pixel slot this thread drains
+        const int PP = p.PR * p.PC, nchunk = N / 32, NP = N + 4;
+        const bool do_lrn = g.lrn.N_lrn > 0;
+        if (te < PP) {
+            const int pi = te / p.PC, pj = te - pi * p.PC;
+            ptab[te] = make_int2(((2 * pi) * p.TC + 2 * pj) * kCbufPitch, (pi << 16) | pj);
+        }
+        if (do_lrn)                                            // pbuf row: [2 zeros | N channels | 2 zeros]
+            for (int i = te; i < PP * 4; i += 128)
+                pbuf[(i >> 2) * NP + ((i & 3) < 2 ? (i & 3) : N + (i & 3))] = 0.f;
+        bar_epilogue();
+        const int half = g.lrn.N_lrn / 2;
+        const float al = g.lrn.mode == B200_LRN_ALPHA_OVER_N ? g.lrn.alpha / (float)max(g.lrn.N_lrn, 1) : g.lrn.alpha;
+        const float nbeta = -g.lrn.beta;
+        const bool win5 = g.lrn.N_lrn == 5;
+        int buf = 0;
+        uint32_t bphase = 0;
+        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
+            const int n = (int)(w / tiles_per_img);
+            const int rem = (int)(w - (long long)n * tiles_per_img);
+            const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
+            const int pr0 = g.p0 + tr_i * p.PR, pc0 = tc_i * p.PC;
+            mbar_wait(tfull_bar + 8 * buf, bphase);
+            tc_fence_after();
+            for (int cc = 0; cc < nchunk; ++cc) {
+                float* cb = cbuf0 + (cc & 1) * (kDbCbufBytes / 4);
+                uint32_t r[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * N + cc * 32), r);
+#pragma unroll
+                for (int c = 0; c < 32; ++c) cb[row * kCbufPitch + c] = __uint_as_float(r[c]);
+                bar_epilogue();                                 // chunk cc is whole; chunk cc-1's reads are over
+                const float bch = s_bias[cc * 32 + lane];
+                for (int pp = we; pp < PP; pp += 4) {           // lane = channel inside the chunk
+                    const int2 e = ptab[pp];
+                    const float* c0p = cb + e.x + lane;
+                    float mx = -INFINITY;
+#pragma unroll
+                    for (int a = 0; a < 3; ++a)
+#pragma unroll
+                        for (int b = 0; b < 3; ++b) mx = fmaxf(mx, c0p[(a * p.TC + b) * kCbufPitch]);
+                    float val = fmaxf(mx + bch, 0.f);
+                    if (do_lrn) {
+                        pbuf[pp * NP + 2 + cc * 32 + lane] = val;
+                    } else {
+                        const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
+                        if (p.round_out) val = to_tf32(val);
+                        if (pr < g.p1 && pr < g.Hp && pc < g.Wp)
+                            out[(((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N + cc * 32 + lane] = val;
+                    }
+                }
+            }
+            // every tcgen05.ld of this warp has completed (wait::ld): hand the accumulator back now, so the
+            // MMAs of the tile after next overlap the LRN pass below
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar + 8 * buf);
+            if (do_lrn) {
+                bar_epilogue();                                 // pbuf is whole
+                for (int pp0 = 0; pp0 < PP; pp0 += 4) {
+                    float* optr[4];
+                    const float* prow[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int pp = pp0 + u < PP ? pp0 + u : PP - 1;
+                        const int2 e = ptab[pp];
+                        const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
+                        const bool ok = pp0 + u < PP && pr < g.p1 && pr < g.Hp && pc < g.Wp;
+                        optr[u] = ok ? out + (((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N : nullptr;
+                        prow[u] = pbuf + pp * NP;
+                    }
+                    for (int c = te; c < N; c += 128) {
+                        float val[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const float* px = prow[u] + c;
+                            float ss;
+                            if (win5) {
+                                const float a0 = px[0], a1 = px[1], a2 = px[2], a3 = px[3], a4 = px[4];
+                                ss = fmaf(a0, a0, fmaf(a1, a1, fmaf(a2, a2, fmaf(a3, a3, a4 * a4))));
+                            } else {
+                                ss = 0.f;
+                                const int c_lo = max(0, c - half), c_hi = min(N - 1, c + half);
+                                for (int qq = c_lo; qq <= c_hi; ++qq) ss = fmaf(prow[u][qq + 2], prow[u][qq + 2], ss);
+                            }
+                            val[u] = px[2] * exp2f(nbeta * __log2f(g.lrn.k + al * ss));
+                            if (p.round_out) val[u] = to_tf32(val[u]);
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            if (optr[u]) optr[u][c] = val[u];
+                    }
+                }
+            }
+            bar_epilogue();                                     // cbuf / pbuf free again, all stores issued
+            if (g.n_signal > 0 && te == 0) {                    // producer side of the halo flags
+                __threadfence_system();
+                for (int i = 0; i < g.n_signal; ++i) red_release_sys_add(g.signal[i] + n, 1);
+            }
+            if (++buf == 2) { buf = 0; bphase ^= 1; }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kMmaWarp) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, p.tmem_cols);
+    }
+}
+
 // --------------------------------------------------------------------------- host ----
 struct TcConv {
     int K, C, F, Kpad, device, patch_mode, FCpad;
@@ -783,14 +1076,14 @@ inline bool direct_eligible(const b200_block_geom* g) {
            !getenv("B200_TC_NO_DIRECT");
 }
 
-bool plan_tiles(const b200_block_geom* g, TcParams* p) {
+bool plan_tiles(const b200_block_geom* g, TcParams* p, int max_nacc = 2) {
     const int rows = g->p1 - g->p0;
     const bool patch = is_patch_mode(g->C) && !direct_eligible(g);
     const int nkb = num_kblocks(g->F, g->C);
     const double mma_kb = 4.0 * (128.0 * g->K / 256.0) * 1.3;         // cycles per k-block per accumulator
     const double prod_kb = patch ? 450.0 : 0.0;                       // smem->smem im2col bound (conv1)
     double best = -1;
-    for (int nacc = 1; nacc <= 2; ++nacc)
+    for (int nacc = 1; nacc <= max_nacc; ++nacc)
         for (int PR = 1; PR <= rows && PR <= 63; ++PR)
             for (int PC = 1; PC <= g->Wp; ++PC) {
                 const int TR = 2 * PR + 1, TC = 2 * PC + 1;
@@ -818,13 +1111,13 @@ bool plan_tiles(const b200_block_geom* g, TcParams* p) {
     return best >= 0;
 }
 
-int fill_params(const b200_block_geom* g, TcParams* p, int flags) {
+int fill_params(const b200_block_geom* g, TcParams* p, int flags, int max_nacc = 2) {
     if (g->K % 32 != 0 || g->K > 256 || g->K < 32) return B200_ERR_UNSUPPORTED;
     const bool patch = is_patch_mode(g->C);
     if (patch && (g->S * g->C) % 4 != 0) return B200_ERR_UNSUPPORTED;   // LDS.128 alignment
     memset(p, 0, sizeof(*p));
     p->g = *g;
-    if (!plan_tiles(g, p)) return B200_ERR_ARG;
+    if (!plan_tiles(g, p, max_nacc)) return B200_ERR_ARG;
     p->nkb = num_kblocks(g->F, g->C);
     p->FCpad = fcpad(g->F, g->C);
     p->round_out = flags & 1;
@@ -881,6 +1174,36 @@ int fill_swapped(const b200_block_geom* g, SwParams* sp, int flags) {
     const size_t total = 1024 + sp->sw_ctl_off + 112 + kRowTab * 8 + 128 * 4 + 64;
     if (total > 227 * 1024) return B200_ERR_UNSUPPORTED;
     return B200_OK;
+}
+
+// double-buffered kernel: layout [A stages | B stages | 2 cbuf | pbuf | ctl]
+inline bool db_requested(const b200_block_geom* g) { return !is_patch_mode(g->C) && getenv("B200_TC_DB") != nullptr; }
+
+int fill_db(const b200_block_geom* g, DbParams* dp, int flags) {
+    if (is_patch_mode(g->C)) return B200_ERR_UNSUPPORTED;
+    int rc = fill_params(g, &dp->t, flags, /*max_nacc=*/1);
+    if (rc != B200_OK) return rc;
+    TcParams& p = dp->t;
+    const size_t pbuf_bytes = g->lrn.N_lrn > 0 ? (size_t)p.PR * p.PC * (g->K + 4) * 4 : 0;
+    const size_t epi = 2 * (size_t)kDbCbufBytes + ((pbuf_bytes + 15) & ~(size_t)15);
+    const size_t ctl = 112 + kRowTab * 8 + kMaxPooled * 8 + (size_t)g->K * 4 + 64;
+    const size_t stage_bytes = (size_t)kDbAStageBytes + p.b_stage_bytes;
+    const long avail = 226 * 1024 - 1024 - (long)epi - (long)ctl;
+    int stages = (int)(avail / (long)stage_bytes);
+    if (stages > 4) stages = 4;
+    if (stages < 2) return B200_ERR_UNSUPPORTED;
+    p.stages = stages;
+    dp->cbuf_off = (uint32_t)(stages * stage_bytes);
+    dp->pbuf_off = dp->cbuf_off + 2 * kDbCbufBytes;
+    dp->db_ctl_off = (uint32_t)(stages * stage_bytes + epi);
+    int cols = 32;
+    while (cols < 2 * g->K) cols *= 2;                 // two accumulators of N columns
+    p.tmem_cols = cols;
+    return B200_OK;
+}
+
+size_t smem_bytes_db(const DbParams& dp) {
+    return 1024 + (size_t)dp.db_ctl_off + 112 + kRowTab * 8 + kMaxPooled * 8 + (size_t)dp.t.g.K * 4 + 64;
 }
 
 size_t smem_bytes_swapped(const SwParams& sp) {
@@ -947,6 +1270,10 @@ extern "C" int b200_tc_conv_destroy(void* handle) {
 extern "C" int b200_tc_block_tiles(const b200_block_geom* g) {
     if (!g) return B200_ERR_ARG;
     if (g->p1 <= g->p0) return 0;
+    if (db_requested(g)) {                             // same tiling the launch will use
+        DbParams dp;
+        if (fill_db(g, &dp, 0) == B200_OK) return dp.t.tiles_r * dp.t.tiles_c;
+    }
     TcParams p;
     int rc = fill_params(g, &p, 0);
     if (rc != B200_OK) return rc;
@@ -973,6 +1300,19 @@ extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const 
                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             const unsigned grid = (unsigned)(sp.t.total_tiles < sms ? sp.t.total_tiles : sms);
             tc_block_swapped_kernel<<<grid, kSwThreads, smem, (cudaStream_t)stream>>>(t->tmap, sp, bias, out);
+            B200_CUDA_TRY(cudaGetLastError());
+            return B200_OK;
+        }
+    }
+    if (db_requested(g)) {
+        DbParams dp;
+        memset(&dp, 0, sizeof(dp));
+        if (fill_db(g, &dp, flags) == B200_OK) {            // else fall through to the single-buffered kernel
+            const size_t smem = smem_bytes_db(dp);
+            B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_db_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               (int)smem));
+            const unsigned grid = (unsigned)(dp.t.total_tiles < sms ? dp.t.total_tiles : sms);
+            tc_block_db_kernel<<<grid, kDbThreads, smem, (cudaStream_t)stream>>>(t->tmap, dp, bias, out);
             B200_CUDA_TRY(cudaGetLastError());
             return B200_OK;
         }
