@@ -9,7 +9,7 @@ zero-argument default reproduces the reference.
 from __future__ import annotations
 
 import argparse
-from dataclasses import dataclass, field, asdict, replace
+from dataclasses import dataclass, asdict, replace
 from typing import Optional
 
 

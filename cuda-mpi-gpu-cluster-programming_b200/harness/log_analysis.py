@@ -17,14 +17,13 @@ from __future__ import annotations
 
 import argparse
 import hashlib
-import math
 import os
 import re
 import sqlite3
 import sys
 from datetime import datetime, timezone
 from pathlib import Path
-from typing import List, Optional
+from typing import Optional
 
 import pandas as pd
 

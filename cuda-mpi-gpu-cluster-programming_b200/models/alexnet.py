@@ -9,7 +9,7 @@ GPU paths live in :mod:`b200cnn.models.engine`.
 """
 from __future__ import annotations
 
-from typing import Callable, Optional, Tuple
+from typing import Callable, Optional
 
 import torch
 

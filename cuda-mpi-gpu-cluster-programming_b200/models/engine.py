@@ -30,7 +30,7 @@ from ..config import NetConfig
 from ..ops import cuda as cu
 from ..ops._ctypes import LrnParams, LRN_MODES
 from ..parallel.planner import make_plan, Plan, RankPlan
-from ..parallel.symm import LocalSymm, DevBuf
+from ..parallel.symm import LocalSymm
 from .init import Blocks12Weights
 
 

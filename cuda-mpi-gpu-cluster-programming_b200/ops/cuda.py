@@ -7,12 +7,12 @@ the native one.
 from __future__ import annotations
 
 import ctypes as C
-from typing import List, Optional, Sequence, Tuple
+from typing import Optional, Sequence, Tuple
 
 import torch
 
 from . import _build
-from ._ctypes import LrnParams, LRN_MODES, check, fptr, NativeError
+from ._ctypes import LrnParams, check, fptr, NativeError
 
 MAX_SEG = 4
 MAX_SIGNAL = 4

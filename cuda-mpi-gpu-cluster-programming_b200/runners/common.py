@@ -4,9 +4,8 @@ from __future__ import annotations
 import argparse
 import sys
 import time
-from typing import Optional
 
-from ..config import add_cli_flags, config_from_args, INIT_CONST, LRN_V1
+from ..config import add_cli_flags, INIT_CONST, LRN_V1
 
 
 def make_parser(prog: str, *, init_default: str = INIT_CONST, lrn_default: str = LRN_V1):

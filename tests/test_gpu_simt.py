@@ -5,7 +5,7 @@ import torch
 from b200cnn import default_config
 from b200cnn.config import INIT_RAND, LRN_V1, LRN_V3
 from b200cnn.models.init import make_problem
-from b200cnn.models.alexnet import forward_cpu, forward_torch_reference
+from b200cnn.models.alexnet import forward_torch_reference
 
 pytestmark = pytest.mark.gpu
 
