@@ -439,8 +439,6 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
 //     three conv rows at a time through a private smem strip, max-pools and stores — no CTA-wide
 //     barrier anywhere in the epilogue.
 constexpr int kSwThreads = 448;
-constexpr int kSwEpiWarp0 = 10;
-constexpr int kSwMaxStages = 4;
 constexpr int kSwWStageBytes = 128 * 128;            // weight stage: 128 rows (K_out rows valid) x 128 B
 
 struct SwParams {
