@@ -40,6 +40,16 @@ def _lib():
     return L
 
 
+def plan_splitk(M: int, N: int, bn: int, nkb: int, sms: int) -> int:
+    """K splits for an [M, N] GEMM with 128 x ``bn`` tiles and ``nkb`` k-blocks of 32 on ``sms`` SMs: layers
+    whose tiles fill less than half of the SMs are split along K until they do, each split keeping at
+    least 8 k-blocks; layers with fewer than 16 k-blocks are never split."""
+    tiles = ((M + 127) // 128) * ((N + bn - 1) // bn)
+    if tiles * 2 > sms or nkb < 16:
+        return 1
+    return max(1, min(sms // tiles, nkb // 8))
+
+
 class TcLinear:
     """Device-resident weights [N,K] (nn.Linear layout) for b200_tc_gemm."""
 
@@ -62,10 +72,7 @@ class TcLinear:
         are split along K until they do; each split keeps >= 8 k-blocks.  B200_GEMM_SPLITK=0 disables."""
         if os.environ.get("B200_GEMM_SPLITK", "1") != "1":
             return 1
-        tiles = ((M + 127) // 128) * ((self.N + self.bn - 1) // self.bn)
-        if tiles * 2 > self._sms or self.nkb < 16:
-            return 1
-        return max(1, min(self._sms // tiles, self.nkb // 8))
+        return plan_splitk(M, self.N, self.bn, self.nkb, self._sms)
 
     def run(self, a_ptr: int, lda: int, M: int, c_ptr: int, ldc: int, bias: Optional[torch.Tensor] = None,
             flags: int = 0) -> None:

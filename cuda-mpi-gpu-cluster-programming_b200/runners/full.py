@@ -30,6 +30,14 @@ from ..utils import logfmt as L
 from .common import make_parser, fail
 
 
+def batch_shard(batch: int, rank: int, world: int):
+    """Images [b0, b1) of the batch whose conv3-5 + pool5 run on ``rank`` (ceil split, trailing ranks may be
+    empty)."""
+    per = -(-batch // world)
+    b0 = min(batch, rank * per)
+    return b0, min(batch, b0 + per)
+
+
 def main(argv=None) -> int:
     ap = make_parser("full_alexnet", init_default=INIT_RAND, lrn_default=LRN_V1)
     ns = ap.parse_args(argv)
@@ -48,9 +56,7 @@ def main(argv=None) -> int:
     tp = TPClassifier(w, sess.symm, ctx.rank, ctx.world, cfg.batch, feat)
     sess.symm.commit()
     shard = ctx.world > 1 and os.environ.get("B200_FULL_CONV_SHARD", "batch") == "batch"
-    per = -(-cfg.batch // ctx.world)
-    b0 = min(cfg.batch, ctx.rank * per) if shard else 0
-    b1 = min(cfg.batch, b0 + per) if shard else (cfg.batch if ctx.rank == 0 else 0)
+    b0, b1 = batch_shard(cfg.batch, ctx.rank, ctx.world) if shard else (0, cfg.batch if ctx.rank == 0 else 0)
     convs = [ConvGemm(w.w3, w.b3, ctx.device, 1), ConvGemm(w.w4, w.b4, ctx.device, 1),
              ConvGemm(w.w5, w.b5, ctx.device, 1)] if b1 > b0 else None
     if shard:

@@ -64,3 +64,19 @@ def test_decomposed_more_ranks_than_rows():
     assert ref.shape[1] == 4
     got = forward_cpu_decomposed(x, w, cfg, 6)
     assert torch.equal(got, ref)
+
+
+def test_splitk_and_batch_shard_plans():
+    """Host-side plans of the full-network extension (pure arithmetic, no GPU)."""
+    from b200cnn.ops.ext import plan_splitk
+    from b200cnn.runners.full import batch_shard
+    # FC6 at batch 256 on 148 SMs: 2 x 16 tiles of 128x256 -> 4 splits of 72 k-blocks
+    assert plan_splitk(256, 4096, 256, 288, 148) == 4
+    assert plan_splitk(256, 1000, 256, 128, 148) == 16          # FC8: 8 tiles, capped by 8 k-blocks per split
+    assert plan_splitk(43264, 384, 256, 72, 148) == 1           # conv3 at batch 256 fills the GPU: no split
+    assert plan_splitk(64, 128, 128, 8, 148) == 1               # too few k-blocks to split
+    for batch, world in ((256, 8), (5, 2), (3, 8), (1, 4)):
+        parts = [batch_shard(batch, r, world) for r in range(world)]
+        assert parts[0][0] == 0 and parts[-1][1] == batch
+        assert all(a[1] == b[0] for a, b in zip(parts, parts[1:]))     # contiguous, disjoint, complete
+        assert all(0 <= b1 - b0 <= -(-batch // world) for b0, b1 in parts)
