@@ -450,11 +450,24 @@ struct SwParams {
     int direct;                                      // 1: B rows are cp.async'd straight from global memory
     int nstages;                                     // 2 (patch) or 3 (direct)
     int cpr;                                         // direct: 16 B chunks per filter row run (F*C/4)
+    int nkb_main;                                    // pixel-TMA mode: k-blocks fed by TMA (= F), rest by cp.async
+    uint32_t pix_bytes;                              // pixel-TMA mode: bytes of one pixel box (32 x TC x TR floats)
 };
 
+// Pixel-TMA mode (DRAFT, B200_TC_TMA1=1, not yet run on a GPU): one tensor map per input
+// row phase r = fy % S over an overlapping-stride view of the resident input,
+//   element (i, x, y, n) = in[n][S*y + r][x*S*C + i],  dims {32, Wc, rows/S, N},
+// so the first 32 floats of every pixel's filter-row run, for a whole TR x TC tile, are ONE box {32, TC, TR, 1}
+// that lands in the 128B-swizzled stage in pixel-slot order.
+struct alignas(64) PixMaps {
+    CUtensorMap m[4];
+};
+
+template <bool kPixTma>
 __global__ void __launch_bounds__(kSwThreads, 1)
 tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_constant__ SwParams sp,
-                        const float* __restrict__ bias, float* __restrict__ out) {
+                        const float* __restrict__ bias, float* __restrict__ out,
+                        const __grid_constant__ PixMaps pm) {
     extern __shared__ uint8_t smem_raw[];
     const TcParams& p = sp.t;
     const b200_block_geom& g = p.g;
@@ -477,7 +490,7 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
         for (int s = 0; s < NS; ++s) {
-            mbar_init(full_bar + 8 * s, (sp.direct ? kProducerThreads : kProducerWarps) + 1);
+            mbar_init(full_bar + 8 * s, ((sp.direct && !kPixTma) ? kProducerThreads : kProducerWarps) + 1);
             mbar_init(empty_bar + 8 * s, 1);
         }
         for (int b = 0; b < 2; ++b) {
@@ -545,6 +558,31 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                     const bool ok = pij[i] >= 0 && (cr0 + pi) < g.Hc && (cc0 + pj) < g.Wc;
                     hsel[i] = ok ? pi * g.S : -1;
                     xb[i] = ((cc0 + pj) * g.S - g.P) * g.C * 4;
+                }
+                if (kPixTma) {
+                    // k-blocks [0, nkb_main) arrive by TMA (warp 9); the producers only keep the barrier
+                    // counts uniform there.  The tail k-blocks hold floats 32.. of every run: chunk j of tail
+                    // block t is the 16 B at run offset 128 B of filter row 8t + j.
+                    for (int kb = 0; kb < p.nkb; ++kb) {
+                        mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+                        if (kb >= sp.nkb_main) {
+                            const uint32_t a_dst = base + stage * kAStageBytes + dst0;
+                            const int tfy = 8 * (kb - sp.nkb_main) + j;
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) {
+                                if (i >= 4 * p.nacc) break;
+                                const char* rp = (tfy < g.F && hsel[i] >= 0)
+                                                     ? reinterpret_cast<const char*>(rowtab[hsel[i] + tfy]) : nullptr;
+                                cp_async16(a_dst + i * 4096u, rp + (xb[i] + 128), rp ? 16u : 0u);
+                            }
+                            cp_async_wait_all();
+                            fence_proxy_async_smem();
+                        }
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(full_bar + 8 * stage);
+                        if (++stage == NS) { stage = 0; phase ^= 1; }
+                    }
+                    continue;
                 }
                 int fy = 0, ch = j;                             // this thread's chunk: run fy, chunk ch in run
                 while (ch >= sp.cpr) { ch -= sp.cpr; ++fy; }
@@ -640,11 +678,26 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
         int stage = 0;
         uint32_t phase = 0;
         for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
+            int pn = 0, pcr0 = 0, pcc0 = 0;                     // pixel-TMA mode: image, conv-row/col origin of the tile
+            if (kPixTma) {
+                pn = (int)(w / tiles_per_img);
+                const int rem = (int)(w - (long long)pn * tiles_per_img);
+                const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
+                pcr0 = 2 * (g.p0 + tr_i * p.PR);
+                pcc0 = 2 * (tc_i * p.PC);
+            }
             for (int kb = 0; kb < p.nkb; ++kb) {
                 mbar_wait(empty_bar + 8 * stage, phase ^ 1);
                 if (lane == 0) {
                     const uint32_t fb = full_bar + 8 * stage;
-                    mbar_arrive_expect_tx(fb, (uint32_t)(KO * 128));
+                    if (kPixTma && kb < sp.nkb_main) {
+                        // filter row fy = kb: input row S*(cr0+pi) + fy = S*(cr0 + pi + fy/S) + fy%S
+                        mbar_arrive_expect_tx(fb, (uint32_t)(KO * 128) + sp.pix_bytes);
+                        tma_load_4d(base + stage * kAStageBytes, &pm.m[kb % g.S], 0, pcc0,
+                                    pcr0 + kb / g.S - g.seg[0].base / g.S, pn, fb);
+                    } else {
+                        mbar_arrive_expect_tx(fb, (uint32_t)(KO * 128));
+                    }
                     tma_load_2d(base + w_off + stage * kSwWStageBytes, &tmapW, kb * kBlockK, 0, fb);
                 }
                 __syncwarp();
@@ -1019,6 +1072,11 @@ struct TcConv {
     int K, C, F, Kpad, device, patch_mode, FCpad;
     float* d_w;
     CUtensorMap tmap;
+    // pixel-TMA mode (draft): weights in the K order (fy | run floats 0..31), then tail blocks (8 filter rows x
+    // 4 floats from run offset 32); 0 k-blocks when the shape does not qualify
+    int nkb_tma;
+    float* d_w_tma;
+    CUtensorMap tmap_tma;
 };
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
@@ -1204,6 +1262,42 @@ size_t smem_bytes_db(const DbParams& dp) {
     return 1024 + (size_t)dp.db_ctl_off + 112 + kRowTab * 8 + kMaxPooled * 8 + (size_t)dp.t.g.K * 4 + 64;
 }
 
+// pixel-TMA mode: turn a direct-mode plan into a TMA-fed one and encode the S row-phase maps.  Returns false
+// (leave sp untouched) when the shape, the geometry or the driver does not take it.
+bool try_pixel_tma(const TcConv* t, const b200_block_geom* g, SwParams* sp, PixMaps* pm) {
+    if (!getenv("B200_TC_TMA1") || !sp->direct || t->nkb_tma == 0 || g->nseg != 1 || g->seg[0].flag) return false;
+    if (g->S < 1 || g->S > 4 || g->seg[0].base % g->S != 0 || g->P != 0) return false;
+    const TcParams& p = sp->t;
+    if (p.TC > 256 || p.TR > 256) return false;
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return false;
+    const int pitch = g->in_pitch ? g->in_pitch : g->W * g->C;
+    const int slab = g->seg[0].slab;
+    if ((pitch * 4) % 16 != 0 || ((long long)slab * pitch * 4) % 16 != 0) return false;
+    PixMaps maps;
+    for (int r = 0; r < g->S; ++r) {
+        const int rows = slab > r ? (slab - r + g->S - 1) / g->S : 0;
+        if (rows == 0) return false;
+        cuuint64_t dims[4] = {(cuuint64_t)kBlockK, (cuuint64_t)g->Wc, (cuuint64_t)rows, (cuuint64_t)g->N};
+        cuuint64_t strides[3] = {(cuuint64_t)g->S * g->C * 4, (cuuint64_t)g->S * pitch * 4,
+                                 (cuuint64_t)slab * pitch * 4};
+        cuuint32_t box[4] = {(cuuint32_t)kBlockK, (cuuint32_t)p.TC, (cuuint32_t)p.TR, 1};
+        cuuint32_t estr[4] = {1, 1, 1, 1};
+        void* base = (void*)(g->seg[0].ptr + (size_t)r * pitch);
+        if (enc(&maps.m[r], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, dims, strides, box, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+            return false;                                            // e.g. overlapping strides refused
+    }
+    for (int r = g->S; r < 4; ++r) maps.m[r] = maps.m[0];
+    *pm = maps;
+    sp->direct = 2;
+    sp->nkb_main = g->F;
+    sp->pix_bytes = (uint32_t)(kBlockK * p.TC * p.TR * 4);
+    sp->t.nkb = t->nkb_tma;
+    return true;
+}
+
 size_t smem_bytes_swapped(const SwParams& sp) {
     return 1024 + (size_t)sp.sw_ctl_off + 112 + kRowTab * 8 + 128 * 4 + 64;
 }
@@ -1252,6 +1346,33 @@ extern "C" int b200_tc_conv_create(const float* w_kcff, int K, int C, int F, voi
         delete t;
         return B200_ERR_CUDA;
     }
+    // pixel-TMA K order: only for runs of 33..36 floats (one 16 B tail chunk per filter row), K_out <= 128
+    t->nkb_tma = 0;
+    t->d_w_tma = nullptr;
+    if (t->patch_mode && K <= 128 && F * C > kBlockK && t->FCpad <= kBlockK + 4) {
+        const int nkb = F + cdiv(F, 8);
+        const int kp = nkb * kBlockK;
+        std::vector<float> wt((size_t)K * kp, 0.f);
+        for (int k = 0; k < K; ++k)
+            for (int c = 0; c < C; ++c)
+                for (int fy = 0; fy < F; ++fy)
+                    for (int fx = 0; fx < F; ++fx) {
+                        const int idx = fx * C + c;                   // float inside the filter-row run
+                        const int kk = idx < kBlockK ? fy * kBlockK + idx
+                                                     : (F + fy / 8) * kBlockK + (fy % 8) * 4 + (idx - kBlockK);
+                        wt[(size_t)k * kp + kk] = host_tf32(w_kcff[(((size_t)k * C + c) * F + fy) * F + fx]);
+                    }
+        if (cudaMalloc(&t->d_w_tma, wt.size() * sizeof(float)) == cudaSuccess &&
+            cudaMemcpy(t->d_w_tma, wt.data(), wt.size() * sizeof(float), cudaMemcpyHostToDevice) == cudaSuccess) {
+            cuuint64_t d2[2] = {(cuuint64_t)kp, (cuuint64_t)K};
+            cuuint64_t s2[1] = {(cuuint64_t)kp * sizeof(float)};
+            if (enc(&t->tmap_tma, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, t->d_w_tma, d2, s2, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS)
+                t->nkb_tma = nkb;
+        }
+        (void)cudaGetLastError();                                     // optional path: never poison the error state
+    }
     *handle = t;
     return B200_OK;
 }
@@ -1260,6 +1381,7 @@ extern "C" int b200_tc_conv_destroy(void* handle) {
     TcConv* t = (TcConv*)handle;
     if (t) {
         cudaFree(t->d_w);
+        if (t->d_w_tma) cudaFree(t->d_w_tma);
         delete t;
     }
     return B200_OK;
@@ -1294,10 +1416,20 @@ extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const 
         memset(&sp, 0, sizeof(sp));
         if (fill_swapped(g, &sp, flags) == B200_OK) {       // else fall through to the generic kernel
             const size_t smem = smem_bytes_swapped(sp);
-            B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_swapped_kernel,
-                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             const unsigned grid = (unsigned)(sp.t.total_tiles < sms ? sp.t.total_tiles : sms);
-            tc_block_swapped_kernel<<<grid, kSwThreads, smem, (cudaStream_t)stream>>>(t->tmap, sp, bias, out);
+            PixMaps pm;
+            memset(&pm, 0, sizeof(pm));
+            if (try_pixel_tma(t, g, &sp, &pm)) {
+                B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_swapped_kernel<true>,
+                                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                tc_block_swapped_kernel<true><<<grid, kSwThreads, smem, (cudaStream_t)stream>>>(t->tmap_tma, sp, bias,
+                                                                                               out, pm);
+            } else {
+                B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_swapped_kernel<false>,
+                                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                tc_block_swapped_kernel<false><<<grid, kSwThreads, smem, (cudaStream_t)stream>>>(t->tmap, sp, bias,
+                                                                                                out, pm);
+            }
             B200_CUDA_TRY(cudaGetLastError());
             return B200_OK;
         }
