@@ -22,6 +22,9 @@ static int g_rank = 0, g_size = 1, g_init = 0;
 static char g_dir[512];
 static int* g_wfd;   /* g_wfd[d]: me -> d */
 static int* g_rfd;   /* g_rfd[s]: s -> me */
+static int* g_kfd;   /* g_kfd[s]: my own write end of s -> me, never written: keeps the fifo from reading EOF
+                        while the real writer has not opened it yet (a rank that finished MPI_Init early
+                        would otherwise see "no writer" = end of file in its first receive) */
 static pthread_mutex_t* g_wlock;
 
 typedef struct pend { int tag; int64_t n; char* data; struct pend* next; } pend;
@@ -149,9 +152,10 @@ int MPI_Init(int* argc, char*** argv) {
     if (d) snprintf(g_dir, sizeof g_dir, "%s", d);
     else snprintf(g_dir, sizeof g_dir, "/tmp/b200mpi_%s_%d", port ? port : "solo", (int)getuid());
     g_wfd = (int*)calloc(g_size, sizeof(int)); g_rfd = (int*)calloc(g_size, sizeof(int));
+    g_kfd = (int*)calloc(g_size, sizeof(int));
     g_wlock = (pthread_mutex_t*)calloc(g_size, sizeof(pthread_mutex_t));
     g_pending = (pend**)calloc(g_size, sizeof(pend*));
-    for (int i = 0; i < g_size; ++i) { pthread_mutex_init(&g_wlock[i], NULL); g_wfd[i] = g_rfd[i] = -1; }
+    for (int i = 0; i < g_size; ++i) { pthread_mutex_init(&g_wlock[i], NULL); g_wfd[i] = g_rfd[i] = g_kfd[i] = -1; }
     if (g_size > 1) {
         mkdir(g_dir, 0700);
         char p[600];
@@ -165,6 +169,7 @@ int MPI_Init(int* argc, char*** argv) {
             if (o == g_rank) continue;
             fifo_path(p, sizeof p, o, g_rank);
             g_rfd[o] = open(p, O_RDONLY | O_NONBLOCK); if (g_rfd[o] < 0) die("open fifo (r)");
+            g_kfd[o] = open(p, O_WRONLY | O_NONBLOCK); if (g_kfd[o] < 0) die("open fifo (keep-alive)");
         }
         for (int o = 0; o < g_size; ++o) {
             if (o == g_rank) continue;
@@ -186,7 +191,7 @@ int MPI_Finalize(void) {
     char p[600];
     for (int o = 0; o < g_size; ++o) {
         if (o == g_rank) continue;
-        close(g_wfd[o]); close(g_rfd[o]);
+        close(g_wfd[o]); close(g_rfd[o]); close(g_kfd[o]);
         fifo_path(p, sizeof p, o, g_rank); unlink(p);
     }
     if (g_size > 1) rmdir(g_dir);
