@@ -1067,6 +1067,248 @@ tc_block_db_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_const
     }
 }
 
+
+// ------------------------------------------ CTA-pair kernel (stride-1 layers, C % 32 == 0) ----
+// DRAFT, off by default (B200_TC_PAIR=1), not yet run on a GPU: DESIGN.md §6 step 1, second half.
+// tc_block_db_kernel overlaps the epilogue but streams the whole weight k-block (32 KB) into every SM for only
+// 128 pixels: 48 KB per 640 MMA cycles is more than an SM can take in from L2, and it runs at ~80 % of the
+// MMA rate.  Here two CTAs of a cluster form a tcgen05 pair (cta_group::2): each stages its own 128 pixel rows
+// (A) and HALF of the weight rows (B), the leader issues one M=256 x N x K8 MMA per k-step for both, and each
+// CTA finds its 128 x N accumulator in its own TMEM, double-buffered as in the db kernel.  The operands are
+// fed by TMA only: for a stride-1 convolution the im2col rows of a whole TR x TC tile for one filter tap and
+// 32 channels are the box {32, TC, TR, 1} of the NHWC activation at (c, x0+fx-P, y0+fy-P, n), zero-filled
+// outside the image — no producer warps, no row table.  Single-GPU geometries only for now (one local row
+// segment, no flags, no signals).
+//   warp 0: TMA issuer (both CTAs; bytes are counted on the leader's barrier)
+//   warp 1: TMEM owner (both CTAs) + MMA issuer (leader only)
+//   warps 2-5: epilogue of the CTA's own tile (TMEM lane quarter = warp % 4)
+constexpr int kPairThreads = 192;
+constexpr int kPairEpiWarp0 = 2;
+constexpr int kPairMaxStages = 5;                     // 5 x 32 KB of stages + epilogue buffers still fit
+
+struct PairParams {
+    TcParams t;                                          // nacc == 1 tiling (same as the db kernel)
+    uint32_t cbuf_off, pbuf_off, pair_ctl_off;
+    uint32_t a_box_bytes, b_half_bytes;                  // per CTA and k-block
+    uint32_t idesc2;                                     // M = 256
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kPairThreads, 1)
+tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_constant__ CUtensorMap tmapA,
+                     const __grid_constant__ PairParams pp, const float* __restrict__ bias,
+                     float* __restrict__ out) {
+    extern __shared__ uint8_t smem_raw[];
+    const TcParams& p = pp.t;
+    const b200_block_geom& g = p.g;
+    const int N = g.K;
+    const uint32_t rank = cluster_ctarank();                  // 0 = leader (even SM of the pair)
+
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
+    const int NS = p.stages;
+    const uint32_t b_off = NS * kDbAStageBytes;
+    const uint32_t full_bar = base + pp.pair_ctl_off;         // [8]  leader's copy is the live one
+    const uint32_t empty_bar = full_bar + 64;                 // [8]  per CTA (multicast commit)
+    const uint32_t tfull_bar = full_bar + 128;                // [2]  per CTA (multicast commit)
+    const uint32_t tempty_bar = full_bar + 144;               // [2]  leader's copy, 8 arrivals (4 warps x 2 CTAs)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + pp.pair_ctl_off + 160);
+    int2* ptab = reinterpret_cast<int2*>(gbase + pp.pair_ctl_off + 176);
+    float* s_bias = reinterpret_cast<float*>(gbase + pp.pair_ctl_off + 176 + kMaxPooled * 8);
+    float* cbuf0 = reinterpret_cast<float*>(gbase + pp.cbuf_off);
+    float* pbuf = reinterpret_cast<float*>(gbase + pp.pbuf_off);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NS; ++s) {
+            mbar_init(full_bar + 8 * s, 1);
+            mbar_init(empty_bar + 8 * s, 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(tfull_bar + 8 * b, 1);
+            mbar_init(tempty_bar + 8 * b, 8);
+        }
+        fence_mbar_init();
+    }
+    for (int i = threadIdx.x; i < N; i += kPairThreads) s_bias[i] = bias[i];
+    if (warp == 1) tmem_alloc2(smem_u32(tmem_slot), p.tmem_cols);
+    tc_fence_before();
+    cluster_sync_all();                                       // both CTAs' barriers and TMEM exist
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int tiles_per_img = p.tiles_r * p.tiles_c;
+    const long long npairs = gridDim.x >> 1, pair_id = blockIdx.x >> 1;
+
+    if (warp == 0) {
+        // ======================================= TMA issuer ==============================
+        int stage = 0;
+        uint32_t phase = 0;
+        for (long long pt = pair_id; 2 * pt < p.total_tiles; pt += npairs) {
+            long long w = 2 * pt + rank;
+            if (w >= p.total_tiles) w = p.total_tiles - 1;     // odd tile count: the partner's tile again
+            const int n = (int)(w / tiles_per_img);
+            const int rem = (int)(w - (long long)n * tiles_per_img);
+            const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
+            const int cr0 = 2 * (g.p0 + tr_i * p.PR), cc0 = 2 * (tc_i * p.PC);
+            int fy = 0, fx = 0, cch = 0;
+            for (int kb = 0; kb < p.nkb; ++kb) {
+                mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+                if (lane == 0) {
+                    const uint32_t fb = full_bar + 8 * stage;
+                    if (rank == 0) mbar_arrive_expect_tx(fb, 2u * (pp.a_box_bytes + pp.b_half_bytes));
+                    tma2_load_4d(base + stage * kDbAStageBytes, &tmapA, cch * kBlockK, cc0 * g.S + fx - g.P,
+                                 cr0 * g.S + fy - g.P, n, fb);
+                    tma2_load_2d(base + b_off + stage * pp.b_half_bytes, &tmapBh, kb * kBlockK,
+                                 (int)rank * (N / 2), fb);
+                }
+                __syncwarp();
+                if (++fx == g.F) { fx = 0; if (++fy == g.F) { fy = 0; ++cch; } }
+                if (++stage == NS) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        // ======================================= MMA issuer (leader CTA only) ============
+        if (rank == 0) {
+            int stage = 0, buf = 0;
+            uint32_t phase = 0, bphase = 0;
+            for (long long pt = pair_id; 2 * pt < p.total_tiles; pt += npairs) {
+                mbar_wait(tempty_bar + 8 * buf, bphase ^ 1);    // both CTAs' epilogues have drained this buffer
+                tc_fence_after();
+                for (int kb = 0; kb < p.nkb; ++kb) {
+                    mbar_wait(full_bar + 8 * stage, phase);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint64_t da = make_smem_desc(base + stage * kDbAStageBytes);
+                        const uint64_t db = make_smem_desc(base + b_off + stage * pp.b_half_bytes);
+#pragma unroll
+                        for (int ks = 0; ks < kBlockK / 8; ++ks)
+                            umma2_tf32(tmem_base + (uint32_t)(buf * N), da + 2 * ks, db + 2 * ks, pp.idesc2,
+                                       (kb | ks) != 0 ? 1u : 0u);
+                        umma2_commit_mc(empty_bar + 8 * stage, 3);       // frees the stage in both CTAs
+                        if (kb == p.nkb - 1) umma2_commit_mc(tfull_bar + 8 * buf, 3);
+                    }
+                    __syncwarp();
+                    if (++stage == NS) { stage = 0; phase ^= 1; }
+                }
+                if (++buf == 2) { buf = 0; bphase ^= 1; }
+            }
+        }
+    } else {
+        // ======================================= epilogue warps ==========================
+        const int q = warp & 3;
+        const int we = warp - kPairEpiWarp0, te = we * 32 + lane;
+        const int row = q * 32 + lane;
+        const int PP = p.PR * p.PC, nchunk = N / 32, NP = N + 4;
+        const bool do_lrn = g.lrn.N_lrn > 0;
+        if (te < PP) {
+            const int pi = te / p.PC, pj = te - pi * p.PC;
+            ptab[te] = make_int2(((2 * pi) * p.TC + 2 * pj) * kCbufPitch, (pi << 16) | pj);
+        }
+        if (do_lrn)
+            for (int i = te; i < PP * 4; i += 128)
+                pbuf[(i >> 2) * NP + ((i & 3) < 2 ? (i & 3) : N + (i & 3))] = 0.f;
+        bar_epilogue();
+        const int half = g.lrn.N_lrn / 2;
+        const float al = g.lrn.mode == B200_LRN_ALPHA_OVER_N ? g.lrn.alpha / (float)max(g.lrn.N_lrn, 1) : g.lrn.alpha;
+        const float nbeta = -g.lrn.beta;
+        const bool win5 = g.lrn.N_lrn == 5;
+        int buf = 0;
+        uint32_t bphase = 0;
+        for (long long pt = pair_id; 2 * pt < p.total_tiles; pt += npairs) {
+            const long long w = 2 * pt + rank;
+            const bool valid = w < p.total_tiles;               // CTA-uniform
+            mbar_wait(tfull_bar + 8 * buf, bphase);
+            tc_fence_after();
+            if (!valid) {                                       // duplicate of the partner's tile: drop it
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_leader(tempty_bar + 8 * buf);
+                if (++buf == 2) { buf = 0; bphase ^= 1; }
+                continue;
+            }
+            const int n = (int)(w / tiles_per_img);
+            const int rem = (int)(w - (long long)n * tiles_per_img);
+            const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
+            const int pr0 = g.p0 + tr_i * p.PR, pc0 = tc_i * p.PC;
+            for (int cc = 0; cc < nchunk; ++cc) {
+                float* cb = cbuf0 + (cc & 1) * (kDbCbufBytes / 4);
+                uint32_t r[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * N + cc * 32), r);
+#pragma unroll
+                for (int c = 0; c < 32; ++c) cb[row * kCbufPitch + c] = __uint_as_float(r[c]);
+                bar_epilogue();
+                const float bch = s_bias[cc * 32 + lane];
+                for (int ppx = we; ppx < PP; ppx += 4) {
+                    const int2 e = ptab[ppx];
+                    const float* c0p = cb + e.x + lane;
+                    float mx = -INFINITY;
+#pragma unroll
+                    for (int a = 0; a < 3; ++a)
+#pragma unroll
+                        for (int b = 0; b < 3; ++b) mx = fmaxf(mx, c0p[(a * p.TC + b) * kCbufPitch]);
+                    float val = fmaxf(mx + bch, 0.f);
+                    if (do_lrn) {
+                        pbuf[ppx * NP + 2 + cc * 32 + lane] = val;
+                    } else {
+                        const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
+                        if (p.round_out) val = to_tf32(val);
+                        if (pr < g.p1 && pr < g.Hp && pc < g.Wp)
+                            out[(((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N + cc * 32 + lane] = val;
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(tempty_bar + 8 * buf);   // accumulator back before the LRN pass
+            if (do_lrn) {
+                bar_epilogue();
+                for (int pp0 = 0; pp0 < PP; pp0 += 4) {
+                    float* optr[4];
+                    const float* prow[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int ppx = pp0 + u < PP ? pp0 + u : PP - 1;
+                        const int2 e = ptab[ppx];
+                        const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
+                        const bool ok = pp0 + u < PP && pr < g.p1 && pr < g.Hp && pc < g.Wp;
+                        optr[u] = ok ? out + (((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N : nullptr;
+                        prow[u] = pbuf + ppx * NP;
+                    }
+                    for (int c = te; c < N; c += 128) {
+                        float val[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const float* px = prow[u] + c;
+                            float ss;
+                            if (win5) {
+                                const float a0 = px[0], a1 = px[1], a2 = px[2], a3 = px[3], a4 = px[4];
+                                ss = fmaf(a0, a0, fmaf(a1, a1, fmaf(a2, a2, fmaf(a3, a3, a4 * a4))));
+                            } else {
+                                ss = 0.f;
+                                const int c_lo = max(0, c - half), c_hi = min(N - 1, c + half);
+                                for (int qq = c_lo; qq <= c_hi; ++qq) ss = fmaf(prow[u][qq + 2], prow[u][qq + 2], ss);
+                            }
+                            val[u] = px[2] * exp2f(nbeta * __log2f(g.lrn.k + al * ss));
+                            if (p.round_out) val[u] = to_tf32(val[u]);
+                        }
+#pragma unroll
+                        for (int u = 0; u < 4; ++u)
+                            if (optr[u]) optr[u][c] = val[u];
+                    }
+                }
+            }
+            bar_epilogue();
+            if (++buf == 2) { buf = 0; bphase ^= 1; }
+        }
+    }
+
+    tc_fence_before();
+    cluster_sync_all();                                       // both CTAs are done with both TMEMs and barriers
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc2(tmem_base, p.tmem_cols);
+    }
+}
+
 // --------------------------------------------------------------------------- host ----
 struct TcConv {
     int K, C, F, Kpad, device, patch_mode, FCpad;
@@ -1077,6 +1319,9 @@ struct TcConv {
     int nkb_tma;
     float* d_w_tma;
     CUtensorMap tmap_tma;
+    // CTA-pair kernel (draft): the same vec-mode weights with a TMA box of K/2 rows (one half per CTA)
+    int half_ok;
+    CUtensorMap tmap_half;
 };
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
@@ -1298,6 +1543,58 @@ bool try_pixel_tma(const TcConv* t, const b200_block_geom* g, SwParams* sp, PixM
     return true;
 }
 
+// CTA-pair kernel: layout [A stages | B half stages | 2 cbuf | pbuf | ctl]
+inline bool pair_requested(const b200_block_geom* g) {
+    return !is_patch_mode(g->C) && getenv("B200_TC_PAIR") != nullptr;
+}
+
+int fill_pair(const TcConv* t, const b200_block_geom* g, PairParams* pp, CUtensorMap* tmapA, int flags) {
+    if (is_patch_mode(g->C) || !t->half_ok || g->S != 1) return B200_ERR_UNSUPPORTED;
+    // first version: one local row segment that is the whole image, no cross-GPU flags or signals
+    if (g->nseg != 1 || g->seg[0].flag || g->n_signal != 0 || g->seg[0].base != 0 || g->seg[0].slab != g->H ||
+        g->seg[0].lo > 0 || g->seg[0].hi < g->H)
+        return B200_ERR_UNSUPPORTED;
+    int rc = fill_params(g, &pp->t, flags, /*max_nacc=*/1);
+    if (rc != B200_OK) return rc;
+    TcParams& p = pp->t;
+    if (p.TC > 256 || p.TR > 256) return B200_ERR_UNSUPPORTED;
+    pp->b_half_bytes = (uint32_t)(g->K / 2) * 128u;
+    pp->a_box_bytes = (uint32_t)(kBlockK * p.TC * p.TR * 4);
+    const size_t pbuf_bytes = g->lrn.N_lrn > 0 ? (size_t)p.PR * p.PC * (g->K + 4) * 4 : 0;
+    const size_t epi = 2 * (size_t)kDbCbufBytes + ((pbuf_bytes + 15) & ~(size_t)15);
+    const size_t ctl = 176 + kMaxPooled * 8 + (size_t)g->K * 4 + 64;
+    const size_t stage_bytes = (size_t)kDbAStageBytes + pp->b_half_bytes;
+    const long avail = 226 * 1024 - 1024 - (long)epi - (long)ctl;
+    int stages = (int)(avail / (long)stage_bytes);
+    if (stages > kPairMaxStages) stages = kPairMaxStages;
+    if (stages < 2) return B200_ERR_UNSUPPORTED;
+    p.stages = stages;
+    pp->cbuf_off = (uint32_t)(stages * stage_bytes);
+    pp->pbuf_off = pp->cbuf_off + 2 * kDbCbufBytes;
+    pp->pair_ctl_off = (uint32_t)(stages * stage_bytes + epi);
+    int cols = 32;
+    while (cols < 2 * g->K) cols *= 2;
+    p.tmem_cols = cols;
+    pp->idesc2 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(g->K >> 3) << 17) | ((256u >> 4) << 24);
+    // A operand: the NHWC activation itself, box = one filter tap x 32 channels of a whole TR x TC tile
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return B200_ERR_UNSUPPORTED;
+    const int pitch = g->in_pitch ? g->in_pitch : g->W * g->C;
+    cuuint64_t dims[4] = {(cuuint64_t)g->C, (cuuint64_t)g->W, (cuuint64_t)g->H, (cuuint64_t)g->N};
+    cuuint64_t strides[3] = {(cuuint64_t)g->C * 4, (cuuint64_t)pitch * 4, (cuuint64_t)g->seg[0].slab * pitch * 4};
+    cuuint32_t box[4] = {(cuuint32_t)kBlockK, (cuuint32_t)p.TC, (cuuint32_t)p.TR, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    if (enc(tmapA, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)g->seg[0].ptr, dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return B200_ERR_UNSUPPORTED;
+    return B200_OK;
+}
+
+size_t smem_bytes_pair(const PairParams& pp) {
+    return 1024 + (size_t)pp.pair_ctl_off + 176 + kMaxPooled * 8 + (size_t)pp.t.g.K * 4 + 64;
+}
+
 size_t smem_bytes_swapped(const SwParams& sp) {
     return 1024 + (size_t)sp.sw_ctl_off + 112 + kRowTab * 8 + 128 * 4 + 64;
 }
@@ -1346,6 +1643,14 @@ extern "C" int b200_tc_conv_create(const float* w_kcff, int K, int C, int F, voi
         delete t;
         return B200_ERR_CUDA;
     }
+    t->half_ok = 0;
+    if (!t->patch_mode && K % 16 == 0 && K <= 256) {
+        cuuint32_t hbox[2] = {(cuuint32_t)kBlockK, (cuuint32_t)(K / 2)};
+        if (enc(&t->tmap_half, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, t->d_w, dims, strides, hbox, estr,
+                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS)
+            t->half_ok = 1;
+    }
     // pixel-TMA K order: only for runs of 33..36 floats (one 16 B tail chunk per filter row), K_out <= 128
     t->nkb_tma = 0;
     t->d_w_tma = nullptr;
@@ -1390,7 +1695,7 @@ extern "C" int b200_tc_conv_destroy(void* handle) {
 extern "C" int b200_tc_block_tiles(const b200_block_geom* g) {
     if (!g) return B200_ERR_ARG;
     if (g->p1 <= g->p0) return 0;
-    if (db_requested(g)) {                             // same tiling the launch will use
+    if (db_requested(g) || pair_requested(g)) {        // same tiling the launch will use
         DbParams dp;
         if (fill_db(g, &dp, 0) == B200_OK) return dp.t.tiles_r * dp.t.tiles_c;
     }
@@ -1430,6 +1735,22 @@ extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const 
                 tc_block_swapped_kernel<false><<<grid, kSwThreads, smem, (cudaStream_t)stream>>>(t->tmap, sp, bias,
                                                                                                 out, pm);
             }
+            B200_CUDA_TRY(cudaGetLastError());
+            return B200_OK;
+        }
+    }
+    if (pair_requested(g)) {
+        PairParams pp;
+        CUtensorMap tmapA;
+        memset(&pp, 0, sizeof(pp));
+        if (fill_pair(t, g, &pp, &tmapA, flags) == B200_OK) {   // else fall through
+            const size_t smem = smem_bytes_pair(pp);
+            B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               (int)smem));
+            long long ctas = 2 * ((pp.t.total_tiles + 1) / 2);
+            if (ctas > (sms & ~1)) ctas = sms & ~1;
+            tc_block_pair_kernel<<<(unsigned)ctas, kPairThreads, smem, (cudaStream_t)stream>>>(t->tmap_half, tmapA, pp,
+                                                                                              bias, out);
             B200_CUDA_TRY(cudaGetLastError());
             return B200_OK;
         }
