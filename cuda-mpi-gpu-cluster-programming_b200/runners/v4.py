@@ -83,11 +83,17 @@ def _oversubscribed(ns, cfg, variant, scatter) -> int:
     part in the barriers.  Output and log lines are identical to a real multi-GPU run."""
     from ..models.engine import EmulatedWorld
     ctx = bdist.init(device="cpu")
+    if ctx.rank == 0:
+        # same footing as the one-GPU-per-rank path, where bdist.init() selects the device (CUDA 12 creates the
+        # primary context there) and the data is generated before the timed region opens
+        torch.cuda.set_device(0)
+        from ..ops import cuda as cu
+        cu.lib()
+        x, w = make_problem(cfg)
     ctx.barrier()
     t0 = time.perf_counter()
     y = None
     if ctx.rank == 0:
-        x, w = make_problem(cfg)
         ew = EmulatedWorld(cfg, w, ctx.world, "cuda:0", precision=cfg.precision, strategy=ns.strategy,
                            scatter=scatter)
         y = ew.forward(x.pin_memory().to("cuda:0", non_blocking=True)).cpu()
