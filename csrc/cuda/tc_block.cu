@@ -1644,7 +1644,7 @@ extern "C" int b200_tc_conv_create(const float* w_kcff, int K, int C, int F, voi
         return B200_ERR_CUDA;
     }
     t->half_ok = 0;
-    if (!t->patch_mode && K % 16 == 0 && K <= 256) {
+    if (!t->patch_mode && K % 16 == 0 && K <= 256 && getenv("B200_TC_PAIR")) {   // draft path: opt-in at create time too
         cuuint32_t hbox[2] = {(cuuint32_t)kBlockK, (cuuint32_t)(K / 2)};
         if (enc(&t->tmap_half, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, t->d_w, dims, strides, hbox, estr,
                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -1654,7 +1654,7 @@ extern "C" int b200_tc_conv_create(const float* w_kcff, int K, int C, int F, voi
     // pixel-TMA K order: only for runs of 33..36 floats (one 16 B tail chunk per filter row), K_out <= 128
     t->nkb_tma = 0;
     t->d_w_tma = nullptr;
-    if (t->patch_mode && K <= 128 && F * C > kBlockK && t->FCpad <= kBlockK + 4) {
+    if (t->patch_mode && K <= 128 && F * C > kBlockK && t->FCpad <= kBlockK + 4 && getenv("B200_TC_TMA1")) {
         const int nkb = F + cdiv(F, 8);
         const int kp = nkb * kBlockK;
         std::vector<float> wt((size_t)K * kp, 0.f);
