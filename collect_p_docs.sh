@@ -3,7 +3,8 @@
 set -euo pipefail
 ROOT="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"; OUT="${1:-$ROOT/docs_bundle.md}"
 : > "$OUT"
-for f in README.md DESIGN.md INTEGRATION.md BASELINE.md homeworks/hw1/summary.md; do
+for f in README.md final_project/README.md final_project/docs/AlexNet_B200_Design.md DESIGN.md INTEGRATION.md \
+         COMPONENTS.md BASELINE.md profiles/README.md profiles/ROOFLINE.md homeworks/hw1/summary.md; do
   [ -f "$ROOT/$f" ] && { printf '\n\n<!-- %s -->\n\n' "$f" >> "$OUT"; cat "$ROOT/$f" >> "$OUT"; }
 done
 echo "wrote $OUT"
