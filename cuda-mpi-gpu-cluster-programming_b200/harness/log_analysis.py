@@ -119,9 +119,14 @@ class Warehouse:
     def df(self, sql: str) -> pd.DataFrame:
         return pd.read_sql_query(sql, self.con)
 
-    def run_stats(self) -> pd.DataFrame:
-        """mean, sample sd, 95 % CI, median, CV per (version, np) (ref run_stats view + scorecard)."""
+    def run_stats(self, canonical: bool = False) -> pd.DataFrame:
+        """mean, sample sd, 95 % CI, median, CV per (version, np) (ref run_stats view + scorecard).
+        ``canonical``: map version labels through :func:`canonical_version_name` first, so that harness CSV
+        rows ("V2 2.2-scatter-halo") and run-log rows ("v2_2_2_scatter_halo_np4") pool into one group, as the
+        reference's notebook does (ref analysis.md:70-99)."""
         d = self.df("SELECT version, np, total_time_s FROM perf_runs")
+        if canonical and not d.empty:
+            d["version"] = d.version.map(canonical_version_name)
         if d.empty:
             return pd.DataFrame(columns=["version", "np", "n", "mean_s", "sd_s", "ci95_s", "median_s", "cv"])
         g = d.groupby(["version", "np"])["total_time_s"]
@@ -130,12 +135,15 @@ class Warehouse:
         out["cv"] = out["sd_s"] / out["mean_s"]
         return out[["version", "np", "n", "mean_s", "sd_s", "ci95_s", "median_s", "cv"]]
 
-    def speedup(self, stat: str = "best") -> pd.DataFrame:
+    def speedup(self, stat: str = "best", canonical: bool = False) -> pd.DataFrame:
         """S = T1(V1 Serial, np=1) / T(version, np); E = S / np (ref :213-222)."""
         if stat == "best":
             b = self.df("SELECT version, np, total_time_s AS t FROM best_runs")
+            if canonical and not b.empty:
+                b["version"] = b.version.map(canonical_version_name)
+                b = b.groupby(["version", "np"], as_index=False)["t"].min()
         else:
-            b = self.run_stats().rename(columns={"median_s": "t"})[["version", "np", "t"]]
+            b = self.run_stats(canonical).rename(columns={"median_s": "t"})[["version", "np", "t"]]
         base = b[(b.version == "V1 Serial") & (b.np == 1)]
         if base.empty:
             raise SystemExit("no 'V1 Serial' np=1 run in the warehouse: speed-up has no baseline")
@@ -308,8 +316,8 @@ def main(argv=None) -> int:
     elif ns.cmd == "speedup":
         print(wh.speedup(ns.stat).to_string(index=False))
     elif ns.cmd == "scorecard":
-        st = wh.run_stats()
-        sp = wh.speedup("median")[["version", "np", "S", "E"]]
+        st = wh.run_stats(canonical=True)
+        sp = wh.speedup("median", canonical=True)[["version", "np", "S", "E"]]
         print(st.merge(sp, on=["version", "np"], how="left").sort_values(["version", "np"]).to_string(index=False))
     elif ns.cmd == "locperf":
         # lines of code per version directory vs its best time (ref analysis.md "LOC vs performance")
