@@ -105,3 +105,18 @@ def test_v1_python_runner_equals_native_binary(tmp_path):
     f = lambda t: re.search(r"Output FNV1a64: (0x[0-9a-f]+)", t).group(1)
     assert f(nat) == f(py)
     assert nat.splitlines()[0] == py.splitlines()[0] == "--- AlexNet Serial CPU Version (V1) ---"
+
+
+def test_scorecard_pools_canonical_names(tmp_path):
+    """Harness CSV labels and run-log tags of the same version land in one (version, np) group."""
+    root = _make_tree(tmp_path)
+    wh = la.Warehouse(tmp_path / "wh.sqlite")
+    wh.ingest(root)
+    raw = wh.run_stats().set_index(["version", "np"])
+    assert ("v4", 2) in raw.index and ("V4 MPI+CUDA", 1) in raw.index          # separate labels
+    st = wh.run_stats(canonical=True).set_index(["version", "np"])
+    assert ("V4 MPI+CUDA", 2) in st.index and ("v4", 2) not in st.index
+    assert st.loc[("V1 Serial", 1), "n"] == 2                                  # the two CSV rows (V1's log has no np != 1 row)
+    sp = wh.speedup("median", canonical=True).set_index(["version", "np"])
+    assert abs(sp.loc[("V2.2 ScatterHalo", 4), "S"] - 0.78 / 0.25) < 1e-9
+    assert abs(sp.loc[("V4 MPI+CUDA", 2), "E"] - 0.78 / 0.1505 / 2) < 1e-9
