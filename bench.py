@@ -174,48 +174,9 @@ def run_ours(a):
     # used only if its output is bit-identical to the single-buffered kernel's and it is faster
     conv2_info = None
     os.environ.pop("B200_TC_DB", None)
-    if N == 1 and precision == "tf32" and a.conv2_kernel != "single":
-        def probe(db):
-            if db:
-                os.environ["B200_TC_DB"] = "1"
-            else:
-                os.environ.pop("B200_TC_DB", None)
-            s_ = Session(cfg, w, device=dev, precision=precision, strategy="halo", scatter=a.scatter)
-            e_ = s_.engine
-            lo_, hi_ = s_.input_rows
-            e_.input_view(0).copy_(x[:, lo_:hi_].to(dev))
-            y_ = e_.forward_enqueue(0, 0).clone()
-            for _ in range(3):
-                e_.forward_enqueue(0, 0)
-            torch.cuda.synchronize(dev)
-            t0_, t1_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            t0_.record()
-            for _ in range(5):
-                e_.forward_enqueue(0, 0)
-            t1_.record()
-            t1_.synchronize()
-            y2_ = e_.forward_enqueue(0, 0).clone()          # graph replay, several tiles per CTA behind it
-            e_.check_status()
-            ok_ = bool(torch.equal(y_, y2_))
-            del s_, e_
-            return y_, t0_.elapsed_time(t1_) / 5, ok_
-        try:
-            y_s, ms_s, _ = probe(False)
-            y_d, ms_d, stable = probe(True)
-            same = bool(torch.equal(y_s, y_d)) and stable
-            use_db = same and (a.conv2_kernel == "double" or ms_d < ms_s)
-            conv2_info = {"single_buffered_forward_ms": round(ms_s, 4),
-                          "double_buffered_forward_ms": round(ms_d, 4), "bit_identical": same,
-                          "used": "double_buffered" if use_db else "single_buffered"}
-            del y_s, y_d
-        except Exception as ex:                   # any host-side problem: stay on the validated kernel
-            use_db = False
-            conv2_info = {"used": "single_buffered", "error": str(ex)[:200]}
-        if use_db:
-            os.environ["B200_TC_DB"] = "1"
-        else:
-            os.environ.pop("B200_TC_DB", None)
-        torch.cuda.empty_cache()
+    if N == 1 and precision == "tf32":
+        from b200cnn.models.session import autotune_conv2_kernel
+        conv2_info = autotune_conv2_kernel(cfg, w, x, device=dev, prefer=a.conv2_kernel)
 
     tuned = None
     if a.strategy == "auto":
