@@ -26,7 +26,14 @@ def cxx_float(v: float) -> str:
 
 
 def emit(line: str = "", file=None) -> None:
-    print(line, file=file or sys.stdout, flush=True)
+    try:
+        print(line, file=file or sys.stdout, flush=True)
+    except BrokenPipeError:           # `./template | head -3`: the reader is gone; keep running quietly
+        import os
+        try:
+            sys.stdout = open(os.devnull, "w")
+        except OSError:
+            pass
 
 
 # ---- V1 (ref v1_serial/src/main.cpp:14-75, alexnet_serial.cpp:61-185) ---------------------------
