@@ -124,7 +124,9 @@ class Orchestrator:
                 remaining -= k
         env = f"GLOO_SOCKET_IFNAME={self.iface} " if self.iface else ""
         for node, (h, k) in enumerate(placed):
-            cmd = (f"{env}python -m torch.distributed.run --nnodes {len(placed)} --node-rank {node} "
+            # torchrun pins every rank to ONE OpenMP thread unless told otherwise: give each its share of the host
+            omp = f"OMP_NUM_THREADS=$(( ($(nproc) + {k} - 1) / {k} )) "
+            cmd = (f"{env}{omp}python -m torch.distributed.run --nnodes {len(placed)} --node-rank {node} "
                    f"--nproc-per-node {k} --master-addr {master} --master-port 29555 -m {module} {args}")
             full = cmd if node == 0 else f"ssh {h.alias} 'cd {shlex.quote(REPO_ROOT)} && {cmd}'"
             self.sh(full + (" &" if node else ""), check=False)
