@@ -225,7 +225,7 @@ def run_ours(a):
                    "parallelism": f"spatial-rows{N}" if N > 1 else "single-gpu",
                    "strategy": a.strategy, "strategy_autotune_ms": tuned,
                    "scatter": a.scatter if N > 1 else "local", "p2p_scatter_images_per_s": p2p_alt,
-                   "conv2_kernel": conv2_info,
+                   "conv2_kernel": conv2_info, "host_binding": getattr(sess, "host_binding", None),
                    "l2": "flushed between timed iterations (256 MiB fill, untimed)"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "impl": "ours",
     }

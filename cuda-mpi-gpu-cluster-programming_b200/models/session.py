@@ -35,6 +35,9 @@ class Session:
                  precision: Optional[str] = None, strategy: str = "halo", scatter: str = "p2p"):
         self.cfg = cfg
         self.dist = dist
+        # run on the CPUs next to this GPU before any pinned buffer is touched (see utils/numa.py)
+        from ..utils.numa import bind_host_to_gpu
+        self.host_binding = bind_host_to_gpu(device or (dist.device if dist else "cuda:0"))
         world = dist.world if dist is not None else 1
         rank = dist.rank if dist is not None else 0
         if world > 1:
