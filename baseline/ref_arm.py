@@ -18,6 +18,8 @@ import statistics
 import subprocess
 import sys
 
+from bench_contract import METRIC, UNIT, HIGHER_IS_BETTER, SCALING, MODEL
+
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 V4_DIR = os.path.join(HERE, "_ref", "src", "final_project", "v4_mpi_cuda")
@@ -66,15 +68,17 @@ def main(a):
     val = 1000.0 / ms
     print(json.dumps({
         "impl": "reference",
-        "metric": "AlexNet blk1-2 images/s (reference's own wall-clock line, 1 image per run)",
-        "value": round(val, 3), "unit": "images/s", "n_gpus": N, "steps": a.steps, "warmup": a.warmup,
-        "ms_per_step": round(ms, 3), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "metric": METRIC,
+        "value": round(val, 3), "unit": UNIT, "n_gpus": N, "steps": a.steps, "warmup": a.warmup,
+        "ms_per_step": round(ms, 3), "higher_is_better": HIGHER_IS_BETTER, "scaling": SCALING, "vs_baseline": None,
         "dtype": "fp32", "data": "synthetic (constant init 1.0 / 0.01 / 0.0, as the reference hard-codes)",
-        "config": {"model": "AlexNet blocks 1-2 (reference V4 MPI+CUDA, unmodified, sm_100 rebuild)",
+        "config": {"model": MODEL, "implementation": "reference V4 MPI+CUDA, unmodified sources, sm_100 rebuild",
+                   "timed_region": "the reference's own wall-clock line: one 227x227x3 image per run, context creation, "
+                                   "cudaMalloc/cudaFree, pageable copies and MPI traffic included (it has no batch and no warm loop)",
                    "global_batch": 1, "input": "227x227x3", "parallelism": f"mpirun -np {N} (row scatter + host halo)",
                    "output_shape_printed": shape,
                    "note": "reference output rows shrink with np (13/8/4 at np 1/2/4): time only, not a correctness target"},
-        "e2e": {"value": round(val, 3), "unit": "images/s", "h2d_bytes_per_step": 3216748,
+        "e2e": {"value": round(val, 3), "unit": UNIT, "h2d_bytes_per_step": 3216748,
                 "d2h_bytes_per_step": 173056, "note": "the reference's timed region already contains its copies"},
         "gpu_launches": 7 * N, "median_ms": round(statistics.median(times), 3),
     }), flush=True)

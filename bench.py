@@ -26,6 +26,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+sys.path.insert(0, os.path.join(ROOT, "baseline"))
+from bench_contract import METRIC, UNIT, HIGHER_IS_BETTER, SCALING, MODEL  # noqa: E402  (shared with the reference arm)
+
 # Reference's published best V4 images/s per np (best_runs.csv:10-12; other HW).
 REF_V4_BEST_IMG_S = {1: 1 / 0.183, 2: 1 / 0.181, 4: 1 / 0.250}
 
@@ -214,13 +217,15 @@ def run_ours(a):
     value = a.batch / (ms_per_step / 1e3)
     base = REF_V4_BEST_IMG_S.get(N)
     line = {
-        "metric": "AlexNet blk1-2 images/s (device-timed, max over ranks)",
-        "value": round(value, 2), "unit": "images/s", "n_gpus": N, "steps": a.steps,
-        "warmup": a.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": round(value / base, 2) if base else None,
+        "metric": METRIC,
+        "value": round(value, 2), "unit": UNIT, "n_gpus": N, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": HIGHER_IS_BETTER,
+        "scaling": SCALING, "vs_baseline": round(value / base, 2) if base else None,
         "dtype": "tf32 (fp32 in/out, fp32 accumulate)" if precision == "tf32" else "fp32",
         "data": "synthetic (glibc rand() stream, seed 1), random-init weights",
-        "config": {"model": "AlexNet blocks 1-2 (conv1-relu-pool1-conv2-relu-pool2-lrn2)",
+        "config": {"model": MODEL, "implementation": "b200cnn (this repository)",
+                   "timed_region": "value: CUDA events around each forward, max over ranks; e2e: wall clock over pinned "
+                                   "H2D + forward + D2H of every step through Session",
                    "global_batch": a.batch, "input": f"{a.height}x{a.width}x3",
                    "parallelism": f"spatial-rows{N}" if N > 1 else "single-gpu",
                    "strategy": a.strategy, "strategy_autotune_ms": tuned,
