@@ -42,23 +42,29 @@ def parse():
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--height", type=int, default=227)
     ap.add_argument("--width", type=int, default=227)
-    ap.add_argument("--precision", choices=["tf32", "simt"], default=None)
-    ap.add_argument("--strategy", choices=["auto", "halo", "recompute"], default="auto",
-                    help="auto: time both decompositions for a few warm steps and keep the faster")
+    ap.add_argument("--precision", choices=["tf32", "simt"], default="tf32")
+    ap.add_argument("--strategy", choices=["halo", "recompute"], default="halo",
+                    help="halo (default): per-layer row ownership, boundary pool1 rows cross NVLink inside the fused "
+                         "kernels; recompute: overlapped tiling, no inter-layer traffic")
+    ap.add_argument("--row-groups", default="auto",
+                    help="auto: 2 row groups x N/2 batch groups; rows: pure row split over all N ranks; or a divisor of N")
     ap.add_argument("--scatter", choices=["p2p", "sharded"], default="sharded",
-                    help="device-timed run: where the images live.  sharded = every rank holds the rows it "
-                         "needs (they arrive by its own H2D in the e2e run); p2p = all images on rank 0, "
-                         "pulled over NVLink inside conv1 (reported as config.p2p_scatter_images_per_s)")
-    ap.add_argument("--e2e-scatter", choices=["p2p", "sharded"], default="sharded",
-                    help="end-to-end run: p2p = rank 0 feeds everything; sharded = each rank feeds its slab")
-    ap.add_argument("--e2e-strategy", choices=["same", "halo", "recompute"], default="halo",
-                    help="decomposition for the end-to-end run (halo = smallest input slabs = fewest H2D bytes)")
-    ap.add_argument("--conv2-kernel", choices=["auto", "single", "double"], default="auto",
-                    help="1 GPU: conv2 through tc_block_kernel (one 256-pixel tile fills TMEM) or tc_block_db_kernel "
-                         "(128-pixel tiles, double-buffered TMEM, own epilogue warps).  auto runs both on the bench "
-                         "input, requires bit-identical outputs and keeps the faster")
+                    help="where the images live.  sharded = every rank holds (and, end to end, uploads) the rows of the "
+                         "images it works on; p2p = all images on rank 0, pulled over NVLink inside conv1")
+    ap.add_argument("--e2e-gather", choices=["host", "rank0"], default="host",
+                    help="end-to-end run: host = every rank copies its rows into one shared pinned host tensor; rank0 = "
+                         "rows are stored into rank 0's device tensor over NVLink and rank 0 copies all of it")
+    ap.add_argument("--alt", action="store_true",
+                    help="also time the alternatives (p2p scatter, pure rows, recompute) for config.alternatives")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-check", action="store_true", help="skip the comparison with a one-rank forward")
     return ap.parse_args()
+
+
+def _row_groups(a, N):
+    if N == 1 or a.row_groups == "rows":
+        return None
+    return "auto" if a.row_groups == "auto" else int(a.row_groups)
 
 
 def run_ours(a):
@@ -75,31 +81,54 @@ def run_ours(a):
                                                    "and has no CPU path", "gpu_launches": 0}))
         sys.exit(2)
     ctx = bdist.init()
-    if ctx.world != a.gpus:
-        if ctx.is_root:
-            sys.stderr.write(f"bench: --gpus {a.gpus} but WORLD_SIZE={ctx.world}; using WORLD_SIZE\n")
+    if ctx.world != a.gpus and ctx.is_root:
+        sys.stderr.write(f"bench: --gpus {a.gpus} but WORLD_SIZE={ctx.world}; using WORLD_SIZE\n")
     N = ctx.world
     precision = a.precision
-    if precision is None:
-        try:
-            from b200cnn.ops import tc  # noqa: F401
-            precision = "tf32"
-        except ImportError:
-            precision = "simt"
+    if precision == "tf32":
+        from b200cnn.ops import tc  # noqa: F401   (raises if the tcgen05 kernels are not in the library)
     cfg = b200cnn.default_config(H=a.height, W=a.width, batch=a.batch, init=INIT_RAND, seed=1,
                                  precision=precision)
     x, w = make_problem(cfg)             # synthetic inputs, random-init weights (same on every rank)
     dev = ctx.device
     torch.cuda.set_device(dev)
+    rg = _row_groups(a, N)
+    dist_arg = ctx if N > 1 else None
+
+    def load_inputs(sess, nbuf):
+        xi = sess.my_input(x)
+        if xi is not None:
+            for i in range(nbuf):
+                sess.engine.input_view(i).copy_(xi.to(dev))
+
+    def check_against_one_rank(sess):
+        """Rank 0's gathered output must be bit-equal to a one-rank forward of the same input (the property
+        the reference's V2.2/V4 decomposition does not have).  Returns (ok, fnv)."""
+        from b200cnn.models.engine import single_gpu_engine
+        from b200cnn.ops.cpu import fnv1a64
+        load_inputs(sess, 1)
+        torch.cuda.synchronize(dev)
+        ctx.barrier()
+        y = sess.engine.forward_enqueue(0, 0)
+        sess.engine.check_status()
+        ok, fnv = True, None
+        if ctx.is_root:
+            y = y.clone()
+            one = single_gpu_engine(cfg, w, dev, precision)
+            ref = one.forward(x.to(dev))
+            one.check_status()
+            ok = bool(torch.equal(ref, y))
+            fnv = f"0x{fnv1a64(y.cpu()):016x}"
+            del one, ref
+            torch.cuda.empty_cache()
+        ctx.barrier()
+        return ctx.broadcast_object((ok, fnv), 0)
 
     def measure_device(sess):
         e = sess.engine
-        if e.in_rows > 0:
-            lo, hi = sess.input_rows
-            for i in range(2):
-                e.input_view(i).copy_(x[:, lo:hi].to(dev))
+        load_inputs(sess, 2)
         flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
-        for i in range(max(a.warmup, 4)):          # >= 2 calls per buffer parity: both CUDA graphs are
+        for i in range(max(a.warmup, 6)):          # >= 2 calls per buffer parity: both CUDA graphs are
             e.forward_enqueue(i % 2, i % 2)        # captured here, never inside the timed region
         torch.cuda.synchronize(dev)
         ctx.barrier()
@@ -117,7 +146,6 @@ def run_ours(a):
             evs.append((ev0, ev1))
         torch.cuda.synchronize(dev)
         total_ms = sum(a_.elapsed_time(b_) for a_, b_ in evs)
-        torch.cuda.synchronize(dev)
         ctx.barrier()
         clocks = sampler.stop()
         launches = e.launches - l0
@@ -125,94 +153,96 @@ def run_ours(a):
         del flush
         return ctx.max_float(total_ms), launches, clocks
 
+    def quick_ms(**kw):
+        """Warm device time per forward of an alternative configuration (no L2 flush; for config.alternatives)."""
+        s_ = Session(cfg, w, dist=dist_arg, device=dev, precision=precision, **kw)
+        load_inputs(s_, 1)
+        e_ = s_.engine
+        for _ in range(4):
+            e_.forward_enqueue(0, 0)
+        torch.cuda.synchronize(dev)
+        ctx.barrier()
+        e_.sync_ranks()
+        t0_, t1_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0_.record()
+        for _ in range(6):
+            e_.forward_enqueue(0, 0)
+        t1_.record()
+        t1_.synchronize()
+        ms_ = ctx.max_float(t0_.elapsed_time(t1_) / 6)
+        e_.check_status()
+        del s_, e_
+        torch.cuda.empty_cache()
+        return round(a.batch / (ms_ / 1e3), 1)
+
     def measure_e2e(sess):
-        e = sess.engine
-        lo, hi = sess.input_rows
-        hx = None
-        if e.in_rows > 0:
-            hx = [x[:, lo:hi].contiguous().pin_memory() for _ in range(2)]
-        for i in range(max(a.warmup, 4)):
-            sess.submit(hx[i % 2] if hx else None)
+        """Wall clock over K steps through Session.submit/result: every step uploads its input from pinned host
+        memory and brings its result back to (pinned) host memory; <= 3 steps in flight, results consumed in order."""
+        xi = sess.my_input(x)
+        hx = [xi.contiguous().pin_memory() for _ in range(2)] if xi is not None else None
+        for i in range(max(a.warmup, 2 * sess.slots)):
+            sess.result(sess.submit(hx[i % 2] if hx else None))
         sess.drain()
         ctx.barrier()
         torch.cuda.synchronize(dev)
         t0 = time.perf_counter()
-        tickets = []
+        tickets, last = [], None
         for i in range(a.steps):
             tickets.append(sess.submit(hx[i % 2] if hx else None))
-            if len(tickets) >= 2:        # keep <= 2 steps in flight, consume results in order
-                sess.result(tickets.pop(0))
+            if len(tickets) >= sess.slots - 1:
+                last = sess.result(tickets.pop(0))
         for t in tickets:
-            sess.result(t)
+            last = sess.result(t)
         sess.drain()
         torch.cuda.synchronize(dev)
         ms = (time.perf_counter() - t0) * 1e3
-        e.check_status()
-        return ctx.max_float(ms), sess.h2d_bytes, sess.d2h_bytes
+        sess.engine.check_status()
+        return ctx.max_float(ms), sess.h2d_bytes, sess.d2h_bytes, last
 
-    def quick_ms(strategy, scatter):
-        s_ = Session(cfg, w, dist=ctx if N > 1 else None, device=dev, precision=precision,
-                     strategy=strategy, scatter=scatter)
-        e_ = s_.engine
-        if e_.in_rows > 0:
-            lo, hi = s_.input_rows
-            e_.input_view(0).copy_(x[:, lo:hi].to(dev))
-        for _ in range(3):
-            e_.forward_enqueue(0, 0)
-        torch.cuda.synchronize(dev)
-        ctx.barrier()
-        t0_, t1_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t0_.record()
-        for _ in range(5):
-            e_.forward_enqueue(0, 0)
-        t1_.record()
-        t1_.synchronize()
-        ms_ = ctx.max_float(t0_.elapsed_time(t1_) / 5)
-        e_.check_status()
-        del s_, e_
-        torch.cuda.empty_cache()
-        return ms_
-
-    # conv2 kernel variant (single GPU): both kernels run the bench input untimed; the double-buffered one is
-    # used only if its output is bit-identical to the single-buffered kernel's and it is faster
-    conv2_info = None
-    os.environ.pop("B200_TC_DB", None)
-    if N == 1 and precision == "tf32":
-        from b200cnn.models.session import autotune_conv2_kernel
-        conv2_info = autotune_conv2_kernel(cfg, w, x, device=dev, prefer=a.conv2_kernel)
-
-    tuned = None
-    if a.strategy == "auto":
-        if N > 1:
-            tuned = {st: round(quick_ms(st, a.scatter), 4) for st in ("halo", "recompute")}
-            a.strategy = min(tuned, key=tuned.get)
-        else:
-            a.strategy = "halo"
-    p2p_alt = None
-    if N > 1 and a.scatter == "sharded":      # the reference's data placement, for the record
-        p2p_alt = round(a.batch / (quick_ms(a.strategy, "p2p") / 1e3), 1)
-    sess = Session(cfg, w, dist=ctx if N > 1 else None, device=dev, precision=precision,
-                   strategy=a.strategy, scatter=a.scatter)
+    strategy = a.strategy if N > 1 else "single-gpu"
+    scatter = a.scatter if N > 1 else "local"
+    sess = Session(cfg, w, dist=dist_arg, device=dev, precision=precision, strategy=a.strategy,
+                   scatter=a.scatter, row_groups=rg, gather="rank0")
+    plan = sess.engine.plan
+    check = None
+    if N > 1 and not a.no_check:
+        ok, fnv = check_against_one_rank(sess)
+        check = {"equals_one_rank_output": ok, "fnv1a64": fnv}
+        if not ok:
+            if ctx.is_root:
+                print(json.dumps({"impl": "ours", "error": f"{N}-rank output differs from the one-rank output; "
+                                  "refusing to time a wrong forward", "check": check, "gpu_launches": 0}), flush=True)
+            ctx.finalize()
+            sys.exit(3)
     total_ms, launches, clocks = measure_device(sess)
     if rejected(clocks):                                  # thermal/hw slowdown: re-measure once
         total_ms, launches, clocks = measure_device(sess)
     clocks.pop("samples", None)
+    host_binding = getattr(sess, "host_binding", None)
+    del sess
+    torch.cuda.empty_cache()
+
+    alternatives = None
+    if a.alt and N > 1:
+        alternatives = {
+            "p2p_scatter_images_per_s": quick_ms(strategy=a.strategy, scatter="p2p", row_groups=rg),
+            "pure_rows_images_per_s": quick_ms(strategy=a.strategy, scatter=a.scatter, row_groups=None),
+            "recompute_images_per_s": quick_ms(strategy="recompute", scatter=a.scatter, row_groups=rg),
+            "note": "warm back-to-back forwards, no L2 flush (not comparable with value)"}
+
     e2e = None
     if not a.no_e2e:
-        e2e_strategy = a.strategy if a.e2e_strategy == "same" else a.e2e_strategy
-        if N > 1 and (a.e2e_scatter != a.scatter or e2e_strategy != a.strategy):
-            del sess
-            torch.cuda.empty_cache()
-            sess = Session(cfg, w, dist=ctx, device=dev, precision=precision,
-                           strategy=e2e_strategy, scatter=a.e2e_scatter)
-        e2e_ms, h2d, d2h = measure_e2e(sess)
+        es = Session(cfg, w, dist=dist_arg, device=dev, precision=precision, strategy=a.strategy,
+                     scatter=a.scatter, row_groups=rg, gather=a.e2e_gather, slots=4)
+        e2e_ms, h2d, d2h, last = measure_e2e(es)
         h2d_all = sum(ctx.all_gather_object(h2d))
         d2h_all = sum(ctx.all_gather_object(d2h))
-        e2e = {"value": round(a.batch * a.steps / (e2e_ms / 1e3), 2), "unit": "images/s",
+        e2e = {"value": round(a.batch * a.steps / (e2e_ms / 1e3), 2), "unit": UNIT,
                "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": d2h_all,
-               "scatter": a.e2e_scatter if N > 1 else "local",
-               "strategy": (a.strategy if a.e2e_strategy == "same" else a.e2e_strategy) if N > 1 else "single-gpu",
-               "pipelined_steps_in_flight": 2}
+               "strategy": strategy, "scatter": scatter, "row_groups": plan.row_groups,
+               "gather": es.gather if N > 1 else "local", "steps_in_flight": es.slots - 1,
+               "result_checked": bool(last is not None and torch.isfinite(last).all()) if ctx.is_root else None}
+        del es
     ms_per_step = total_ms / a.steps
     value = a.batch / (ms_per_step / 1e3)
     base = REF_V4_BEST_IMG_S.get(N)
@@ -227,10 +257,11 @@ def run_ours(a):
                    "timed_region": "value: CUDA events around each forward, max over ranks; e2e: wall clock over pinned "
                                    "H2D + forward + D2H of every step through Session",
                    "global_batch": a.batch, "input": f"{a.height}x{a.width}x3",
-                   "parallelism": f"spatial-rows{N}" if N > 1 else "single-gpu",
-                   "strategy": a.strategy, "strategy_autotune_ms": tuned,
-                   "scatter": a.scatter if N > 1 else "local", "p2p_scatter_images_per_s": p2p_alt,
-                   "conv2_kernel": conv2_info, "host_binding": getattr(sess, "host_binding", None),
+                   "parallelism": (f"spatial rows x batch: {plan.row_groups} row groups x {plan.batch_groups} batch groups"
+                                   if N > 1 else "single-gpu"),
+                   "strategy": strategy, "scatter": scatter, "gather": "rank0 (P2P stores from the LRN epilogue)" if N > 1 else "local",
+                   "check": check, "alternatives": alternatives, "host_binding": host_binding,
+                   "vs_baseline_note": "value / the reference's published best V4 images/s at this np (other hardware, batch 1)",
                    "l2": "flushed between timed iterations (256 MiB fill, untimed)"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "impl": "ours",
     }

@@ -56,6 +56,22 @@ __device__ __forceinline__ bool wait_flag_ge(const int* flag, int target, int* s
         __nanosleep(64);
     }
 }
+// Flow-control gate and completion notice of a block launch (b200_block_geom::gate / done*).
+// gate: called by ONE thread per CTA before the CTA-wide barrier that ends the kernel prologue.
+__device__ __forceinline__ void block_gate_wait(const b200_block_geom& g) {
+    if (g.gate) wait_flag_ge(g.gate, g.gate_target * (g.epoch ? *g.epoch : 1), g.status, g.timeout_ns);
+}
+// done: called by ONE thread per CTA after a CTA-wide barrier that follows the CTA's last store.  The
+// fences order every CTA's stores (made visible to this thread by that barrier) before the notice.
+__device__ __forceinline__ void block_done_signal(const b200_block_geom& g) {
+    if (!g.done_count) return;
+    __threadfence_system();
+    const unsigned int old = atomicAdd(g.done_count, 1u);
+    if ((old + 1u) % gridDim.x == 0u) {
+        __threadfence_system();
+        for (int i = 0; i < g.n_done; ++i) red_release_sys_add(g.done[i], 1);
+    }
+}
 #endif
 
 }  // namespace b200

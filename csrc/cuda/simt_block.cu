@@ -51,6 +51,7 @@ simt_block_kernel(const float* __restrict__ wt,    // [F][F*C][K]
 
     // ---- wait for remote rows this patch touches (consumer side of the flag protocol) ----
     if (threadIdx.x == 0) {
+        block_gate_wait(g);
         for (int s = 0; s < g.nseg; ++s) {
             const b200_row_seg& sg = g.seg[s];
             if (sg.flag && ir0 < sg.hi && ir0 + IR > sg.lo)
@@ -193,11 +194,14 @@ simt_block_kernel(const float* __restrict__ wt,    // [F][F*C][K]
     }
 
     // ---- producer side of the flag protocol ----
-    if (g.n_signal > 0) {
+    if (g.n_signal > 0 || g.done_count) {
         __syncthreads();
         if (threadIdx.x == 0) {
-            __threadfence_system();
-            for (int i = 0; i < g.n_signal; ++i) red_release_sys_add(g.signal[i] + n, 1);
+            if (g.n_signal > 0) {
+                __threadfence_system();
+                for (int i = 0; i < g.n_signal; ++i) red_release_sys_add(g.signal[i] + n, 1);
+            }
+            block_done_signal(g);
         }
     }
 }
@@ -227,7 +231,8 @@ extern "C" int b200_simt_block_tiles(const b200_block_geom* g) {
 extern "C" int b200_simt_block(const float* wt, const float* bias, float* out,
                                const b200_block_geom* g, void* stream) {
     if (!g || !wt || !bias || !out) return B200_ERR_ARG;
-    if (g->nseg < 1 || g->nseg > B200_MAX_SEG || g->n_signal < 0 || g->n_signal > B200_MAX_SIGNAL)
+    if (g->nseg < 1 || g->nseg > B200_MAX_SEG || g->n_signal < 0 || g->n_signal > B200_MAX_SIGNAL ||
+        g->n_done < 0 || g->n_done > 2)
         return B200_ERR_ARG;
     const int rows = g->p1 - g->p0;
     if (rows <= 0 || g->N <= 0) return B200_OK;

@@ -58,6 +58,31 @@ extern "C" int b200_memcpy2d_h2d(void* dst, size_t dpitch, const void* src, size
     return B200_OK;
 }
 
+extern "C" int b200_memcpy2d_d2h(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width,
+                                 size_t height, void* stream) {
+    if (!dst || !src) return B200_ERR_ARG;
+    if (width == 0 || height == 0) return B200_OK;
+    B200_CUDA_TRY(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, height, cudaMemcpyDeviceToHost,
+                                    (cudaStream_t)stream));
+    return B200_OK;
+}
+
+// Host memory that several processes share (POSIX shm mapped by each of them): pin it for DMA and get the
+// address kernels use for it.
+extern "C" int b200_host_register(void* host, size_t bytes, void** dev_ptr) {
+    if (!host || !bytes) return B200_ERR_ARG;
+    cudaError_t e = cudaHostRegister(host, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped);
+    if (e == cudaErrorHostMemoryAlreadyRegistered) { cudaGetLastError(); e = cudaSuccess; }
+    B200_CUDA_TRY(e);
+    if (dev_ptr) B200_CUDA_TRY(cudaHostGetDevicePointer(dev_ptr, host, 0));
+    return B200_OK;
+}
+
+extern "C" int b200_host_unregister(void* host) {
+    if (host && cudaHostUnregister(host) != cudaSuccess) cudaGetLastError();
+    return B200_OK;
+}
+
 extern "C" int b200_can_access_peer(int dev, int peer) {
     int ok = 0;
     if (cudaDeviceCanAccessPeer(&ok, dev, peer) != cudaSuccess) { cudaGetLastError(); return 0; }
@@ -93,6 +118,22 @@ __global__ void flag_wait_kernel(WaitArgs a, int* status, unsigned long long tim
     __threadfence_system();
 }
 
+// One word of (mapped, pinned) host memory := value, after everything earlier in the stream — e.g. the D2H
+// copy a reader in another process is waiting for.  A plain store: host memory takes no device atomics here.
+__global__ void host_flag_store_kernel(volatile int* flag, int value) {
+    __threadfence_system();
+    *flag = value;
+    __threadfence_system();
+}
+
+// Opens a forward: bump the local forward counter and publish "go" to the ranks whose launches are gated on
+// this rank (they write into its buffers).  Everything earlier in the stream is ordered before the bump.
+__global__ void flag_begin_kernel(SignalArgs a, int* epoch) {
+    if (threadIdx.x == 0 && epoch) ++(*epoch);
+    __threadfence_system();
+    if ((int)threadIdx.x < a.n) red_release_sys_add(a.target[threadIdx.x], 1);
+}
+
 // Barrier in one launch: bump one counter on every peer, then wait for every peer's bump on ours.
 // Only for ranks that own a GPU each (the waits would deadlock if ranks shared a device).
 __global__ void flag_barrier_kernel(SignalArgs sig, WaitArgs w, int* status, unsigned long long timeout_ns,
@@ -120,6 +161,24 @@ extern "C" int b200_flag_barrier(int* const* signal_targets, const int* const* w
     s.n = w.n = n;
     for (int i = 0; i < n; ++i) { s.target[i] = signal_targets[i]; w.flag[i] = wait_flags[i]; w.target[i] = wait_target[i]; }
     flag_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(s, w, status, timeout_ns, epoch);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+extern "C" int b200_host_flag_store(int* flag_dev_ptr, int value, void* stream) {
+    if (!flag_dev_ptr) return B200_ERR_ARG;
+    host_flag_store_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(flag_dev_ptr, value);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+extern "C" int b200_flag_begin(int* epoch, int* const* go_targets, int n, void* stream) {
+    if (n < 0 || n > 16 || (n && !go_targets)) return B200_ERR_ARG;
+    if (n == 0 && !epoch) return B200_OK;
+    SignalArgs a;
+    a.n = n;
+    for (int i = 0; i < n; ++i) a.target[i] = go_targets[i];
+    flag_begin_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(a, epoch);
     B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;
 }

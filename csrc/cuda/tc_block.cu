@@ -124,6 +124,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
         mbar_init(tmem_full_bar, 1);
         mbar_init(tile_free_bar, kProducerWarps);
         fence_mbar_init();
+        block_gate_wait(g);
     }
     for (int i = threadIdx.x; i < N; i += kThreads) s_bias[i] = bias[i];
     if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
@@ -423,6 +424,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
         tc_fence_after();
         tmem_dealloc(tmem_base, p.tmem_cols);
     }
+    if (threadIdx.x == 0) block_done_signal(g);
 }
 
 // ------------------------------------------------------- small-K_out kernel (conv1) ----
@@ -498,6 +500,7 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
             mbar_init(tempty_bar + 8 * b, 4);
         }
         fence_mbar_init();
+        block_gate_wait(g);
     }
     for (int i = threadIdx.x; i < 128; i += kSwThreads) s_bias[i] = i < KO ? bias[i] : 0.f;
     if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_slot), 512);
@@ -772,6 +775,7 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
     }
+    if (threadIdx.x == 0) block_done_signal(g);
 }
 
 
@@ -833,6 +837,7 @@ tc_block_db_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_const
             mbar_init(tempty_bar + 8 * b, 4);
         }
         fence_mbar_init();
+        block_gate_wait(g);
     }
     for (int i = threadIdx.x; i < N; i += kDbThreads) s_bias[i] = bias[i];
     if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
@@ -1065,6 +1070,7 @@ tc_block_db_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_const
         tc_fence_after();
         tmem_dealloc(tmem_base, p.tmem_cols);
     }
+    if (threadIdx.x == 0) block_done_signal(g);
 }
 
 
@@ -1128,6 +1134,7 @@ tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_co
             mbar_init(tempty_bar + 8 * b, 8);
         }
         fence_mbar_init();
+        block_gate_wait(g);
     }
     for (int i = threadIdx.x; i < N; i += kPairThreads) s_bias[i] = bias[i];
     if (warp == 1) tmem_alloc2(smem_u32(tmem_slot), p.tmem_cols);
@@ -1307,6 +1314,7 @@ tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_co
         tc_fence_after();
         tmem_dealloc2(tmem_base, p.tmem_cols);
     }
+    if (threadIdx.x == 0) block_done_signal(g);
 }
 
 // --------------------------------------------------------------------------- host ----
@@ -1710,7 +1718,8 @@ extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const 
                              int flags, void* stream) {
     TcConv* t = (TcConv*)handle;
     if (!t || !bias || !out || !g) return B200_ERR_ARG;
-    if (g->nseg < 1 || g->nseg > B200_MAX_SEG || g->n_signal < 0 || g->n_signal > B200_MAX_SIGNAL)
+    if (g->nseg < 1 || g->nseg > B200_MAX_SEG || g->n_signal < 0 || g->n_signal > B200_MAX_SIGNAL ||
+        g->n_done < 0 || g->n_done > 2)
         return B200_ERR_ARG;
     if (g->K != t->K || g->C != t->C || g->F != t->F) return B200_ERR_ARG;
     if (g->p1 <= g->p0 || g->N <= 0) return B200_OK;

@@ -14,8 +14,13 @@ decomposition logic inlined in V4's main (ref v4_mpi_cuda/src/main_mpi_cuda.cpp:
 * block 2 = conv2+bias+ReLU+pool2+LRN in ONE kernel whose loader reads halo pool1 rows straight
   from the owning peer (gated by those counters) and whose epilogue stores the final rows straight
   into rank 0's output tensor (the gather);
-* a device-side barrier opens every forward and a completion counter closes it, so the whole
-  multi-GPU forward is stream-ordered with no host synchronisation.
+* no barrier sits on the forward: the pool1 slabs are double-buffered by forward parity, rank 0 opens
+  forward k by bumping a ``go`` counter on every rank (one tiny launch), block 2 of forward k is gated
+  on ``go >= k`` (off the critical path: it was published one conv1 earlier), and the last CTA of every
+  rank's block 2 bumps a completion counter on rank 0 — so the whole multi-GPU forward is
+  stream-ordered with no host synchronisation and no all-to-all (see ``_enqueue_stages``);
+* the world is R row groups x B batch groups (``row_groups``): a rank splits rows only with the R-1
+  ranks that hold the other rows of ITS images.
 
 ``precision``: ``"simt"`` exact FP32 (validation twin) or ``"tf32"`` tcgen05 tensor cores.
 """
@@ -61,21 +66,36 @@ class _Layout:
         return self.status_off + 2
 
     @property
-    def epoch_off(self):    # device-side forward counter (bumped by the barrier kernel)
+    def epoch_off(self):    # device-side forward counter (bumped by the kernel that opens a forward)
         return self.status_off + 1
 
     @property
+    def go_off(self):       # forwards opened by rank 0 (gate of block 2)
+        return self.sync_off + self.world
+
+    @property
+    def cta_off(self):      # CTAs of block 2 that have finished, all forwards (completion notice)
+        return self.go_off + 1
+
+    @property
     def count(self):
-        return self.status_off + 2 + self.world + 16
+        return self.cta_off + 1 + 16
 
 
 class Blocks12Engine:
     def __init__(self, cfg: NetConfig, weights: Blocks12Weights, symm, rank: int = 0,
                  world: int = 1, *, precision: Optional[str] = None, strategy: str = "halo",
                  scatter: str = "p2p", timeout_ns: int = cu.DEFAULT_TIMEOUT_NS,
-                 device_epoch: Optional[bool] = None, use_graph: Optional[bool] = None):
+                 device_epoch: Optional[bool] = None, use_graph: Optional[bool] = None,
+                 row_groups=None, gather: str = "rank0", slots: int = 2):
         if scatter not in ("p2p", "sharded"):
             raise ValueError(scatter)
+        if gather not in ("rank0", "local"):
+            raise ValueError(gather)
+        # gather="rank0": the LRN epilogue stores every rank's rows into rank 0's output tensor over NVLink
+        # (the reference's MPI_Gatherv); "local": every rank keeps the rows of the images it owns (callers
+        # that want the result in HOST memory read each rank's rows back over that rank's own PCIe link).
+        self.gather = gather
         self.cfg = cfg
         self.rank, self.world = rank, world
         self.symm = symm
@@ -83,8 +103,9 @@ class Blocks12Engine:
         self.precision = precision or cfg.precision
         self.scatter = scatter
         self.timeout_ns = timeout_ns
-        self.plan: Plan = make_plan(cfg, world, strategy)
+        self.plan: Plan = make_plan(cfg, world, strategy, row_groups)
         self.rp: RankPlan = self.plan.ranks[rank]
+        self.n_img, self.img0 = self.rp.n_images, self.rp.images[0]
         self.sh = self.plan.shapes
         self.epoch = 0
         self.launches = 0            # kernels launched by this engine (bench reports it)
@@ -96,10 +117,11 @@ class Blocks12Engine:
         self.device_epoch = (world > 1) if device_epoch is None else device_epoch
         self.use_graph = True if use_graph is None else use_graph
         self._stage = None           # contiguous H2D landing buffers (pitched inputs only)
-        self._graphs = {}            # (in_idx, out_idx) -> (torch.cuda.CUDAGraph, kernels per replay)
+        self._graphs = {}            # (in_idx, out_idx, parity) -> (torch.cuda.CUDAGraph, kernels per replay)
         self._calls = {}
         self.lay = _Layout(world, cfg.batch)
-        sh, rp, N = self.sh, self.rp, cfg.batch
+        sh, rp = self.sh, self.rp
+        N = self.n_img               # images this rank works on
 
         # ---- weights: packed once, resident ------------------------------------------------
         with torch.cuda.device(self.device):
@@ -125,13 +147,15 @@ class Blocks12Engine:
 
         # ---- symmetric buffers ---------------------------------------------------------------
         f4 = 4
-        self.n_in_buf = 2
-        if scatter == "p2p":
+        self.n_in_buf = slots          # input / output slots a pipelined caller cycles through
+        if scatter == "p2p":                 # rank 0 holds every image of the batch, whole
             in_rows = sh.H if rank == 0 else 0
             self.in_base = 0
+            self.in_imgs = cfg.batch if rank == 0 else 0
         else:
-            in_rows = rp.in_rows[1] - rp.in_rows[0]
+            in_rows = rp.in_rows[1] - rp.in_rows[0] if N > 0 else 0
             self.in_base = rp.in_rows[0]
+            self.in_imgs = N
         self.in_rows = in_rows
         # Row pitch of the resident input: padded to a multiple of 4 floats (and long enough for the last
         # pixel's filter-row run) so conv1's loader can cp.async 16 B chunks straight from it; the H2D
@@ -141,8 +165,8 @@ class Blocks12Engine:
         if self.precision == "tf32" and not self.s2d and p1.P == 0 and (p1.S * sh.C) % 4 == 0:
             run = (p1.F * sh.C + 3) // 4 * 4
             self.in_pitch = (max(sh.W * sh.C, (sh.Wc1 - 1) * p1.S * sh.C + run) + 3) // 4 * 4
-        self.in_bytes = N * in_rows * sh.W * sh.C * f4          # payload bytes per step (H2D accounting)
-        self.in_alloc = N * in_rows * self.in_pitch * f4 + 256
+        self.in_bytes = self.in_imgs * in_rows * sh.W * sh.C * f4   # payload bytes per step (H2D accounting)
+        self.in_alloc = self.in_imgs * in_rows * self.in_pitch * f4 + 256
         self.buf_in = [symm.alloc(f"in{i}", self.in_alloc) for i in range(self.n_in_buf)]
         if self.s2d:
             S1 = cfg.conv1.S
@@ -154,13 +178,19 @@ class Blocks12Engine:
                 self.s2d_ys = -(-(self.in_base + in_rows) // S1) - self.s2d_y0
             else:
                 self.s2d_y0, self.s2d_ys = 0, 0
-            self.buf_s2d = [symm.alloc(f"s2d{i}", N * self.s2d_ys * self.s2d_ws * self.s2d_c * f4)
+            self.buf_s2d = [symm.alloc(f"s2d{i}", self.in_imgs * self.s2d_ys * self.s2d_ws * self.s2d_c * f4)
                             for i in range(self.n_in_buf)]
         own = rp.pool1_own[1] - rp.pool1_own[0]
-        self.buf_pool1 = symm.alloc("pool1", N * own * sh.Wp1 * sh.K1 * f4)
-        out_rows = sh.Hp2 if rank == 0 else 0
-        self.n_out_buf = 2
-        self.buf_out = [symm.alloc(f"out{i}", N * out_rows * sh.Wp2 * sh.K2 * f4)
+        # two pool1 slabs, used alternately by forward parity: a neighbour may still read forward k's rows
+        # while this rank's conv1 already writes forward k+1's
+        self.buf_pool1 = [symm.alloc(f"pool1_{i}", N * own * sh.Wp1 * sh.K1 * f4) for i in range(2)]
+        self.n_out_buf = slots
+        if gather == "rank0":
+            self.out_imgs, self.out_row0, self.out_rows = (cfg.batch, 0, sh.Hp2) if rank == 0 else (0, 0, 0)
+        else:
+            self.out_imgs, self.out_row0 = N, rp.out_rows[0]
+            self.out_rows = rp.out_rows[1] - rp.out_rows[0]
+        self.buf_out = [symm.alloc(f"out{i}", self.out_imgs * self.out_rows * sh.Wp2 * sh.K2 * f4)
                         for i in range(self.n_out_buf)]
         self.buf_flags = symm.alloc("flags", self.lay.count * 4)
         self._final = False
@@ -169,12 +199,13 @@ class Blocks12Engine:
     def finalize(self) -> None:
         """Call after every rank allocated and ``symm.commit()`` ran: resolves peer pointers."""
         self._final = True
-        if self.rank == 0:
-            sh = self.sh
-            self.outs = [b.tensor((self.cfg.batch, sh.Hp2, sh.Wp2, sh.K2)) for b in self.buf_out]
+        sh = self.sh
+        if self.out_imgs * self.out_rows > 0:
+            self.outs = [b.tensor((self.out_imgs, self.out_rows, sh.Wp2, sh.K2)) for b in self.buf_out]
         else:
             self.outs = [None] * self.n_out_buf
         self.out = self.outs[0]
+        self._active = [r for r in range(self.world) if self.plan.ranks[r].active]
         self.flags_t = self.buf_flags.tensor((self.lay.count,), torch.int32)
         # tiles per image of every rank's block 1 (arrival-counter targets)
         self._b1_tiles = [self._tiles(self._geom_block1(r, probe=True)) for r in range(self.world)]
@@ -193,16 +224,21 @@ class Blocks12Engine:
         """This rank's input buffer ``i`` as an [N, rows, W, C] view (rows are ``in_pitch`` floats apart;
         rank 0 holds the whole batch in p2p-scatter mode)."""
         sh = self.sh
-        n, rows, pitch = self.cfg.batch, self.in_rows, self.in_pitch
+        n, rows, pitch = self.in_imgs, self.in_rows, self.in_pitch
         flat = self.buf_in[i].tensor((max(n * rows * pitch, 1),))
         return flat.as_strided((n, rows, sh.W, sh.C), (rows * pitch, pitch, sh.C, 1))
+
+    def pool1_view(self) -> torch.Tensor:
+        """This rank's pool1 rows of the latest forward, [n_img, own rows, Wp1, K1]."""
+        sh, (a, b) = self.sh, self.rp.pool1_own
+        return self.buf_pool1[self.epoch & 1].tensor((self.n_img, b - a, sh.Wp1, sh.K1))
 
     def h2d(self, i: int, x_host: torch.Tensor) -> None:
         """Pinned host [N, rows, W, C] -> input buffer ``i`` on the current stream.  A pitched input is
         filled in two steps — one contiguous DMA at full PCIe rate into a staging buffer, then a ~30 us
         device copy that spreads the rows to their pitch (a 2-D DMA of 2.7 KB rows is 3x slower)."""
         sh = self.sh
-        assert x_host.is_contiguous() and tuple(x_host.shape) == (self.cfg.batch, self.in_rows, sh.W, sh.C)
+        assert x_host.is_contiguous() and tuple(x_host.shape) == (self.in_imgs, self.in_rows, sh.W, sh.C)
         with torch.cuda.device(self.device):
             if self.in_pitch == sh.W * sh.C:
                 self.input_view(i).copy_(x_host, non_blocking=True)
@@ -212,12 +248,13 @@ class Blocks12Engine:
                                for _ in range(self.n_in_buf)]
             self._stage[i].copy_(x_host, non_blocking=True)
             from ..ops import ext
-            ext.repitch_rows_(self._stage[i].data_ptr(), self.buf_in[i].ptr, self.cfg.batch * self.in_rows,
+            ext.repitch_rows_(self._stage[i].data_ptr(), self.buf_in[i].ptr, self.in_imgs * self.in_rows,
                               sh.W * sh.C, self.in_pitch)
 
     def _geom_block1(self, r: int, probe: bool = False, in_idx: int = 0):
         cfg, sh, p1 = self.cfg, self.sh, self.cfg.conv1
         rp = self.plan.ranks[r]
+        img_bytes = rp.images[0] * 4                      # x floats per image: offset into rank 0's batch
         s2d = self.s2d
         S1 = p1.S
         Hin = self.s2d_hs if s2d else sh.H
@@ -225,9 +262,10 @@ class Blocks12Engine:
             segs = [dict(ptr=1, base=0, slab=Hin, lo=0, hi=Hin)]
             signals, out_ptr = [], 0
         else:
-            if self.scatter == "p2p":
+            if self.scatter == "p2p":                  # this rank's images inside rank 0's whole batch
                 name = f"s2d{in_idx}" if s2d else f"in{in_idx}"
-                segs = [dict(ptr=self.symm.ptr(0, name), base=0, slab=Hin, lo=0, hi=Hin)]
+                per_img = Hin * (self.s2d_ws * self.s2d_c if s2d else self.in_pitch)
+                segs = [dict(ptr=self.symm.ptr(0, name) + img_bytes * per_img, base=0, slab=Hin, lo=0, hi=Hin)]
             elif s2d:
                 segs = [dict(ptr=self.buf_s2d[in_idx].ptr, base=self.s2d_y0, slab=self.s2d_ys,
                              lo=self.s2d_y0, hi=self.s2d_y0 + self.s2d_ys)]
@@ -239,7 +277,7 @@ class Blocks12Engine:
         conv = dict(H=Hin, W=self.s2d_ws, Cin=self.s2d_c, F=-(-p1.F // S1), S=1, P=0) if s2d else \
             dict(H=sh.H, W=sh.W, Cin=sh.C, F=p1.F, S=p1.S, P=p1.P, in_pitch=self.in_pitch)
         g = cu.make_block_geom(
-            N=cfg.batch, K=p1.K, **conv,
+            N=rp.n_images, K=p1.K, **conv,
             Hc=sh.Hc1, Wc=sh.Wc1, Hp=sh.Hp1, Wp=sh.Wp1, rows=rp.pool1_own,
             out_base=rp.pool1_own[0], out_slab=rp.pool1_own[1] - rp.pool1_own[0], lrn=None,
             segs=segs, signals=signals,
@@ -247,53 +285,53 @@ class Blocks12Engine:
             timeout_ns=self.timeout_ns)
         return g
 
-    def _geom_block2(self):
+    def _geom_block2(self, parity: int = 0):
         cfg, sh, p2, rp = self.cfg, self.sh, self.cfg.conv2, self.rp
         own0, own1 = rp.pool1_own
         segs = []
         if own1 > own0:
-            segs.append(dict(ptr=self.buf_pool1.ptr, base=own0, slab=own1 - own0, lo=own0, hi=own1))
+            segs.append(dict(ptr=self.buf_pool1[parity].ptr, base=own0, slab=own1 - own0, lo=own0, hi=own1))
         for peer, lo, hi in rp.halo:
             po = self.plan.ranks[peer].pool1_own
-            segs.append(dict(ptr=self.symm.ptr(peer, "pool1"), base=po[0], slab=po[1] - po[0],
+            segs.append(dict(ptr=self.symm.ptr(peer, f"pool1_{parity}"), base=po[0], slab=po[1] - po[0],
                              lo=lo, hi=hi,
                              flag=self._flag_ptr(self.rank, self.lay.arr_off + peer * self.lay.nmax),
                              target=(1 if self.device_epoch else self.epoch) * self._b1_tiles[peer]))
         lrn = LrnParams(p2.N_lrn, p2.alpha, p2.beta, p2.k_lrn, LRN_MODES[cfg.lrn_mode])
+        multi = self.world > 1
+        per_fwd = 1 if self.device_epoch else self.epoch
+        if self.gather == "rank0":
+            out_base, out_slab = 0, sh.Hp2
+        else:
+            out_base, out_slab = self.out_row0, self.out_rows
         return cu.make_block_geom(
-            N=cfg.batch, H=sh.Hp1, W=sh.Wp1, Cin=sh.K1, K=p2.K, F=p2.F, S=p2.S, P=p2.P,
+            N=self.n_img, H=sh.Hp1, W=sh.Wp1, Cin=sh.K1, K=p2.K, F=p2.F, S=p2.S, P=p2.P,
             Hc=sh.Hc2, Wc=sh.Wc2, Hp=sh.Hp2, Wp=sh.Wp2, rows=rp.out_rows,
-            out_base=0, out_slab=sh.Hp2, lrn=lrn, segs=segs, signals=[],
+            out_base=out_base, out_slab=out_slab, lrn=lrn, segs=segs, signals=[],
             status_ptr=self._flag_ptr(self.rank, self.lay.status_off), timeout_ns=self.timeout_ns,
-            epoch_ptr=self._flag_ptr(self.rank, self.lay.epoch_off) if self.device_epoch else 0)
+            epoch_ptr=self._flag_ptr(self.rank, self.lay.epoch_off) if self.device_epoch else 0,
+            # flow control: rank 0 has opened this forward, i.e. everything of the forward before the previous
+            # one is finished everywhere (its output slot and the pool1 slabs of this parity are free)
+            gate_ptr=self._flag_ptr(self.rank, self.lay.go_off) if multi and self.rank != 0 else 0,
+            gate_target=per_fwd,
+            done_count_ptr=self._flag_ptr(self.rank, self.lay.cta_off),
+            done=[self._flag_ptr(0, self.lay.done_off + self.rank)] if multi else [])
 
     # ---- forward stages (each enqueues on the current stream) ----------------------------------
     def stage_begin(self) -> None:
         self.epoch += 1
 
-    def stage_barrier_signal(self) -> None:
+    def stage_open(self) -> None:
+        """Opens the forward on the device: bumps this rank's forward counter and, on rank 0, the ``go``
+        counter of every other active rank.  Replaces the all-to-all barrier that used to open a forward
+        (the reference's MPI_Barrier, ref v4_mpi_cuda/src/main_mpi_cuda.cpp:151): rank 0 gets here only
+        after its completion wait of the previous forward, so ``go >= k`` tells a rank that every block 2
+        of forward k-1 has finished everywhere."""
         if self.world > 1:
-            cu.flag_signal([self._flag_ptr(r, self.lay.bar_off + self.rank)
-                            for r in range(self.world)])
-            self.launches += 1
-
-    def stage_barrier_wait(self) -> None:
-        if self.world > 1:
-            cu.flag_wait([self._flag_ptr(self.rank, self.lay.bar_off + r) for r in range(self.world)],
-                         [self.epoch] * self.world,
-                         self._flag_ptr(self.rank, self.lay.status_off), self.timeout_ns)
-            self.launches += 1
-
-    def stage_barrier(self) -> None:
-        """signal + wait in ONE launch; only valid when every rank owns its GPU (real multi-GPU)."""
-        if self.world > 1:
-            W = range(self.world)
-            cu.flag_barrier([self._flag_ptr(r, self.lay.bar_off + self.rank) for r in W],
-                            [self._flag_ptr(self.rank, self.lay.bar_off + r) for r in W],
-                            [self.epoch] * self.world,
-                            self._flag_ptr(self.rank, self.lay.status_off), self.timeout_ns,
-                            self._flag_ptr(self.rank, self.lay.epoch_off) if self.device_epoch else 0)
-            self.launches += 1
+            go = [self._flag_ptr(r, self.lay.go_off) for r in self._active if r != 0] if self.rank == 0 else []
+            if go or self.device_epoch:
+                cu.flag_begin(self._flag_ptr(self.rank, self.lay.epoch_off) if self.device_epoch else 0, go)
+                self.launches += 1
 
     def sync_ranks(self) -> None:
         """Stream-ordered device-side barrier on its own counters (does not open a forward): used to
@@ -314,7 +352,7 @@ class Blocks12Engine:
             from ..ops import ext
             sh = self.sh
             assert self.in_pitch == sh.W * sh.C, "the s2d pre-pass reads an unpadded input"
-            ext.space_to_depth_(self.buf_in[in_idx].ptr, self.buf_s2d[in_idx].ptr, self.cfg.batch, sh.H, sh.W,
+            ext.space_to_depth_(self.buf_in[in_idx].ptr, self.buf_s2d[in_idx].ptr, self.in_imgs, sh.H, sh.W,
                                 sh.C, self.cfg.conv1.S, self.in_base, self.in_rows, self.s2d_y0, self.s2d_ys)
             self.launches += 1
 
@@ -323,32 +361,33 @@ class Blocks12Engine:
         if rp.pool1_own[1] <= rp.pool1_own[0]:
             return
         g = self._geom_block1(self.rank, in_idx=in_idx)
+        pool1 = self.buf_pool1[self.epoch & 1].ptr
         if self.precision == "simt":
-            cu.simt_block(self.w1p, self.b1, self.buf_pool1.ptr, g)
+            cu.simt_block(self.w1p, self.b1, pool1, g)
         else:
-            self.tc1.run(self.b1, self.buf_pool1.ptr, g, round_out=True)
+            self.tc1.run(self.b1, pool1, g, round_out=True)
         self.launches += 1
 
     def stage_block2(self, out_idx: int = 0) -> None:
         if not self.rp.active:
             return
-        g = self._geom_block2()
-        out_ptr = self.symm.ptr(0, f"out{out_idx}")
+        g = self._geom_block2(self.epoch & 1)
+        if self.gather == "rank0":       # this rank's images inside rank 0's [batch, Hp2, Wp2, K2] tensor
+            sh = self.sh
+            out_ptr = self.symm.ptr(0, f"out{out_idx}") + self.img0 * sh.Hp2 * sh.Wp2 * sh.K2 * 4
+        else:
+            out_ptr = self.buf_out[out_idx].ptr
         if self.precision == "simt":
             cu.simt_block(self.w2p, self.b2, out_ptr, g)
         else:
             self.tc2.run(self.b2, out_ptr, g)
         self.launches += 1
 
-    def stage_done_signal(self) -> None:
-        if self.world > 1:
-            cu.flag_signal([self._flag_ptr(0, self.lay.done_off + self.rank)])
-            self.launches += 1
-
     def stage_done_wait(self) -> None:
+        """Rank 0: every active rank's block 2 has stored its rows (their last CTAs bumped the counters)."""
         if self.world > 1 and self.rank == 0:
-            cu.flag_wait([self._flag_ptr(0, self.lay.done_off + r) for r in range(self.world)],
-                         [1 if self.device_epoch else self.epoch] * self.world,
+            cu.flag_wait([self._flag_ptr(0, self.lay.done_off + r) for r in self._active],
+                         [1 if self.device_epoch else self.epoch] * len(self._active),
                          self._flag_ptr(0, self.lay.status_off), self.timeout_ns,
                          self._flag_ptr(0, self.lay.epoch_off) if self.device_epoch else 0)
             self.launches += 1
@@ -359,7 +398,7 @@ class Blocks12Engine:
         mode).  Returns rank 0's output tensor ``out_idx`` (valid once the stream gets here).
         Every rank must pass the same ``in_idx`` / ``out_idx`` for the same forward."""
         assert self._final, "call finalize() first"
-        key = (in_idx, out_idx)
+        key = (in_idx, out_idx, (self.epoch + 1) & 1)     # launch arguments depend on the pool1 slab parity
         with torch.cuda.device(self.device):
             hit = self._graphs.get(key)
             if hit is not None:
@@ -388,17 +427,24 @@ class Blocks12Engine:
         return self.outs[out_idx]
 
     def _enqueue_stages(self, in_idx: int, out_idx: int) -> None:
+        """Forward k on one rank, stream-ordered:  open -> block 1 -> block 2 [-> completion wait on rank 0].
+        Why no barrier is needed (k = forward number, slabs/slots indexed by k % 2):
+        * block 1 of k overwrites the pool1 slab last read by the neighbours' block 2 of k-2.  It follows
+          this rank's block 2 of k-1 in stream order, which was gated on go >= k-1, which rank 0 published
+          after its completion wait of k-2: every block 2 of k-2 has finished.
+        * block 2 of k writes rank 0's output slot last used by forward k-2 (the caller owns the k-2 vs k
+          hand-over on rank 0; go >= k says rank 0 has begun k).
+        * arrival counters only grow; a neighbour that runs ahead can only over-satisfy a wait."""
         self.stage_begin()
         self.stage_s2d(in_idx)
-        self.stage_barrier()
+        self.stage_open()
         self.stage_block1(in_idx)
         self.stage_block2(out_idx)
-        self.stage_done_signal()
         self.stage_done_wait()
 
     def forward(self, x: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
-        """Device-tensor API: copies ``x`` (this rank's input; whole batch on rank 0 in p2p mode)
-        into the resident buffer and runs one forward."""
+        """Device-tensor API: copies ``x`` (this rank's images and rows; the whole batch on rank 0 in p2p
+        mode) into the resident buffer and runs one forward."""
         if x is not None and self.in_rows > 0:
             self.input_view(0).copy_(x, non_blocking=True)
         return self.forward_enqueue(0)
@@ -431,11 +477,13 @@ class EmulatedWorld:
     and gather index math of the multi-GPU path."""
 
     def __init__(self, cfg: NetConfig, weights: Blocks12Weights, world: int, device="cuda:0",
-                 precision: Optional[str] = None, strategy: str = "halo", scatter: str = "p2p"):
+                 precision: Optional[str] = None, strategy: str = "halo", scatter: str = "p2p",
+                 row_groups=None, gather: str = "rank0", slots: int = 2):
         self.symm = LocalSymm(world, device)
         self.engines: List[Blocks12Engine] = [
             Blocks12Engine(cfg, weights, self.symm.view(r), r, world, precision=precision,
-                           strategy=strategy, scatter=scatter, device_epoch=False, use_graph=False)
+                           strategy=strategy, scatter=scatter, device_epoch=False, use_graph=False,
+                           row_groups=row_groups, gather=gather)
             for r in range(world)]
         for e in self.engines:
             e.finalize()
@@ -448,18 +496,27 @@ class EmulatedWorld:
                     e.input_view(0).copy_(x)
                 else:
                     a, b = e.rp.in_rows
-                    e.input_view(0).copy_(x[:, a:b])
+                    n0, n1 = e.rp.images
+                    e.input_view(0).copy_(x[n0:n1, a:b])
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        """One forward, layer by layer over the ranks (rank 0 first: its ``go`` is out before any gated
+        launch runs).  With gather="local" the ranks' row blocks are assembled here."""
         self.load_input(x)
         E = self.engines
         for e in E: e.stage_begin()
         for e in E: e.stage_s2d(0)
-        for e in E: e.stage_barrier_signal()
-        for e in E: e.stage_barrier_wait()
+        for e in E: e.stage_open()
         for e in E: e.stage_block1(0)
         for e in E: e.stage_block2()
-        for e in E: e.stage_done_signal()
         for e in E: e.stage_done_wait()
         for e in E: e.check_status()
-        return E[0].out
+        if E[0].gather == "rank0":
+            return E[0].out
+        sh = E[0].sh
+        y = torch.empty((self.cfg.batch, sh.Hp2, sh.Wp2, sh.K2), dtype=torch.float32, device=E[0].device)
+        for e in E:
+            if e.out is not None:
+                n0, n1 = e.rp.images
+                y[n0:n1, e.out_row0:e.out_row0 + e.out_rows] = e.out
+        return y

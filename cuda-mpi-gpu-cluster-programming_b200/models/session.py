@@ -31,8 +31,18 @@ from .init import Blocks12Weights
 
 
 class Session:
+    """``gather``: where the result is assembled.  ``"rank0"`` = in rank 0's device tensor (every rank's LRN
+    epilogue stores its rows there over NVLink) and rank 0 copies it to the host; ``"host"`` = every rank copies
+    the rows it owns straight into ONE pinned host tensor shared by all ranks (parallel/hostshm.py), so the
+    result leaves the node's GPUs over all their PCIe links at once.  ``row_groups``: see parallel/planner.py
+    (None = the reference's pure row split, "auto" = two row groups x world/2 batch groups).  ``slots`` input /
+    output slots are cycled; a result returned by :meth:`result` stays valid for ``slots - 2`` further submits."""
+
     def __init__(self, cfg: NetConfig, weights: Blocks12Weights, dist=None, device=None,
-                 precision: Optional[str] = None, strategy: str = "halo", scatter: str = "p2p"):
+                 precision: Optional[str] = None, strategy: str = "halo", scatter: str = "p2p",
+                 row_groups=None, gather: str = "rank0", slots: int = 2):
+        if gather not in ("rank0", "host"):
+            raise ValueError(gather)
         self.cfg = cfg
         self.dist = dist
         # run on the CPUs next to this GPU before any pinned buffer is touched (see utils/numa.py)
@@ -40,31 +50,43 @@ class Session:
         self.host_binding = bind_host_to_gpu(device or (dist.device if dist else "cuda:0"))
         world = dist.world if dist is not None else 1
         rank = dist.rank if dist is not None else 0
+        self.rank, self.world, self.slots = rank, world, slots
         if world > 1:
             self.symm = IpcSymm(dist)
         else:
             self.symm = LocalSymm(1, device or (dist.device if dist else "cuda:0")).view(0)
+        self.gather = gather if world > 1 else "rank0"
         self.engine = Blocks12Engine(cfg, weights, self.symm, rank, world, precision=precision,
-                                     strategy=strategy, scatter=scatter)
+                                     strategy=strategy, scatter=scatter, row_groups=row_groups,
+                                     gather="local" if self.gather == "host" else "rank0", slots=slots)
         self.symm.commit()
         self.engine.finalize()
         e = self.engine
+        sh = e.sh
         self.device = e.device
         with torch.cuda.device(self.device):
             self.s_in = torch.cuda.Stream()
             self.s_compute = torch.cuda.Stream()
             self.s_out = torch.cuda.Stream()
-            self.ev_h2d = [torch.cuda.Event() for _ in range(2)]
-            self.ev_compute = [torch.cuda.Event() for _ in range(2)]
-            self.ev_d2h = [torch.cuda.Event() for _ in range(2)]
+            self.ev_h2d = [torch.cuda.Event() for _ in range(slots)]
+            self.ev_compute = [torch.cuda.Event() for _ in range(slots)]
+            self.ev_d2h = [torch.cuda.Event() for _ in range(slots)]
         self.step = 0
+        self._slot_step = [0] * slots        # step number (1-based) last submitted into each slot
         self.h_out = None
-        if rank == 0:
-            sh = e.sh
-            self.h_out = [torch.empty((cfg.batch, sh.Hp2, sh.Wp2, sh.K2), dtype=torch.float32,
-                                      pin_memory=True) for _ in range(2)]
+        self.shared = None
+        full = (cfg.batch, sh.Hp2, sh.Wp2, sh.K2)
+        if self.gather == "host":
+            from ..parallel.hostshm import SharedHostTensor
+            self.shared = SharedHostTensor(full, slots, dist, self.device)
+            if rank == 0:
+                self.h_out = self.shared.views
+            self.d2h_bytes = e.out_imgs * e.out_rows * sh.Wp2 * sh.K2 * 4
+        else:
+            if rank == 0:
+                self.h_out = [torch.empty(full, dtype=torch.float32, pin_memory=True) for _ in range(slots)]
+            self.d2h_bytes = (self.h_out[0].numel() * 4) if rank == 0 else 0
         self.h2d_bytes = e.in_bytes
-        self.d2h_bytes = (self.h_out[0].numel() * 4) if rank == 0 else 0
 
     # -- what this rank must feed ---------------------------------------------------------------
     @property
@@ -74,12 +96,29 @@ class Session:
         e = self.engine
         return (e.in_base, e.in_base + e.in_rows)
 
+    @property
+    def input_images(self):
+        """Images of the global batch this rank supplies (all of them on rank 0 in p2p mode; the share of
+        the rank's batch group in sharded mode)."""
+        e = self.engine
+        if e.scatter == "p2p":
+            return (0, self.cfg.batch) if self.rank == 0 else (0, 0)
+        return e.rp.images
+
+    def my_input(self, x: torch.Tensor) -> Optional[torch.Tensor]:
+        """The part of a whole-batch host tensor [N,H,W,C] this rank feeds (None: nothing)."""
+        (n0, n1), (lo, hi) = self.input_images, self.input_rows
+        if n1 <= n0 or hi <= lo:
+            return None
+        return x[n0:n1, lo:hi]
+
     def submit(self, x_host: Optional[torch.Tensor]) -> int:
         e = self.engine
-        i = self.step % 2
+        i = self.step % self.slots
         self.step += 1
+        self._slot_step[i] = self.step
         with torch.cuda.device(self.device):
-            if e.in_rows > 0:
+            if e.in_rows > 0 and e.in_imgs > 0:
                 assert x_host is not None and x_host.is_pinned(), "feed pinned host memory"
                 # slot i is free once the forward that last read it has finished
                 self.s_in.wait_event(self.ev_compute[i])
@@ -95,12 +134,28 @@ class Session:
             if out is not None:
                 self.s_out.wait_event(self.ev_compute[i])
                 with torch.cuda.stream(self.s_out):
-                    self.h_out[i].copy_(out, non_blocking=True)
+                    if self.shared is not None:      # my rows of my images -> their place in the shared tensor
+                        sh = e.sh
+                        row = sh.Wp2 * sh.K2 * 4
+                        dst = (self.shared.slot_host_ptr(i)
+                               + (e.rp.images[0] * sh.Hp2 + e.out_row0) * row)
+                        from ..ops import cuda as cu
+                        cu.memcpy2d_d2h(dst, sh.Hp2 * row, e.buf_out[i].ptr, e.out_rows * row,
+                                        e.out_rows * row, e.out_imgs)
+                        cu.host_flag_store(self.shared.flag_dev_ptr(i), self.step)
+                    else:
+                        self.h_out[i].copy_(out, non_blocking=True)
                     self.ev_d2h[i].record(self.s_out)
         return i
 
     def result(self, ticket: int) -> Optional[torch.Tensor]:
-        """Blocks until the ticket's output is in host memory (rank 0) / its forward is done."""
+        """Blocks until the ticket's output is in host memory (rank 0) / this rank's part of it is done."""
+        if self.shared is not None:
+            self.ev_d2h[ticket].synchronize()
+            if self.rank != 0:
+                return None
+            self.shared.wait_all(ticket, self._slot_step[ticket], self.engine._active)
+            return self.h_out[ticket]
         if self.h_out is not None:
             self.ev_d2h[ticket].synchronize()
             return self.h_out[ticket]
@@ -109,7 +164,7 @@ class Session:
 
     def infer(self, x_host: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
         if x_host is not None and not x_host.is_pinned():
-            x_host = x_host.pin_memory()
+            x_host = x_host.contiguous().pin_memory()
         y = self.result(self.submit(x_host))
         self.engine.check_status()
         return y

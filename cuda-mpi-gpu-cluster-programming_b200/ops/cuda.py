@@ -30,7 +30,9 @@ class BlockGeom(C.Structure):
         "out_base", "out_slab")] + [
         ("lrn", LrnParams), ("nseg", C.c_int), ("n_signal", C.c_int), ("in_pitch", C.c_int),
         ("seg", RowSeg * MAX_SEG), ("signal", C.c_void_p * MAX_SIGNAL),
-        ("status", C.c_void_p), ("timeout_ns", C.c_ulonglong), ("epoch", C.c_void_p)]
+        ("status", C.c_void_p), ("timeout_ns", C.c_ulonglong), ("epoch", C.c_void_p),
+        ("gate", C.c_void_p), ("gate_target", C.c_int), ("n_done", C.c_int),
+        ("done_count", C.c_void_p), ("done", C.c_void_p * 2)]
 
 
 _lib = None
@@ -54,9 +56,15 @@ def lib():
         L.b200_enable_peer.argtypes = [C.c_int]
         L.b200_memcpy2d_h2d.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
                                         C.c_void_p]
+        L.b200_memcpy2d_d2h.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
+                                        C.c_void_p]
+        L.b200_host_register.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
+        L.b200_host_unregister.argtypes = [C.c_void_p]
+        L.b200_host_flag_store.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.b200_flag_signal.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_void_p]
         L.b200_flag_wait.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.c_int,
                                      C.c_void_p, C.c_ulonglong, C.c_void_p, C.c_void_p]
+        L.b200_flag_begin.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_int, C.c_void_p]
         L.b200_flag_barrier.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_int),
                                         C.c_int, C.c_void_p, C.c_ulonglong, C.c_void_p, C.c_void_p]
         L.b200_conv_nchw.argtypes = [C.c_void_p] * 4 + [C.c_int] * 8 + [C.c_void_p]
@@ -89,7 +97,8 @@ def make_block_geom(*, N, H, W, Cin, K, F, S, P, Hc, Wc, Hp, Wp, rows: Tuple[int
                     out_base: int, out_slab: int, lrn: Optional[LrnParams],
                     segs: Sequence[dict], signals: Sequence[int] = (),
                     status_ptr: int = 0, timeout_ns: int = DEFAULT_TIMEOUT_NS,
-                    epoch_ptr: int = 0, in_pitch: int = 0) -> BlockGeom:
+                    epoch_ptr: int = 0, in_pitch: int = 0, gate_ptr: int = 0, gate_target: int = 0,
+                    done_count_ptr: int = 0, done: Sequence[int] = ()) -> BlockGeom:
     g = BlockGeom()
     g.N, g.H, g.W, g.C = N, H, W, Cin
     g.K, g.F, g.S, g.P = K, F, S, P
@@ -112,6 +121,14 @@ def make_block_geom(*, N, H, W, Cin, K, F, S, P, Hc, Wc, Hp, Wp, rows: Tuple[int
     g.timeout_ns = timeout_ns
     g.epoch = epoch_ptr or None
     g.in_pitch = in_pitch
+    g.gate = gate_ptr or None
+    g.gate_target = gate_target
+    if len(done) > 2:
+        raise NativeError("at most 2 completion targets")
+    g.done_count = (done_count_ptr or None) if done else None
+    g.n_done = len(done)
+    for i, p in enumerate(done):
+        g.done[i] = p
     return g
 
 
@@ -129,6 +146,13 @@ def flag_signal(targets: Sequence[int], add: int = 1) -> None:
         return
     arr = (C.c_void_p * len(targets))(*targets)
     cu_check(lib().b200_flag_signal(arr, len(targets), add, current_stream_ptr()), "flag_signal")
+
+
+def flag_begin(epoch_ptr: int = 0, go_targets: Sequence[int] = ()) -> None:
+    """Opens a forward on the current stream: ++*epoch (device) and +1 on every ``go`` counter."""
+    n = len(go_targets)
+    arr = (C.c_void_p * max(n, 1))(*go_targets)
+    cu_check(lib().b200_flag_begin(C.c_void_p(epoch_ptr or None), arr, n, current_stream_ptr()), "flag_begin")
 
 
 def flag_wait(flags: Sequence[int], targets: Sequence[int], status_ptr: int = 0,
@@ -174,3 +198,24 @@ def memcpy2d_h2d(dst_ptr: int, dpitch: int, src: torch.Tensor, spitch: int, widt
     """Pitched pinned-host -> device copy on the current stream (bytes)."""
     cu_check(lib().b200_memcpy2d_h2d(C.c_void_p(dst_ptr), dpitch, C.c_void_p(src.data_ptr()), spitch, width,
                                      height, current_stream_ptr()), "memcpy2d_h2d")
+
+
+def memcpy2d_d2h(dst_host_ptr: int, dpitch: int, src_ptr: int, spitch: int, width: int, height: int) -> None:
+    """Pitched device -> pinned-host copy on the current stream (bytes)."""
+    cu_check(lib().b200_memcpy2d_d2h(C.c_void_p(dst_host_ptr), dpitch, C.c_void_p(src_ptr), spitch, width,
+                                     height, current_stream_ptr()), "memcpy2d_d2h")
+
+
+def host_register(host_ptr: int, nbytes: int) -> int:
+    """Pins foreign host memory (shared memory) and returns its device-side address."""
+    d = C.c_void_p()
+    cu_check(lib().b200_host_register(C.c_void_p(host_ptr), nbytes, C.byref(d)), "host_register")
+    return int(d.value)
+
+
+def host_unregister(host_ptr: int) -> None:
+    lib().b200_host_unregister(C.c_void_p(host_ptr))
+
+
+def host_flag_store(flag_dev_ptr: int, value: int) -> None:
+    cu_check(lib().b200_host_flag_store(C.c_void_p(flag_dev_ptr), value, current_stream_ptr()), "host_flag_store")

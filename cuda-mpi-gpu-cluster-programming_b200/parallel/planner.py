@@ -16,6 +16,13 @@ exactly the np=1 output.  Two strategies:
 * ``recompute`` overlapped tiling: each rank computes every pool1 row it needs itself from
                 a larger input slab (the strategy of live V4, made exact).
 
+Rows x batch.  13 final rows over 8 ranks split 2,2,2,2,2,1,1,1 (max/mean 1.23) and every rank then sits
+next to two cuts.  ``row_groups=R`` (R divides the world) keeps the row decomposition inside groups of R
+consecutive ranks and gives every group its own share of the batch (the batch dimension the reference
+never had, SURVEY §2.4 "DP over batch"): 8 ranks as 2 row groups x 4 batch groups split 7/6 rows and a
+rank only talks to the one neighbour that holds the other half of ITS images.  ``row_groups=None`` is
+the reference's pure row split (R = world).
+
 All intervals are half-open ``(lo, hi)`` with ``lo <= hi``; an empty range is ``(x, x)``.
 """
 from __future__ import annotations
@@ -73,10 +80,17 @@ class RankPlan:
     in_rows: Range           # input rows conv1 reads (the "scatter" slab)
     halo: List[Tuple[int, int, int]] = field(default_factory=list)    # (peer, lo, hi) pool1 rows read from peer
     serves: List[Tuple[int, int, int]] = field(default_factory=list)  # (peer, lo, hi) pool1 rows peer reads from me
+    images: Range = (0, 0)   # images [n0, n1) of the global batch this rank works on (its batch group's share)
+    row_group: int = 0       # position inside the group of ranks that split the rows of the same images
+    batch_group: int = 0
 
     @property
     def active(self) -> bool:
-        return _len(self.out_rows) > 0
+        return _len(self.out_rows) > 0 and _len(self.images) > 0
+
+    @property
+    def n_images(self) -> int:
+        return _len(self.images)
 
 
 @dataclass
@@ -86,25 +100,58 @@ class Plan:
     world: int
     strategy: str
     ranks: List[RankPlan]
+    row_groups: int = 0      # R: ranks that split the rows of one image set (== world for the pure row split)
+    batch_groups: int = 1    # B: world == R * B, rank == batch_group * R + row_group
 
-    def owner_of_pool1_row(self, p: int) -> int:
+    def owner_of_pool1_row(self, p: int, batch_group: int = 0) -> int:
         for rp in self.ranks:
-            if rp.pool1_own[0] <= p < rp.pool1_own[1]:
+            if rp.batch_group == batch_group and rp.pool1_own[0] <= p < rp.pool1_own[1]:
                 return rp.rank
         raise IndexError(p)
 
     def summary(self) -> str:
-        lines = [f"plan world={self.world} strategy={self.strategy} "
-                 f"H={self.shapes.H} -> out {self.shapes.Hp2}x{self.shapes.Wp2}x{self.shapes.K2}"]
+        lines = [f"plan world={self.world} = {self.row_groups} row groups x {self.batch_groups} batch groups, "
+                 f"strategy={self.strategy} H={self.shapes.H} -> out {self.shapes.Hp2}x{self.shapes.Wp2}x{self.shapes.K2}"]
         for r in self.ranks:
-            lines.append(f"  r{r.rank}: out{r.out_rows} conv2{r.conv2_rows} need{r.pool1_need} "
+            lines.append(f"  r{r.rank}: images{r.images} out{r.out_rows} conv2{r.conv2_rows} need{r.pool1_need} "
                          f"own{r.pool1_own} conv1{r.conv1_rows} in{r.in_rows} halo{r.halo}")
         return "\n".join(lines)
 
 
-def make_plan(cfg: NetConfig, world: int, strategy: str = "halo") -> Plan:
+def default_row_groups(world: int) -> int:
+    """Rows x batch shape used when the caller asks for ``row_groups="auto"``: two row groups whenever the
+    world is even (every rank has exactly one halo neighbour and the 13 final rows of AlexNet split 7/6),
+    otherwise the pure row split."""
+    return 2 if world >= 2 and world % 2 == 0 else world
+
+
+def make_plan(cfg: NetConfig, world: int, strategy: str = "halo", row_groups=None) -> Plan:
+    """``row_groups``: None / 0 = pure row split over all ranks (the reference's decomposition),
+    "auto" = :func:`default_row_groups`, or an explicit divisor R of ``world``."""
     if strategy not in ("halo", "recompute"):
         raise ValueError(strategy)
+    if row_groups == "auto":
+        row_groups = default_row_groups(world)
+    R = int(row_groups) if row_groups else world
+    if R < 1 or world % R != 0:
+        raise ValueError(f"row_groups={R} does not divide world={world}")
+    B = world // R
+    group = _make_row_plan(cfg, R, strategy)
+    shares = split_rows(cfg.batch, B)
+    ranks: List[RankPlan] = []
+    for bg in range(B):
+        for q in group:
+            ranks.append(RankPlan(
+                rank=bg * R + q.rank, world=world, out_rows=q.out_rows, conv2_rows=q.conv2_rows,
+                pool1_need=q.pool1_need, pool1_own=q.pool1_own, conv1_rows=q.conv1_rows, in_rows=q.in_rows,
+                halo=[(bg * R + p, lo, hi) for p, lo, hi in q.halo],
+                serves=[(bg * R + p, lo, hi) for p, lo, hi in q.serves],
+                images=shares[bg], row_group=q.rank, batch_group=bg))
+    return Plan(cfg, block12_shapes(cfg), world, strategy, ranks, R, B)
+
+
+def _make_row_plan(cfg: NetConfig, world: int, strategy: str) -> List[RankPlan]:
+    """The row decomposition of one image set over ``world`` ranks (ranks numbered inside the group)."""
     sh = block12_shapes(cfg)
     p1, p2 = cfg.conv1, cfg.conv2
     finals = split_rows(sh.Hp2, world)
@@ -142,7 +189,7 @@ def make_plan(cfg: NetConfig, world: int, strategy: str = "halo") -> Plan:
 
     if strategy == "halo":
         for rp in ranks:
-            if not rp.active:
+            if _len(rp.out_rows) == 0:
                 continue
             for other in ranks:
                 if other.rank == rp.rank or _len(other.pool1_own) == 0:
@@ -151,30 +198,40 @@ def make_plan(cfg: NetConfig, world: int, strategy: str = "halo") -> Plan:
                 if _len(ov):
                     rp.halo.append((other.rank, ov[0], ov[1]))
                     other.serves.append((rp.rank, ov[0], ov[1]))
-    return Plan(cfg, sh, world, strategy, ranks)
+    return ranks
 
 
 def validate_plan(plan: Plan) -> None:
     """Invariants (also exercised by hypothesis tests): output rows tile [0,Hp2) exactly,
     pool1 needs are covered by own+halo, halo rows come from their owner."""
     sh = plan.shapes
-    covered = []
+    assert plan.row_groups * plan.batch_groups == plan.world == len(plan.ranks)
+    imgs = []
+    for bg in range(plan.batch_groups):
+        members = [rp for rp in plan.ranks if rp.batch_group == bg]
+        assert [rp.rank for rp in members] == list(range(bg * plan.row_groups, (bg + 1) * plan.row_groups))
+        assert len({rp.images for rp in members}) == 1, "a row group must share one image range"
+        imgs.extend(range(*members[0].images))
+        covered = []
+        for rp in members:
+            covered.extend(range(*rp.out_rows))
+        assert covered == list(range(sh.Hp2)), "final rows are not an exact partition"
+        if plan.strategy == "halo":
+            owned = []
+            for rp in members:
+                owned.extend(range(*rp.pool1_own))
+            used = sorted(set(p for rp in members for p in range(*rp.pool1_need)))
+            assert owned == sorted(set(owned)), "pool1 ownership overlaps"
+            assert set(used) <= set(owned), "a needed pool1 row has no owner"
+    assert imgs == list(range(plan.cfg.batch)), "batch groups are not an exact partition of the images"
     for rp in plan.ranks:
-        covered.extend(range(*rp.out_rows))
-    assert covered == list(range(sh.Hp2)), "final rows are not an exact partition"
-    if plan.strategy == "halo":
-        owned = []
-        for rp in plan.ranks:
-            owned.extend(range(*rp.pool1_own))
-        used = sorted(set(p for rp in plan.ranks for p in range(*rp.pool1_need)))
-        assert owned == sorted(set(owned)), "pool1 ownership overlaps"
-        assert set(used) <= set(owned), "a needed pool1 row has no owner"
-    for rp in plan.ranks:
-        if not rp.active:
+        if _len(rp.out_rows) == 0:
             continue
         have = set(range(*rp.pool1_own))
         for (peer, lo, hi) in rp.halo:
-            po = plan.ranks[peer].pool1_own
+            q = plan.ranks[peer]
+            assert q.batch_group == rp.batch_group and q.images == rp.images, "halo peer works on other images"
+            po = q.pool1_own
             assert po[0] <= lo and hi <= po[1], "halo rows not owned by the named peer"
             have |= set(range(lo, hi))
         assert set(range(*rp.pool1_need)) <= have, "conv2 input rows not covered"

@@ -15,6 +15,12 @@ def make_parser(prog: str, *, init_default: str = INIT_CONST, lrn_default: str =
     add_cli_flags(ap, init_default=init_default, lrn_default=lrn_default)
     ap.add_argument("--strategy", choices=["halo", "recompute"], default="halo")
     ap.add_argument("--scatter", choices=["p2p", "sharded"], default="p2p")
+    ap.add_argument("--row-groups", default="rows",
+                    help="rows (default: the reference's pure row split), auto (2 row groups x np/2 batch groups) "
+                         "or a divisor R of np: R ranks split the rows of one share of the batch")
+    ap.add_argument("--gather", choices=["rank0", "host"], default="rank0",
+                    help="rank0: rows are stored into rank 0's device tensor over NVLink; host: every rank copies "
+                         "its rows into one shared pinned host tensor over its own PCIe link")
     ap.add_argument("--quiet-extras", action="store_true", help="print only the reference's lines")
     return ap
 

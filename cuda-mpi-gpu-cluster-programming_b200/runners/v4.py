@@ -46,9 +46,10 @@ def main(argv=None, variant: str = "v4") -> int:
         ctx.barrier()
         t0 = time.perf_counter()
         sess = Session(cfg, w, dist=ctx if ctx.world > 1 else None, device=ctx.device,
-                       precision=cfg.precision, strategy=ns.strategy, scatter=scatter)
-        lo, hi = sess.input_rows
-        xin = x[:, lo:hi].contiguous().pin_memory() if hi > lo else None
+                       precision=cfg.precision, strategy=ns.strategy, scatter=scatter,
+                       row_groups=_row_groups(ns), gather=ns.gather)
+        xin = sess.my_input(x)
+        xin = xin.contiguous().pin_memory() if xin is not None else None
         y = sess.infer(xin)
         ctx.barrier()
         ms = (time.perf_counter() - t0) * 1e3
@@ -75,6 +76,13 @@ def main(argv=None, variant: str = "v4") -> int:
     return 0
 
 
+def _row_groups(ns):
+    rg = getattr(ns, "row_groups", None)
+    if rg in (None, "", "rows"):
+        return None                      # the reference's decomposition: rows only
+    return "auto" if rg == "auto" else int(rg)
+
+
 def _oversubscribed(ns, cfg, variant, scatter) -> int:
     """More ranks than GPUs (the reference happily runs `mpirun -np 4` on one GPU, ref
     scripts/common_test_utils.sh:275).  Ranks that spin on each other's flags must never share a
@@ -95,7 +103,7 @@ def _oversubscribed(ns, cfg, variant, scatter) -> int:
     y = None
     if ctx.rank == 0:
         ew = EmulatedWorld(cfg, w, ctx.world, "cuda:0", precision=cfg.precision, strategy=ns.strategy,
-                           scatter=scatter)
+                           scatter=scatter, row_groups=_row_groups(ns))
         y = ew.forward(x.pin_memory().to("cuda:0", non_blocking=True)).cpu()
     ctx.barrier()
     ms = (time.perf_counter() - t0) * 1e3

@@ -130,6 +130,18 @@ typedef struct {
     const int* epoch;        /* optional device counter of forwards: when set, seg[].target is a
                                 per-forward increment and the wait target is (*epoch) * target, so
                                 the launch arguments never change (CUDA-graph friendly)         */
+    /* Flow control between forwards without a barrier (the role of the reference's MPI_Barrier pair,
+     * ref v4_mpi_cuda/src/main_mpi_cuda.cpp:151,154): no CTA of the launch starts before *gate >=
+     * gate_target (times *epoch when epoch is set); NULL = no gate.  The counter lives in local symmetric
+     * memory and is bumped by the rank that owns the buffers this launch writes to. */
+    const int* gate;
+    int gate_target;
+    /* Completion notice without an extra launch: every CTA adds 1 to *done_count (a local device
+     * counter that therefore grows by the grid size per launch) after its last store, and the CTA that
+     * completes a multiple of the grid size adds 1 to done[0..n_done) (usually rank 0's counter). */
+    int n_done;
+    unsigned int* done_count;
+    int* done[2];
 } b200_block_geom;
 
 /* host: [K][C][F][F] (reference layout) -> [F][F][C][K] used by the SIMT kernels */
@@ -227,10 +239,24 @@ int b200_enable_peer(int peer);
 /* pinned host -> device copy of `height` rows of `width` bytes with different pitches (cudaMemcpy2DAsync) */
 int b200_memcpy2d_h2d(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width, size_t height,
                       void* stream);
+/* device -> pinned host, rows of `width` bytes with different pitches: every rank writes the rows it owns
+ * straight into one host tensor (the reference's D2H + MPI_Gatherv, ref v4_mpi_cuda/src/main_mpi_cuda.cpp:100-130) */
+int b200_memcpy2d_d2h(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width, size_t height,
+                      void* stream);
+/* pin host memory this process did not allocate through CUDA (e.g. POSIX shm shared by all ranks) and return
+ * its device-side address; b200_host_flag_store writes one int there in stream order (a "my copy has landed"
+ * notice a reader in another process polls) */
+int b200_host_register(void* host, size_t bytes, void** dev_ptr);
+int b200_host_unregister(void* host);
+int b200_host_flag_store(int* flag_dev_ptr, int value, void* stream);
 int b200_flag_signal(int* const* targets, int n, int add, void* stream);
 int b200_flag_wait(const int* const* flags, const int* target, int n, int* status,
                    unsigned long long timeout_ns, const int* epoch /* NULL or device counter: target *= *epoch */,
                    void* stream);
+/* Opens a forward: ++*epoch (device counter of forwards, may be NULL) and adds 1 to each of the n (<= 16)
+ * `go` counters (local or peer).  Rank 0 calls it with every rank's gate counter, the others with n = 0:
+ * one tiny launch instead of an all-to-all barrier on the critical path. */
+int b200_flag_begin(int* epoch, int* const* go_targets, int n, void* stream);
 /* signal + wait in one launch (one GPU per rank only: the wait spins on peers' signals) */
 int b200_flag_barrier(int* const* signal_targets, const int* const* wait_flags, const int* wait_target,
                       int n, int* status, unsigned long long timeout_ns,

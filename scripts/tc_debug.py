@@ -35,7 +35,7 @@ for (H, W, B) in [(227, 227, 2), (99, 131, 1)]:
     y = eng.forward(x.cuda())
     torch.cuda.synchronize()
     print("status", eng.status())
-    p1 = eng.buf_pool1.tensor((B, eng.sh.Hp1, eng.sh.Wp1, eng.sh.K1)).cpu()
+    p1 = eng.pool1_view().cpu()
     report(f"pool1 {H}x{W}", p1, forward_torch_reference(x, w, cfg, upto="pool1"))
     report(f"out   {H}x{W}", y.cpu(), forward_torch_reference(x, w, cfg))
 print("tc_debug done")

@@ -25,7 +25,7 @@ def test_tc_matches_oracle(H, W, batch):
     eng = single_gpu_engine(cfg, w, "cuda:0")
     y = eng.forward(x.cuda()).cpu()
     eng.check_status()
-    p1 = eng.buf_pool1.tensor((batch, eng.sh.Hp1, eng.sh.Wp1, eng.sh.K1)).cpu()
+    p1 = eng.pool1_view().cpu()
     assert _rel(p1, forward_torch_reference(x, w, cfg, upto="pool1")) < TOL
     assert y.shape == ref.shape
     assert _rel(y, ref) < TOL
@@ -45,7 +45,8 @@ def test_tc_const_closed_form():
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
-@pytest.mark.parametrize("strategy,scatter", [("halo", "p2p"), ("halo", "sharded"), ("recompute", "p2p")])
+@pytest.mark.parametrize("strategy,scatter", [("halo", "p2p"), ("halo", "sharded"), ("recompute", "p2p"),
+                                              ("recompute", "sharded")])
 def test_tc_emulated_ranks_equal_single(world, strategy, scatter):
     from b200cnn.models.engine import single_gpu_engine, EmulatedWorld
     cfg = default_config(batch=2, init=INIT_RAND, seed=9, precision="tf32")
@@ -65,3 +66,17 @@ def test_tc_agrees_with_simt_twin():
     a = single_gpu_engine(cfg, w, "cuda:0", "simt").forward(x.cuda()).clone()
     b = single_gpu_engine(cfg, w, "cuda:0", "tf32").forward(x.cuda()).clone()
     assert _rel(b, a) < TOL
+
+
+@pytest.mark.parametrize("world,R", [(2, 1), (4, 2), (8, 2), (8, 4), (6, 3)])
+@pytest.mark.parametrize("scatter,gather", [("p2p", "rank0"), ("sharded", "rank0"), ("sharded", "local")])
+def test_tc_rows_x_batch_equal_single(world, R, scatter, gather):
+    """R row groups x B batch groups (uneven: 5 images over up to 4 groups), flow-control gate instead of a
+    barrier, pool1 slabs alternating by forward parity: three forwards in a row, bit-equal to one rank."""
+    from b200cnn.models.engine import single_gpu_engine, EmulatedWorld
+    cfg = default_config(batch=5, init=INIT_RAND, seed=13, precision="tf32")
+    x, w = make_problem(cfg)
+    one = single_gpu_engine(cfg, w, "cuda:0").forward(x.cuda()).clone()
+    ew = EmulatedWorld(cfg, w, world, "cuda:0", strategy="halo", scatter=scatter, row_groups=R, gather=gather)
+    for _ in range(3):
+        assert torch.equal(ew.forward(x.cuda()), one)

@@ -39,6 +39,16 @@ def test_all_gpus_equal_np1():
     assert f1 == fn, out
 
 
+@pytest.mark.parametrize("extra", [("--gather", "host"), ("--row-groups", "auto", "--gather", "host"),
+                                   ("--row-groups", "auto", "--strategy", "recompute")])
+def test_all_gpus_rows_x_batch_and_host_gather_equal_np1(extra):
+    """Rows x batch decomposition, the barrier-free forward and the shared-host-tensor gather on real peers."""
+    n = torch.cuda.device_count()
+    f1, _, _ = _run(1, "v5")
+    fn, _, out = _run(n, "v5", extra)
+    assert f1 == fn, out
+
+
 def test_full_network_tp_np2_equals_np1():
     """Full AlexNet: spatial blocks 1-2 + tensor-parallel FC over real peer memory."""
     outs = []

@@ -57,6 +57,39 @@ def test_decomposed_equals_whole_227(world, strategy):
     assert torch.equal(got, ref)        # same op order per output => bit-identical
 
 
+def test_rows_x_batch_plan_8_ranks():
+    """8 ranks as 2 row groups x 4 batch groups: 7/6 final rows instead of 2,2,2,2,2,1,1,1; one halo neighbour."""
+    plan = make_plan(default_config(batch=128), 8, "halo", row_groups=2)
+    validate_plan(plan)
+    assert (plan.row_groups, plan.batch_groups) == (2, 4)
+    assert [rp.images for rp in plan.ranks] == [(0, 32)] * 2 + [(32, 64)] * 2 + [(64, 96)] * 2 + [(96, 128)] * 2
+    assert [rp.out_rows for rp in plan.ranks] == [(0, 7), (7, 13)] * 4
+    assert plan.ranks[5].halo == [(4, 12, 14)] and plan.ranks[4].halo == [(5, 14, 17)]
+    assert plan.ranks[4].serves == [(5, 12, 14)]
+    assert make_plan(default_config(batch=128), 8, "halo", "auto").row_groups == 2
+    assert make_plan(default_config(batch=128), 3, "halo", "auto").row_groups == 3      # odd world: pure rows
+    assert make_plan(default_config(batch=128), 8, "halo").row_groups == 8              # default: the reference's split
+    with pytest.raises(ValueError):
+        make_plan(default_config(batch=8), 8, "halo", row_groups=3)
+
+
+@settings(max_examples=120, deadline=None)
+@given(H=st.integers(35, 500), batch=st.integers(1, 9), R=st.integers(1, 4), B=st.integers(1, 4),
+       strategy=st.sampled_from(["halo", "recompute"]))
+def test_rows_x_batch_invariants(H, batch, R, B, strategy):
+    validate_plan(make_plan(default_config(H=H, W=67, batch=batch), R * B, strategy, row_groups=R))
+
+
+@pytest.mark.parametrize("world,R", [(2, 1), (4, 2), (8, 2), (6, 3), (8, 4)])
+@pytest.mark.parametrize("strategy", ["halo", "recompute"])
+def test_rows_x_batch_decomposed_equals_whole(world, R, strategy):
+    cfg = default_config(H=131, W=99, batch=5, init=INIT_RAND, seed=3)     # 5 images over up to 4 batch groups: uneven
+    x, w = make_problem(cfg)
+    ref = forward_cpu(x, w, cfg)
+    got = forward_cpu_decomposed(x, w, cfg, world, strategy, row_groups=R)
+    assert torch.equal(got, ref)
+
+
 def test_decomposed_more_ranks_than_rows():
     cfg = default_config(H=83, W=83, batch=2, init=INIT_RAND, seed=5)   # 4 final rows
     x, w = make_problem(cfg)
