@@ -46,6 +46,9 @@ def parse():
     ap.add_argument("--strategy", choices=["halo", "recompute"], default="halo",
                     help="halo (default): per-layer row ownership, boundary pool1 rows cross NVLink inside the fused "
                          "kernels; recompute: overlapped tiling, no inter-layer traffic")
+    ap.add_argument("--halo", choices=["push", "pull"], default="push",
+                    help="push: conv1's epilogue stores boundary pool1 rows into the neighbour's slab (P2P stores), conv2 "
+                         "reads local memory through TMA; pull: conv2's loader reads them from the neighbour (P2P loads)")
     ap.add_argument("--row-groups", default="auto",
                     help="auto: 2 row groups x N/2 batch groups; rows: pure row split over all N ranks; or a divisor of N")
     ap.add_argument("--scatter", choices=["p2p", "sharded"], default="sharded",
@@ -202,7 +205,7 @@ def run_ours(a):
     strategy = a.strategy if N > 1 else "single-gpu"
     scatter = a.scatter if N > 1 else "local"
     sess = Session(cfg, w, dist=dist_arg, device=dev, precision=precision, strategy=a.strategy,
-                   scatter=a.scatter, row_groups=rg, gather="rank0")
+                   scatter=a.scatter, row_groups=rg, gather="rank0", halo=a.halo)
     plan = sess.engine.plan
     check = None
     if N > 1 and not a.no_check:
@@ -225,15 +228,17 @@ def run_ours(a):
     alternatives = None
     if a.alt and N > 1:
         alternatives = {
-            "p2p_scatter_images_per_s": quick_ms(strategy=a.strategy, scatter="p2p", row_groups=rg),
-            "pure_rows_images_per_s": quick_ms(strategy=a.strategy, scatter=a.scatter, row_groups=None),
+            "as_timed_images_per_s": quick_ms(strategy=a.strategy, scatter=a.scatter, row_groups=rg, halo=a.halo),
+            "halo_pull_images_per_s": quick_ms(strategy=a.strategy, scatter=a.scatter, row_groups=rg, halo="pull"),
+            "p2p_scatter_images_per_s": quick_ms(strategy=a.strategy, scatter="p2p", row_groups=rg, halo=a.halo),
+            "pure_rows_images_per_s": quick_ms(strategy=a.strategy, scatter=a.scatter, row_groups=None, halo=a.halo),
             "recompute_images_per_s": quick_ms(strategy="recompute", scatter=a.scatter, row_groups=rg),
             "note": "warm back-to-back forwards, no L2 flush (not comparable with value)"}
 
     e2e = None
     if not a.no_e2e:
         es = Session(cfg, w, dist=dist_arg, device=dev, precision=precision, strategy=a.strategy,
-                     scatter=a.scatter, row_groups=rg, gather=a.e2e_gather, slots=4)
+                     scatter=a.scatter, row_groups=rg, gather=a.e2e_gather, slots=4, halo=a.halo)
         e2e_ms, h2d, d2h, last = measure_e2e(es)
         h2d_all = sum(ctx.all_gather_object(h2d))
         d2h_all = sum(ctx.all_gather_object(d2h))
@@ -259,7 +264,7 @@ def run_ours(a):
                    "global_batch": a.batch, "input": f"{a.height}x{a.width}x3",
                    "parallelism": (f"spatial rows x batch: {plan.row_groups} row groups x {plan.batch_groups} batch groups"
                                    if N > 1 else "single-gpu"),
-                   "strategy": strategy, "scatter": scatter, "gather": "rank0 (P2P stores from the LRN epilogue)" if N > 1 else "local",
+                   "strategy": strategy, "halo": a.halo if N > 1 else None, "scatter": scatter, "gather": "rank0 (P2P stores from the LRN epilogue)" if N > 1 else "local",
                    "check": check, "alternatives": alternatives, "host_binding": host_binding,
                    "vs_baseline_note": "value / the reference's published best V4 images/s at this np (other hardware, batch 1)",
                    "l2": "flushed between timed iterations (256 MiB fill, untimed)"},

@@ -189,6 +189,9 @@ simt_block_kernel(const float* __restrict__ wt,    // [F][F*C][K]
                     v = v / powf(g.lrn.k + a * ss, g.lrn.beta);
                 }
                 out[(((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * K + k] = v;
+                for (int m = 0; m < g.n_mirror; ++m)           // halo push: the neighbour's copy of this row
+                    if (pr >= g.mirror[m].lo && pr < g.mirror[m].hi)
+                        g.mirror[m].ptr[(((size_t)n * g.mirror[m].slab + (pr - g.mirror[m].base)) * g.Wp + pc) * K + k] = v;
             }
         }
     }
@@ -232,7 +235,7 @@ extern "C" int b200_simt_block(const float* wt, const float* bias, float* out,
                                const b200_block_geom* g, void* stream) {
     if (!g || !wt || !bias || !out) return B200_ERR_ARG;
     if (g->nseg < 1 || g->nseg > B200_MAX_SEG || g->n_signal < 0 || g->n_signal > B200_MAX_SIGNAL ||
-        g->n_done < 0 || g->n_done > 2)
+        g->n_done < 0 || g->n_done > 2 || g->n_mirror < 0 || g->n_mirror > B200_MAX_MIRROR)
         return B200_ERR_ARG;
     const int rows = g->p1 - g->p0;
     if (rows <= 0 || g->N <= 0) return B200_OK;

@@ -78,6 +78,134 @@ __device__ __forceinline__ const float* seg_row_ptr(const b200_block_geom& g, in
     return nullptr;
 }
 
+// ------------------------------------------------------ shared fused epilogue ----
+// TMEM -> shared memory -> 3x3/2 max-pool -> +bias, ReLU [-> LRN over channels] -> store (+ halo push), used by
+// every kernel whose accumulator is pixels x channels (tc_block_kernel, tc_block_db_kernel, tc_block_pair_kernel).
+// kWarps epilogue warps (4: one 128-pixel accumulator; 8: two) synchronise on named barrier kBar; warp `we`
+// drains TMEM lane quarter we % 4 of accumulator we / 4, 32 channels at a time, into a double-buffered chunk
+// buffer; each warp then pools a subset of the pooled pixels (lane = channel inside the chunk).
+// `release()` runs once every tcgen05.ld of the calling warp has completed — the double-buffered kernels hand
+// the accumulator back to the MMA warp there, BEFORE the LRN pass.
+__device__ __forceinline__ float* out_ptr_at(float* base, int n, int slab, int row0, int pr, int Wp, int pc, int N) {
+    return base + (((size_t)n * slab + (pr - row0)) * Wp + pc) * N;
+}
+
+template <int kBar, int kWarps>
+__device__ __forceinline__ void bar_group() {
+    asm volatile("bar.sync %0, %1;" ::"n"(kBar), "n"(kWarps * 32) : "memory");
+}
+
+template <int kBar, int kWarps, typename Release>
+__device__ __forceinline__ void epilogue_pool_lrn(const TcParams& p, uint32_t tmem_acc, float* cbuf0, int cbuf_floats,
+                                                  float* pbuf, const int2* ptab, const float* s_bias, float* out,
+                                                  int n, int pr0, int pc0, int we, int lane, bool has_acc,
+                                                  Release&& release) {
+    const b200_block_geom& g = p.g;
+    const int N = g.K;
+    const int q = we & 3, hacc = we >> 2;
+    const int te = we * 32 + lane;
+    const int row = hacc * 128 + q * 32 + lane;              // pixel slot this thread drains
+    const int PP = p.PR * p.PC, nchunk = N / 32, NP = N + 4; // pbuf row: [2 zeros | N channels | 2 zeros]
+    const bool do_lrn = g.lrn.N_lrn > 0;
+    for (int cc = 0; cc < ((p.dbg & 4) ? 0 : nchunk); ++cc) {
+        float* cb = cbuf0 + (cc & 1) * cbuf_floats;
+        if (has_acc) {
+            uint32_t r[32];
+            tmem_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)(hacc * N + cc * 32), r);
+#pragma unroll
+            for (int c = 0; c < 32; ++c) cb[row * kCbufPitch + c] = __uint_as_float(r[c]);
+        }
+        bar_group<kBar, kWarps>();                            // chunk cc is whole; chunk cc-1's reads are over
+        const float bch = s_bias[cc * 32 + lane];
+        for (int pp = we; pp < ((p.dbg & 32) ? 0 : PP); pp += kWarps) {
+            const int2 e = ptab[pp];
+            const float* c0p = cb + e.x + lane;
+            float mx = -INFINITY;
+#pragma unroll
+            for (int a = 0; a < 3; ++a)
+#pragma unroll
+                for (int b = 0; b < 3; ++b) mx = fmaxf(mx, c0p[(a * p.TC + b) * kCbufPitch]);
+            float val = fmaxf(mx + bch, 0.f);                 // relu(max(x)+b) == max(relu(x+b))
+            if (do_lrn) {
+                pbuf[pp * NP + 2 + cc * 32 + lane] = val;
+            } else {
+                const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
+                if (p.round_out) val = to_tf32(val);
+                if (pr < g.p1 && pr < g.Hp && pc < g.Wp) {
+                    out_ptr_at(out, n, g.out_slab, g.out_base, pr, g.Wp, pc, N)[cc * 32 + lane] = val;
+                    for (int m = 0; m < g.n_mirror; ++m)      // halo push: the neighbour's copy of this row
+                        if (pr >= g.mirror[m].lo && pr < g.mirror[m].hi)
+                            out_ptr_at(g.mirror[m].ptr, n, g.mirror[m].slab, g.mirror[m].base, pr, g.Wp, pc,
+                                       N)[cc * 32 + lane] = val;
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncwarp();
+    release();
+    if (do_lrn && !(p.dbg & (4 | 16))) {
+        bar_group<kBar, kWarps>();                            // pbuf is whole
+        const int half = g.lrn.N_lrn / 2;
+        const float al = g.lrn.mode == B200_LRN_ALPHA_OVER_N ? g.lrn.alpha / (float)max(g.lrn.N_lrn, 1) : g.lrn.alpha;
+        const float nbeta = -g.lrn.beta;
+        const bool win5 = g.lrn.N_lrn == 5;                   // AlexNet's window: straight-line 5 taps
+        for (int pp0 = 0; pp0 < PP; pp0 += 4) {               // 4 independent pixels per trip (ILP)
+            float* optr[4];
+            const float* prow[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int pp = pp0 + u < PP ? pp0 + u : PP - 1;
+                const int2 e = ptab[pp];
+                const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
+                const bool ok = pp0 + u < PP && pr < g.p1 && pr < g.Hp && pc < g.Wp;
+                optr[u] = ok ? out_ptr_at(out, n, g.out_slab, g.out_base, pr, g.Wp, pc, N) : nullptr;
+                prow[u] = pbuf + pp * NP;                     // channel c sits at prow[c + 2]
+            }
+            for (int c = te; c < N; c += kWarps * 32) {
+                float val[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const float* px = prow[u] + c;
+                    float ss;
+                    if (win5) {
+                        const float a0 = px[0], a1 = px[1], a2 = px[2], a3 = px[3], a4 = px[4];
+                        ss = fmaf(a0, a0, fmaf(a1, a1, fmaf(a2, a2, fmaf(a3, a3, a4 * a4))));
+                    } else {
+                        ss = 0.f;
+                        const int c_lo = max(0, c - half), c_hi = min(N - 1, c + half);
+                        for (int qq = c_lo; qq <= c_hi; ++qq) ss = fmaf(prow[u][qq + 2], prow[u][qq + 2], ss);
+                    }
+                    // x / (k + a*ss)^beta; the base is >= k > 0, so exp2/log2 is safe
+                    val[u] = px[2] * exp2f(nbeta * __log2f(g.lrn.k + al * ss));
+                    if (p.round_out) val[u] = to_tf32(val[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (optr[u]) optr[u][c] = val[u];
+            }
+        }
+    }
+    bar_group<kBar, kWarps>();                                // cbuf / pbuf free again, all stores issued
+    if (g.n_signal > 0 && te == 0) {                          // producer side of the halo flags
+        __threadfence_system();
+        for (int i = 0; i < g.n_signal; ++i) red_release_sys_add(g.signal[i] + n, 1);
+    }
+}
+
+// pooled-pixel table (cbuf offset of the window origin, (pi,pj)) and the zero borders of the LRN rows
+template <int kThreadsInGroup>
+__device__ __forceinline__ void epilogue_tables(const TcParams& p, int2* ptab, float* pbuf, int te) {
+    const int PP = p.PR * p.PC, N = p.g.K, NP = N + 4;
+    if (te < PP) {
+        const int pi = te / p.PC, pj = te - pi * p.PC;
+        ptab[te] = make_int2(((2 * pi) * p.TC + 2 * pj) * kCbufPitch, (pi << 16) | pj);
+    }
+    if (p.g.lrn.N_lrn > 0)
+        for (int i = te; i < PP * 4; i += kThreadsInGroup)
+            pbuf[(i >> 2) * NP + ((i & 3) < 2 ? (i & 3) : N + (i & 3))] = 0.f;
+}
+
 // ------------------------------------------------------------------------ kernel ----
 // kPatch = false ("vec" mode, C % 32 == 0: conv2..5): a k-block is 32 channels of one filter tap;
 //   every A row is 128 contiguous bytes of the activation -> cp.async 16 B straight into the
@@ -153,11 +281,6 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
             const int pi = m / p.TC;
             pij[i] = m < p.TR * p.TC ? (pi << 16) | (m - pi * p.TC) : -1;
         }
-        if (tid < p.PR * p.PC) {                              // pooled pixel -> cbuf offset, (pi,pj)
-            const int pi = tid / p.PC, pj = tid - pi * p.PC;
-            ptab[tid] = make_int2(((2 * pi) * p.TC + 2 * pj) * kCbufPitch, (pi << 16) | pj);
-        }
-        bar_producers();
         int it = 0;
         for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x, ++it) {
             const int n = (int)(w / tiles_per_img);
@@ -276,98 +399,9 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
             // ------------------------------ epilogue ------------------------------------
             mbar_wait(tmem_full_bar, (uint32_t)(it & 1));
             tc_fence_after();
-            const int q4 = warp & 3, hacc = warp >> 2;         // TMEM lane quarter, accumulator
-            const int row = hacc * 128 + q4 * 32 + lane;       // pixel slot this thread drains
-            const bool has_acc = hacc < p.nacc;
-            const int PP = p.PR * p.PC;
-            const int nchunk = N / 32;
-            const bool do_lrn = g.lrn.N_lrn > 0;
-            const int NP = N + 4;                              // pbuf row: [2 zeros | N channels | 2 zeros]
-            if (do_lrn)
-                for (int i = tid; i < PP * 4; i += kProducerThreads)
-                    pbuf[(i >> 2) * NP + ((i & 3) < 2 ? (i & 3) : N + (i & 3))] = 0.f;
-            for (int cc = 0; cc < ((p.dbg & 4) ? 0 : nchunk); ++cc) {
-                float* cb = cbuf0 + (cc & 1) * (kCbufBytes / 4);
-                if (has_acc) {
-                    uint32_t r[32];
-                    tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(hacc * N + cc * 32), r);
-#pragma unroll
-                    for (int c = 0; c < 32; ++c) cb[row * kCbufPitch + c] = __uint_as_float(r[c]);
-                }
-                bar_producers();
-                // pool: lane = channel inside the chunk, warp strides over pooled pixels
-                const float bch = s_bias[cc * 32 + lane];
-                for (int pp = warp; pp < ((p.dbg & 32) ? 0 : PP); pp += kProducerWarps) {
-                    const int2 e = ptab[pp];
-                    const float* c0p = cb + e.x + lane;
-                    float mx = -INFINITY;
-#pragma unroll
-                    for (int a = 0; a < 3; ++a)
-#pragma unroll
-                        for (int b = 0; b < 3; ++b)
-                            mx = fmaxf(mx, c0p[(a * p.TC + b) * kCbufPitch]);
-                    float val = fmaxf(mx + bch, 0.f);          // relu(max(x)+b) == max(relu(x+b))
-                    if (do_lrn) {
-                        pbuf[pp * NP + 2 + cc * 32 + lane] = val;
-                    } else {
-                        const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
-                        if (p.round_out) val = to_tf32(val);
-                        if (pr < g.p1 && pr < g.Hp && pc < g.Wp)
-                            out[(((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N +
-                                cc * 32 + lane] = val;
-                    }
-                }
-            }
-            if (do_lrn && !(p.dbg & (4 | 16))) {
-                bar_producers();
-                const int half = g.lrn.N_lrn / 2;
-                const float al = g.lrn.mode == B200_LRN_ALPHA_OVER_N
-                                     ? g.lrn.alpha / (float)g.lrn.N_lrn : g.lrn.alpha;
-                const float nbeta = -g.lrn.beta;
-                const bool win5 = g.lrn.N_lrn == 5;           // AlexNet's window: straight-line 5 taps
-                for (int pp0 = 0; pp0 < PP; pp0 += 4) {       // 4 independent pixels per trip (ILP)
-                    float* optr[4];
-                    const float* prow[4];
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const int pp = pp0 + u < PP ? pp0 + u : PP - 1;
-                        const int2 e = ptab[pp];
-                        const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
-                        const bool ok = pp0 + u < PP && pr < g.p1 && pr < g.Hp && pc < g.Wp;
-                        optr[u] = ok ? out + (((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N : nullptr;
-                        prow[u] = pbuf + pp * NP;              // channel c sits at prow[c + 2]; 2 zero pads each side
-                    }
-                    for (int c = tid; c < N; c += kProducerThreads) {
-                        float val[4];
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            const float* px = prow[u] + c;
-                            float ss;
-                            if (win5) {
-                                const float a0 = px[0], a1 = px[1], a2 = px[2], a3 = px[3], a4 = px[4];
-                                ss = fmaf(a0, a0, fmaf(a1, a1, fmaf(a2, a2, fmaf(a3, a3, a4 * a4))));
-                            } else {
-                                ss = 0.f;
-                                const int c_lo = max(0, c - half), c_hi = min(N - 1, c + half);
-                                for (int q = c_lo; q <= c_hi; ++q) ss = fmaf(prow[u][q + 2], prow[u][q + 2], ss);
-                            }
-                            // x / (k + a*ss)^beta; the base is >= k > 0, so exp2/log2 is safe
-                            val[u] = px[2] * exp2f(nbeta * __log2f(g.lrn.k + al * ss));
-                            if (p.round_out) val[u] = to_tf32(val[u]);
-                        }
-#pragma unroll
-                        for (int u = 0; u < 4; ++u)
-                            if (optr[u]) optr[u][c] = val[u];
-                    }
-                }
-            }
-            // hand the stages / TMEM back: all tcgen05.ld of this warp are complete (wait::ld)
-            tc_fence_before();
-            bar_producers();                                   // everyone is done with cbuf/pbuf
-            if (g.n_signal > 0 && tid == 0) {                  // producer side of the halo flags
-                __threadfence_system();
-                for (int i = 0; i < g.n_signal; ++i) red_release_sys_add(g.signal[i] + n, 1);
-            }
+            epilogue_tables<kProducerThreads>(p, ptab, pbuf, tid);   // pbuf aliases the stages: borders per tile
+            epilogue_pool_lrn<1, kProducerWarps>(p, tmem_base, cbuf0, kCbufBytes / 4, pbuf, ptab, s_bias, out, n, pr0,
+                                                 pc0, warp, lane, (warp >> 2) < p.nacc, [] {});
             if (lane == 0) mbar_arrive(tile_free_bar);
         }
     } else if (warp == kMmaWarp) {
@@ -375,7 +409,8 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
         for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
             for (int kb = 0; kb < p.nkb; ++kb) {
                 if (!(p.dbg & 8)) mbar_wait(full_bar + 8 * stage, phase);
-                tc_fence_after();
+                fence_proxy_async_smem();                       // cp.async (generic proxy) wrote A; the MMA reads it
+                tc_fence_after();                               // through the async proxy
                 if (lane == 0) {
                     const uint32_t a_stage = base + stage * kAStageBytes;
                     const uint32_t b_stage = base + b_off + stage * p.b_stage_bytes;
@@ -562,27 +597,33 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                     hsel[i] = ok ? pi * g.S : -1;
                     xb[i] = ((cc0 + pj) * g.S - g.P) * g.C * 4;
                 }
-                if (kPixTma) {
-                    // k-blocks [0, nkb_main) arrive by TMA (warp 9); the producers only keep the barrier
-                    // counts uniform there.  The tail k-blocks hold floats 32.. of every run: chunk j of tail
-                    // block t is the 16 B at run offset 128 B of filter row 8t + j.
+                if (sp.direct == 2) {
+                    // Row K order (shared by both loaders, so they are bit-identical): k-block kb < nkb_main holds
+                    // floats 0..31 of filter row kb's run of every pixel; tail block t holds, as chunk j, the 16 B at
+                    // run offset 128 B of filter row 8t + j.  kPixTma: the main blocks arrive by TMA (warp 9) and the
+                    // producers only keep the barrier counts uniform there.
                     for (int kb = 0; kb < p.nkb; ++kb) {
                         mbar_wait(empty_bar + 8 * stage, phase ^ 1);
-                        if (kb >= sp.nkb_main) {
+                        const bool tail = kb >= sp.nkb_main;
+                        if (tail || !kPixTma) {
                             const uint32_t a_dst = base + stage * kAStageBytes + dst0;
-                            const int tfy = 8 * (kb - sp.nkb_main) + j;
+                            const int tfy = tail ? 8 * (kb - sp.nkb_main) + j : kb;
+                            const int boff = tail ? 128 : 16 * j;
 #pragma unroll
                             for (int i = 0; i < 8; ++i) {
                                 if (i >= 4 * p.nacc) break;
                                 const char* rp = (tfy < g.F && hsel[i] >= 0)
                                                      ? reinterpret_cast<const char*>(rowtab[hsel[i] + tfy]) : nullptr;
-                                cp_async16(a_dst + i * 4096u, rp + (xb[i] + 128), rp ? 16u : 0u);
+                                cp_async16(a_dst + i * 4096u, rp + (xb[i] + boff), rp ? 16u : 0u);
                             }
-                            cp_async_wait_all();
-                            fence_proxy_async_smem();
                         }
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(full_bar + 8 * stage);
+                        if (kPixTma) {
+                            if (tail) { cp_async_wait_all(); fence_proxy_async_smem(); }
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(full_bar + 8 * stage);
+                        } else {
+                            cp_async_mbar_arrive_noinc(full_bar + 8 * stage);
+                        }
                         if (++stage == NS) { stage = 0; phase ^= 1; }
                     }
                     continue;
@@ -660,6 +701,7 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
             tc_fence_after();
             for (int kb = 0; kb < p.nkb; ++kb) {
                 mbar_wait(full_bar + 8 * stage, phase);
+                fence_proxy_async_smem();                       // producers' cp.async data -> async-proxy reads
                 tc_fence_after();
                 if (lane == 0) {
                     const uint64_t dpix = make_smem_desc(base + stage * kAStageBytes);
@@ -749,8 +791,13 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                         float val = fmaxf(mx + bch, 0.f);
                         if (p.round_out) val = to_tf32(val);
                         const int pcg = pc0 + pc;
-                        if (prg < g.p1 && prg < g.Hp && pcg < g.Wp && ch < KO)
+                        if (prg < g.p1 && prg < g.Hp && pcg < g.Wp && ch < KO) {
                             out[(((size_t)n * g.out_slab + (prg - g.out_base)) * g.Wp + pcg) * KO + ch] = val;
+                            for (int m = 0; m < g.n_mirror; ++m)   // halo push: the neighbour's copy of this row
+                                if (prg >= g.mirror[m].lo && prg < g.mirror[m].hi)
+                                    out_ptr_at(g.mirror[m].ptr, n, g.mirror[m].slab, g.mirror[m].base, prg, g.Wp, pcg,
+                                               KO)[ch] = val;
+                        }
                     }
                     __syncwarp();
                 }
@@ -926,6 +973,7 @@ tc_block_db_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_const
             tc_fence_after();
             for (int kb = 0; kb < p.nkb; ++kb) {
                 mbar_wait(full_bar + 8 * stage, phase);
+                fence_proxy_async_smem();                       // producers' cp.async data -> async-proxy reads
                 tc_fence_after();
                 if (lane == 0) {
                     const uint64_t da = make_smem_desc(base + stage * kDbAStageBytes);
@@ -960,23 +1008,9 @@ tc_block_db_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_const
         }
     } else {
         // ======================================= epilogue warps ==========================
-        const int q = warp & 3;                                // TMEM lane quarter this warp may read
-        const int we = warp - kDbEpiWarp0, te = we * 32 + lane; // warp / thread index inside the epilogue group
-        const int row = q * 32 + lane;                         // pixel slot this thread drains
-        const int PP = p.PR * p.PC, nchunk = N / 32, NP = N + 4;
-        const bool do_lrn = g.lrn.N_lrn > 0;
-        if (te < PP) {
-            const int pi = te / p.PC, pj = te - pi * p.PC;
-            ptab[te] = make_int2(((2 * pi) * p.TC + 2 * pj) * kCbufPitch, (pi << 16) | pj);
-        }
-        if (do_lrn)                                            // pbuf row: [2 zeros | N channels | 2 zeros]
-            for (int i = te; i < PP * 4; i += 128)
-                pbuf[(i >> 2) * NP + ((i & 3) < 2 ? (i & 3) : N + (i & 3))] = 0.f;
+        const int we = warp & 3;                               // TMEM lane quarter this warp may read (warps 10..13)
+        epilogue_tables<128>(p, ptab, pbuf, (warp - kDbEpiWarp0) * 32 + lane);
         bar_epilogue();
-        const int half = g.lrn.N_lrn / 2;
-        const float al = g.lrn.mode == B200_LRN_ALPHA_OVER_N ? g.lrn.alpha / (float)max(g.lrn.N_lrn, 1) : g.lrn.alpha;
-        const float nbeta = -g.lrn.beta;
-        const bool win5 = g.lrn.N_lrn == 5;
         int buf = 0;
         uint32_t bphase = 0;
         for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
@@ -986,80 +1020,9 @@ tc_block_db_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_const
             const int pr0 = g.p0 + tr_i * p.PR, pc0 = tc_i * p.PC;
             mbar_wait(tfull_bar + 8 * buf, bphase);
             tc_fence_after();
-            for (int cc = 0; cc < nchunk; ++cc) {
-                float* cb = cbuf0 + (cc & 1) * (kDbCbufBytes / 4);
-                uint32_t r[32];
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * N + cc * 32), r);
-#pragma unroll
-                for (int c = 0; c < 32; ++c) cb[row * kCbufPitch + c] = __uint_as_float(r[c]);
-                bar_epilogue();                                 // chunk cc is whole; chunk cc-1's reads are over
-                const float bch = s_bias[cc * 32 + lane];
-                for (int pp = we; pp < PP; pp += 4) {           // lane = channel inside the chunk
-                    const int2 e = ptab[pp];
-                    const float* c0p = cb + e.x + lane;
-                    float mx = -INFINITY;
-#pragma unroll
-                    for (int a = 0; a < 3; ++a)
-#pragma unroll
-                        for (int b = 0; b < 3; ++b) mx = fmaxf(mx, c0p[(a * p.TC + b) * kCbufPitch]);
-                    float val = fmaxf(mx + bch, 0.f);
-                    if (do_lrn) {
-                        pbuf[pp * NP + 2 + cc * 32 + lane] = val;
-                    } else {
-                        const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
-                        if (p.round_out) val = to_tf32(val);
-                        if (pr < g.p1 && pr < g.Hp && pc < g.Wp)
-                            out[(((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N + cc * 32 + lane] = val;
-                    }
-                }
-            }
-            // every tcgen05.ld of this warp has completed (wait::ld): hand the accumulator back now, so the
-            // MMAs of the tile after next overlap the LRN pass below
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(tempty_bar + 8 * buf);
-            if (do_lrn) {
-                bar_epilogue();                                 // pbuf is whole
-                for (int pp0 = 0; pp0 < PP; pp0 += 4) {
-                    float* optr[4];
-                    const float* prow[4];
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const int pp = pp0 + u < PP ? pp0 + u : PP - 1;
-                        const int2 e = ptab[pp];
-                        const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
-                        const bool ok = pp0 + u < PP && pr < g.p1 && pr < g.Hp && pc < g.Wp;
-                        optr[u] = ok ? out + (((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N : nullptr;
-                        prow[u] = pbuf + pp * NP;
-                    }
-                    for (int c = te; c < N; c += 128) {
-                        float val[4];
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            const float* px = prow[u] + c;
-                            float ss;
-                            if (win5) {
-                                const float a0 = px[0], a1 = px[1], a2 = px[2], a3 = px[3], a4 = px[4];
-                                ss = fmaf(a0, a0, fmaf(a1, a1, fmaf(a2, a2, fmaf(a3, a3, a4 * a4))));
-                            } else {
-                                ss = 0.f;
-                                const int c_lo = max(0, c - half), c_hi = min(N - 1, c + half);
-                                for (int qq = c_lo; qq <= c_hi; ++qq) ss = fmaf(prow[u][qq + 2], prow[u][qq + 2], ss);
-                            }
-                            val[u] = px[2] * exp2f(nbeta * __log2f(g.lrn.k + al * ss));
-                            if (p.round_out) val[u] = to_tf32(val[u]);
-                        }
-#pragma unroll
-                        for (int u = 0; u < 4; ++u)
-                            if (optr[u]) optr[u][c] = val[u];
-                    }
-                }
-            }
-            bar_epilogue();                                     // cbuf / pbuf free again, all stores issued
-            if (g.n_signal > 0 && te == 0) {                    // producer side of the halo flags
-                __threadfence_system();
-                for (int i = 0; i < g.n_signal; ++i) red_release_sys_add(g.signal[i] + n, 1);
-            }
+            const uint32_t tb = tempty_bar + 8 * buf;
+            epilogue_pool_lrn<2, 4>(p, tmem_base + (uint32_t)(buf * N), cbuf0, kDbCbufBytes / 4, pbuf, ptab, s_bias, out,
+                                    n, pr0, pc0, we, lane, true, [&] { if (lane == 0) mbar_arrive(tb); });
             if (++buf == 2) { buf = 0; bphase ^= 1; }
         }
     }
@@ -1156,6 +1119,19 @@ tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_co
             const int rem = (int)(w - (long long)n * tiles_per_img);
             const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
             const int cr0 = 2 * (g.p0 + tr_i * p.PR), cc0 = 2 * (tc_i * p.PC);
+            const int ir0 = cr0 * g.S - g.P;                   // first input row of the tile
+            if (p.any_flag) {                                   // pushed halo rows of image n have landed?
+                if (lane == 0) {
+                    const int IRT = (p.TR - 1) * g.S + g.F;
+                    for (int s = 0; s < g.nseg; ++s)
+                        if (g.seg[s].flag && ir0 < g.seg[s].hi && ir0 + IRT > g.seg[s].lo)
+                            wait_flag_ge(g.seg[s].flag + n, g.seg[s].target * (g.epoch ? *g.epoch : 1), g.status,
+                                         g.timeout_ns);
+                    fence_proxy_async_global();                 // peer's generic stores -> our TMA reads
+                }
+                __syncwarp();
+            }
+            const int y0 = ir0 - g.seg[0].base;                 // slab-relative row of filter row 0
             int fy = 0, fx = 0, cch = 0;
             for (int kb = 0; kb < p.nkb; ++kb) {
                 mbar_wait(empty_bar + 8 * stage, phase ^ 1);
@@ -1163,7 +1139,7 @@ tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_co
                     const uint32_t fb = full_bar + 8 * stage;
                     if (rank == 0) mbar_arrive_expect_tx(fb, 2u * (pp.a_box_bytes + pp.b_half_bytes));
                     tma2_load_4d(base + stage * kDbAStageBytes, &tmapA, cch * kBlockK, cc0 * g.S + fx - g.P,
-                                 cr0 * g.S + fy - g.P, n, fb);
+                                 y0 + fy, n, fb);
                     tma2_load_2d(base + b_off + stage * pp.b_half_bytes, &tmapBh, kb * kBlockK,
                                  (int)rank * (N / 2), fb);
                 }
@@ -1201,23 +1177,9 @@ tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_co
         }
     } else {
         // ======================================= epilogue warps ==========================
-        const int q = warp & 3;
-        const int we = warp - kPairEpiWarp0, te = we * 32 + lane;
-        const int row = q * 32 + lane;
-        const int PP = p.PR * p.PC, nchunk = N / 32, NP = N + 4;
-        const bool do_lrn = g.lrn.N_lrn > 0;
-        if (te < PP) {
-            const int pi = te / p.PC, pj = te - pi * p.PC;
-            ptab[te] = make_int2(((2 * pi) * p.TC + 2 * pj) * kCbufPitch, (pi << 16) | pj);
-        }
-        if (do_lrn)
-            for (int i = te; i < PP * 4; i += 128)
-                pbuf[(i >> 2) * NP + ((i & 3) < 2 ? (i & 3) : N + (i & 3))] = 0.f;
+        const int we = warp & 3;                               // TMEM lane quarter this warp may read (warps 2..5)
+        epilogue_tables<128>(p, ptab, pbuf, (warp - kPairEpiWarp0) * 32 + lane);
         bar_epilogue();
-        const int half = g.lrn.N_lrn / 2;
-        const float al = g.lrn.mode == B200_LRN_ALPHA_OVER_N ? g.lrn.alpha / (float)max(g.lrn.N_lrn, 1) : g.lrn.alpha;
-        const float nbeta = -g.lrn.beta;
-        const bool win5 = g.lrn.N_lrn == 5;
         int buf = 0;
         uint32_t bphase = 0;
         for (long long pt = pair_id; 2 * pt < p.total_tiles; pt += npairs) {
@@ -1225,10 +1187,11 @@ tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_co
             const bool valid = w < p.total_tiles;               // CTA-uniform
             mbar_wait(tfull_bar + 8 * buf, bphase);
             tc_fence_after();
+            const uint32_t tb = tempty_bar + 8 * buf;
             if (!valid) {                                       // duplicate of the partner's tile: drop it
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive_leader(tempty_bar + 8 * buf);
+                if (lane == 0) mbar_arrive_leader(tb);
                 if (++buf == 2) { buf = 0; bphase ^= 1; }
                 continue;
             }
@@ -1236,74 +1199,8 @@ tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_co
             const int rem = (int)(w - (long long)n * tiles_per_img);
             const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
             const int pr0 = g.p0 + tr_i * p.PR, pc0 = tc_i * p.PC;
-            for (int cc = 0; cc < nchunk; ++cc) {
-                float* cb = cbuf0 + (cc & 1) * (kDbCbufBytes / 4);
-                uint32_t r[32];
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * N + cc * 32), r);
-#pragma unroll
-                for (int c = 0; c < 32; ++c) cb[row * kCbufPitch + c] = __uint_as_float(r[c]);
-                bar_epilogue();
-                const float bch = s_bias[cc * 32 + lane];
-                for (int ppx = we; ppx < PP; ppx += 4) {
-                    const int2 e = ptab[ppx];
-                    const float* c0p = cb + e.x + lane;
-                    float mx = -INFINITY;
-#pragma unroll
-                    for (int a = 0; a < 3; ++a)
-#pragma unroll
-                        for (int b = 0; b < 3; ++b) mx = fmaxf(mx, c0p[(a * p.TC + b) * kCbufPitch]);
-                    float val = fmaxf(mx + bch, 0.f);
-                    if (do_lrn) {
-                        pbuf[ppx * NP + 2 + cc * 32 + lane] = val;
-                    } else {
-                        const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
-                        if (p.round_out) val = to_tf32(val);
-                        if (pr < g.p1 && pr < g.Hp && pc < g.Wp)
-                            out[(((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N + cc * 32 + lane] = val;
-                    }
-                }
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_leader(tempty_bar + 8 * buf);   // accumulator back before the LRN pass
-            if (do_lrn) {
-                bar_epilogue();
-                for (int pp0 = 0; pp0 < PP; pp0 += 4) {
-                    float* optr[4];
-                    const float* prow[4];
-#pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const int ppx = pp0 + u < PP ? pp0 + u : PP - 1;
-                        const int2 e = ptab[ppx];
-                        const int pr = pr0 + (e.y >> 16), pc = pc0 + (e.y & 0xFFFF);
-                        const bool ok = pp0 + u < PP && pr < g.p1 && pr < g.Hp && pc < g.Wp;
-                        optr[u] = ok ? out + (((size_t)n * g.out_slab + (pr - g.out_base)) * g.Wp + pc) * N : nullptr;
-                        prow[u] = pbuf + ppx * NP;
-                    }
-                    for (int c = te; c < N; c += 128) {
-                        float val[4];
-#pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            const float* px = prow[u] + c;
-                            float ss;
-                            if (win5) {
-                                const float a0 = px[0], a1 = px[1], a2 = px[2], a3 = px[3], a4 = px[4];
-                                ss = fmaf(a0, a0, fmaf(a1, a1, fmaf(a2, a2, fmaf(a3, a3, a4 * a4))));
-                            } else {
-                                ss = 0.f;
-                                const int c_lo = max(0, c - half), c_hi = min(N - 1, c + half);
-                                for (int qq = c_lo; qq <= c_hi; ++qq) ss = fmaf(prow[u][qq + 2], prow[u][qq + 2], ss);
-                            }
-                            val[u] = px[2] * exp2f(nbeta * __log2f(g.lrn.k + al * ss));
-                            if (p.round_out) val[u] = to_tf32(val[u]);
-                        }
-#pragma unroll
-                        for (int u = 0; u < 4; ++u)
-                            if (optr[u]) optr[u][c] = val[u];
-                    }
-                }
-            }
-            bar_epilogue();
+            epilogue_pool_lrn<2, 4>(p, tmem_base + (uint32_t)(buf * N), cbuf0, kDbCbufBytes / 4, pbuf, ptab, s_bias, out,
+                                    n, pr0, pc0, we, lane, true, [&] { if (lane == 0) mbar_arrive_leader(tb); });
             if (++buf == 2) { buf = 0; bphase ^= 1; }
         }
     }
@@ -1318,8 +1215,46 @@ tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_co
 }
 
 // --------------------------------------------------------------------------- host ----
+// Which kernel serves a layer is a process-wide policy, decided ONCE (environment at first use, or
+// b200_tc_set_policy) and never by a getenv on the launch path:
+//   conv2-type layers (C % 32 == 0):  auto = CTA-pair kernel where its TMA-fed operands apply (stride 1, one
+//     local slab), else the double-buffered kernel;  "single" / "db" / "pair" force one (pair still falls back
+//     to db on geometries it cannot take)
+//   conv1-type layers (C % 32 != 0, K_out <= 128): auto = pixel operand by TMA when the input slab is local and
+//     eligible, else cp.async;  "cpasync" forces the LSU loader.  Both loaders use one K order, so they are
+//     bit-identical.
+struct Policy {
+    int conv2 = 0;        // 0 auto, 1 single-buffered, 2 double-buffered, 3 pair
+    int conv1_tma = 1;    // 1 auto (TMA when eligible), 0 cp.async only
+    int no_swap = 0;      // conv1-type layers through the generic kernel (experiments)
+    int no_direct = 0;    // conv1: shared-memory patch instead of the direct loader (experiments)
+    int dbg = 0;          // perf-decomposition knobs of tc_block_kernel (TcParams::dbg)
+};
+
+int parse_conv2(const char* v) {
+    if (!v) return 0;
+    if (!strcmp(v, "single")) return 1;
+    if (!strcmp(v, "db")) return 2;
+    if (!strcmp(v, "pair")) return 3;
+    return 0;
+}
+
+Policy& policy() {
+    static Policy pol = [] {
+        Policy q;
+        q.conv2 = parse_conv2(getenv("B200_TC_CONV2"));
+        if (const char* e = getenv("B200_TC_CONV1")) q.conv1_tma = strcmp(e, "cpasync") != 0;
+        q.no_swap = getenv("B200_TC_NO_SWAP") != nullptr;
+        q.no_direct = getenv("B200_TC_NO_DIRECT") != nullptr;
+        if (const char* e = getenv("B200_TC_DBG")) q.dbg = atoi(e);
+        return q;
+    }();
+    return pol;
+}
+
 struct TcConv {
     int K, C, F, Kpad, device, patch_mode, FCpad;
+    int sms;                                             // SMs of `device`
     float* d_w;
     CUtensorMap tmap;
     // pixel-TMA mode (draft): weights in the K order (fy | run floats 0..31), then tail blocks (8 filter rows x
@@ -1382,7 +1317,7 @@ inline bool direct_eligible(const b200_block_geom* g) {
     const int pitch = g->in_pitch ? g->in_pitch : g->W * g->C;
     return is_patch_mode(g->C) && g->K <= 128 && g->lrn.N_lrn == 0 && g->P == 0 && (g->S * g->C) % 4 == 0 &&
            pitch % 4 == 0 && pitch >= (g->Wc - 1) * g->S * g->C + fcpad(g->F, g->C) &&
-           !getenv("B200_TC_NO_DIRECT");
+           !policy().no_direct;
 }
 
 bool plan_tiles(const b200_block_geom* g, TcParams* p, int max_nacc = 2) {
@@ -1430,7 +1365,7 @@ int fill_params(const b200_block_geom* g, TcParams* p, int flags, int max_nacc =
     p->nkb = num_kblocks(g->F, g->C);
     p->FCpad = fcpad(g->F, g->C);
     p->round_out = flags & 1;
-    if (const char* e = getenv("B200_TC_DBG")) p->dbg = atoi(e);
+    p->dbg = policy().dbg;
     p->b_stage_bytes = g->K * 128;
     size_t patch_bytes = 0;
     if (patch) {
@@ -1486,7 +1421,8 @@ int fill_swapped(const b200_block_geom* g, SwParams* sp, int flags) {
 }
 
 // double-buffered kernel: layout [A stages | B stages | 2 cbuf | pbuf | ctl]
-inline bool db_requested(const b200_block_geom* g) { return !is_patch_mode(g->C) && getenv("B200_TC_DB") != nullptr; }
+// conv2-type layers run 128-pixel tiles (db / pair kernels) unless the single-buffered kernel is forced
+inline bool db_requested(const b200_block_geom* g) { return !is_patch_mode(g->C) && policy().conv2 != 1; }
 
 int fill_db(const b200_block_geom* g, DbParams* dp, int flags) {
     if (is_patch_mode(g->C)) return B200_ERR_UNSUPPORTED;
@@ -1518,7 +1454,15 @@ size_t smem_bytes_db(const DbParams& dp) {
 // pixel-TMA mode: turn a direct-mode plan into a TMA-fed one and encode the S row-phase maps.  Returns false
 // (leave sp untouched) when the shape, the geometry or the driver does not take it.
 bool try_pixel_tma(const TcConv* t, const b200_block_geom* g, SwParams* sp, PixMaps* pm) {
-    if (!getenv("B200_TC_TMA1") || !sp->direct || t->nkb_tma == 0 || g->nseg != 1 || g->seg[0].flag) return false;
+    if (!policy().conv1_tma || !sp->direct || t->nkb_tma == 0 || g->nseg != 1 || g->seg[0].flag) return false;
+    {   // TMA only over memory of this GPU (an input that lives on a peer is pulled by the cp.async loader)
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, g->seg[0].ptr) != cudaSuccess || at.type != cudaMemoryTypeDevice ||
+            at.device != t->device) {
+            (void)cudaGetLastError();
+            return false;
+        }
+    }
     if (g->S < 1 || g->S > 4 || g->seg[0].base % g->S != 0 || g->P != 0) return false;
     const TcParams& p = sp->t;
     if (p.TC > 256 || p.TR > 256) return false;
@@ -1544,24 +1488,33 @@ bool try_pixel_tma(const TcConv* t, const b200_block_geom* g, SwParams* sp, PixM
     }
     for (int r = g->S; r < 4; ++r) maps.m[r] = maps.m[0];
     *pm = maps;
-    sp->direct = 2;
-    sp->nkb_main = g->F;
     sp->pix_bytes = (uint32_t)(kBlockK * p.TC * p.TR * 4);
-    sp->t.nkb = t->nkb_tma;
     return true;
 }
 
 // CTA-pair kernel: layout [A stages | B half stages | 2 cbuf | pbuf | ctl]
 inline bool pair_requested(const b200_block_geom* g) {
-    return !is_patch_mode(g->C) && getenv("B200_TC_PAIR") != nullptr;
+    return !is_patch_mode(g->C) && (policy().conv2 == 0 || policy().conv2 == 3);
+}
+
+// true when every row segment is a window of ONE local slab (same pointer, base and height): the halo rows were
+// pushed into this rank's own copy, so a single tensor map covers everything conv reads
+bool one_local_slab(const TcConv* t, const b200_block_geom* g) {
+    for (int s = 1; s < g->nseg; ++s)
+        if (g->seg[s].ptr != g->seg[0].ptr || g->seg[s].base != g->seg[0].base || g->seg[s].slab != g->seg[0].slab)
+            return false;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, g->seg[0].ptr) != cudaSuccess || at.type != cudaMemoryTypeDevice ||
+        at.device != t->device) {
+        (void)cudaGetLastError();
+        return false;
+    }
+    return true;
 }
 
 int fill_pair(const TcConv* t, const b200_block_geom* g, PairParams* pp, CUtensorMap* tmapA, int flags) {
-    if (is_patch_mode(g->C) || !t->half_ok || g->S != 1) return B200_ERR_UNSUPPORTED;
-    // first version: one local row segment that is the whole image, no cross-GPU flags or signals
-    if (g->nseg != 1 || g->seg[0].flag || g->n_signal != 0 || g->seg[0].base != 0 || g->seg[0].slab != g->H ||
-        g->seg[0].lo > 0 || g->seg[0].hi < g->H)
-        return B200_ERR_UNSUPPORTED;
+    if (is_patch_mode(g->C) || !t->half_ok || g->S != 1 || t->sms < 2) return B200_ERR_UNSUPPORTED;
+    if (!one_local_slab(t, g)) return B200_ERR_UNSUPPORTED;
     int rc = fill_params(g, &pp->t, flags, /*max_nacc=*/1);
     if (rc != B200_OK) return rc;
     TcParams& p = pp->t;
@@ -1584,12 +1537,16 @@ int fill_pair(const TcConv* t, const b200_block_geom* g, PairParams* pp, CUtenso
     while (cols < 2 * g->K) cols *= 2;
     p.tmem_cols = cols;
     pp->idesc2 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(g->K >> 3) << 17) | ((256u >> 4) << 24);
-    // A operand: the NHWC activation itself, box = one filter tap x 32 channels of a whole TR x TC tile
+    // A operand: the NHWC slab itself (rows [base, base+slab) of every image), box = one filter tap x 32 channels
+    // of a whole TR x TC tile; rows and columns outside the slab read as zero, which is the conv's padding at the
+    // image border and never reaches a valid output elsewhere (the slab holds every row this rank's pixels need)
     EncodeTiledFn enc = get_encode();
     if (!enc) return B200_ERR_UNSUPPORTED;
     const int pitch = g->in_pitch ? g->in_pitch : g->W * g->C;
-    cuuint64_t dims[4] = {(cuuint64_t)g->C, (cuuint64_t)g->W, (cuuint64_t)g->H, (cuuint64_t)g->N};
-    cuuint64_t strides[3] = {(cuuint64_t)g->C * 4, (cuuint64_t)pitch * 4, (cuuint64_t)g->seg[0].slab * pitch * 4};
+    const int slab = g->seg[0].slab;
+    if (slab <= 0 || (pitch * 4) % 16 != 0) return B200_ERR_UNSUPPORTED;
+    cuuint64_t dims[4] = {(cuuint64_t)g->C, (cuuint64_t)g->W, (cuuint64_t)slab, (cuuint64_t)g->N};
+    cuuint64_t strides[3] = {(cuuint64_t)g->C * 4, (cuuint64_t)pitch * 4, (cuuint64_t)slab * pitch * 4};
     cuuint32_t box[4] = {(cuuint32_t)kBlockK, (cuuint32_t)p.TC, (cuuint32_t)p.TR, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     if (enc(tmapA, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)g->seg[0].ptr, dims, strides, box, estr,
@@ -1624,6 +1581,7 @@ extern "C" int b200_tc_conv_create(const float* w_kcff, int K, int C, int F, voi
     t->FCpad = fcpad(F, C);
     t->Kpad = num_kblocks(F, C) * kBlockK;
     B200_CUDA_TRY(cudaGetDevice(&t->device));
+    B200_CUDA_TRY(cudaDeviceGetAttribute(&t->sms, cudaDevAttrMultiProcessorCount, t->device));
     // [K][C][F][F] -> K-major rows [K][Kpad], TF32-rounded, zero padded; k order per mode (see kernel)
     std::vector<float> wk((size_t)K * t->Kpad, 0.f);
     for (int k = 0; k < K; ++k)
@@ -1652,7 +1610,7 @@ extern "C" int b200_tc_conv_create(const float* w_kcff, int K, int C, int F, voi
         return B200_ERR_CUDA;
     }
     t->half_ok = 0;
-    if (!t->patch_mode && K % 16 == 0 && K <= 256 && getenv("B200_TC_PAIR")) {   // draft path: opt-in at create time too
+    if (!t->patch_mode && K % 32 == 0 && K <= 256) {                 // CTA-pair kernel: each CTA stages K/2 weight rows
         cuuint32_t hbox[2] = {(cuuint32_t)kBlockK, (cuuint32_t)(K / 2)};
         if (enc(&t->tmap_half, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, t->d_w, dims, strides, hbox, estr,
                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -1662,7 +1620,7 @@ extern "C" int b200_tc_conv_create(const float* w_kcff, int K, int C, int F, voi
     // pixel-TMA K order: only for runs of 33..36 floats (one 16 B tail chunk per filter row), K_out <= 128
     t->nkb_tma = 0;
     t->d_w_tma = nullptr;
-    if (t->patch_mode && K <= 128 && F * C > kBlockK && t->FCpad <= kBlockK + 4 && getenv("B200_TC_TMA1")) {
+    if (t->patch_mode && K <= 128 && F * C > kBlockK && t->FCpad <= kBlockK + 4) {
         const int nkb = F + cdiv(F, 8);
         const int kp = nkb * kBlockK;
         std::vector<float> wt((size_t)K * kp, 0.f);
@@ -1700,6 +1658,19 @@ extern "C" int b200_tc_conv_destroy(void* handle) {
     return B200_OK;
 }
 
+// key: "conv2" = auto|single|db|pair, "conv1" = auto|cpasync, "no_swap" / "no_direct" / "dbg" = integer
+extern "C" int b200_tc_set_policy(const char* key, const char* value) {
+    if (!key || !value) return B200_ERR_ARG;
+    Policy& q = policy();
+    if (!strcmp(key, "conv2")) q.conv2 = parse_conv2(value);
+    else if (!strcmp(key, "conv1")) q.conv1_tma = strcmp(value, "cpasync") != 0;
+    else if (!strcmp(key, "no_swap")) q.no_swap = atoi(value);
+    else if (!strcmp(key, "no_direct")) q.no_direct = atoi(value);
+    else if (!strcmp(key, "dbg")) q.dbg = atoi(value);
+    else return B200_ERR_ARG;
+    return B200_OK;
+}
+
 extern "C" int b200_tc_block_tiles(const b200_block_geom* g) {
     if (!g) return B200_ERR_ARG;
     if (g->p1 <= g->p0) return 0;
@@ -1719,13 +1690,12 @@ extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const 
     TcConv* t = (TcConv*)handle;
     if (!t || !bias || !out || !g) return B200_ERR_ARG;
     if (g->nseg < 1 || g->nseg > B200_MAX_SEG || g->n_signal < 0 || g->n_signal > B200_MAX_SIGNAL ||
-        g->n_done < 0 || g->n_done > 2)
+        g->n_done < 0 || g->n_done > 2 || g->n_mirror < 0 || g->n_mirror > B200_MAX_MIRROR)
         return B200_ERR_ARG;
     if (g->K != t->K || g->C != t->C || g->F != t->F) return B200_ERR_ARG;
     if (g->p1 <= g->p0 || g->N <= 0) return B200_OK;
-    static int sms = 0;
-    if (!sms) B200_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, t->device));
-    if (t->patch_mode && g->K <= 128 && g->lrn.N_lrn == 0 && !getenv("B200_TC_NO_SWAP")) {
+    const int sms = t->sms;
+    if (t->patch_mode && g->K <= 128 && g->lrn.N_lrn == 0 && !policy().no_swap) {
         SwParams sp;
         memset(&sp, 0, sizeof(sp));
         if (fill_swapped(g, &sp, flags) == B200_OK) {       // else fall through to the generic kernel
@@ -1733,7 +1703,13 @@ extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const 
             const unsigned grid = (unsigned)(sp.t.total_tiles < sms ? sp.t.total_tiles : sms);
             PixMaps pm;
             memset(&pm, 0, sizeof(pm));
-            if (try_pixel_tma(t, g, &sp, &pm)) {
+            const bool row_order = sp.direct && t->nkb_tma > 0;     // the handle has weights in the row K order
+            if (row_order) {
+                sp.direct = 2;
+                sp.nkb_main = g->F;
+                sp.t.nkb = t->nkb_tma;
+            }
+            if (row_order && try_pixel_tma(t, g, &sp, &pm)) {
                 B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_swapped_kernel<true>,
                                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
                 tc_block_swapped_kernel<true><<<grid, kSwThreads, smem, (cudaStream_t)stream>>>(t->tmap_tma, sp, bias,
@@ -1741,8 +1717,8 @@ extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const 
             } else {
                 B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_swapped_kernel<false>,
                                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-                tc_block_swapped_kernel<false><<<grid, kSwThreads, smem, (cudaStream_t)stream>>>(t->tmap, sp, bias,
-                                                                                                out, pm);
+                tc_block_swapped_kernel<false><<<grid, kSwThreads, smem, (cudaStream_t)stream>>>(
+                    row_order ? t->tmap_tma : t->tmap, sp, bias, out, pm);
             }
             B200_CUDA_TRY(cudaGetLastError());
             return B200_OK;

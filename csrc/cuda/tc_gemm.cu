@@ -166,6 +166,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_constant_
             tc_fence_after();
             for (int kb = gt.kb0; kb < gt.kb1; ++kb) {
                 mbar_wait(full_bar + 8 * stage, phase);
+                fence_proxy_async_smem();                       // producers' cp.async data -> async-proxy reads
                 tc_fence_after();
                 if (lane == 0) {
                     const uint64_t da = make_smem_desc(base + stage * kAStage);

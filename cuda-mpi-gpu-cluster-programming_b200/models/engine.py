@@ -87,11 +87,17 @@ class Blocks12Engine:
                  world: int = 1, *, precision: Optional[str] = None, strategy: str = "halo",
                  scatter: str = "p2p", timeout_ns: int = cu.DEFAULT_TIMEOUT_NS,
                  device_epoch: Optional[bool] = None, use_graph: Optional[bool] = None,
-                 row_groups=None, gather: str = "rank0", slots: int = 2):
+                 row_groups=None, gather: str = "rank0", slots: int = 2, halo: str = "push"):
         if scatter not in ("p2p", "sharded"):
             raise ValueError(scatter)
         if gather not in ("rank0", "local"):
             raise ValueError(gather)
+        if halo not in ("push", "pull"):
+            raise ValueError(halo)
+        # halo="push": conv1's epilogue also stores the boundary pool1 rows into the neighbour's slab (P2P stores
+        # over NVLink, then the arrival counter), so conv2 reads local memory only and can be fed by TMA;
+        # halo="pull": conv2's loader reads them from the neighbour's slab (P2P loads in the producer warps).
+        self.halo = halo
         # gather="rank0": the LRN epilogue stores every rank's rows into rank 0's output tensor over NVLink
         # (the reference's MPI_Gatherv); "local": every rank keeps the rows of the images it owns (callers
         # that want the result in HOST memory read each rank's rows back over that rank's own PCIe link).
@@ -180,7 +186,8 @@ class Blocks12Engine:
                 self.s2d_y0, self.s2d_ys = 0, 0
             self.buf_s2d = [symm.alloc(f"s2d{i}", self.in_imgs * self.s2d_ys * self.s2d_ws * self.s2d_c * f4)
                             for i in range(self.n_in_buf)]
-        own = rp.pool1_own[1] - rp.pool1_own[0]
+        self.p1_base, self.p1_rows = self._pool1_slab(rp)
+        own = self.p1_rows
         # two pool1 slabs, used alternately by forward parity: a neighbour may still read forward k's rows
         # while this rank's conv1 already writes forward k+1's
         self.buf_pool1 = [symm.alloc(f"pool1_{i}", N * own * sh.Wp1 * sh.K1 * f4) for i in range(2)]
@@ -210,6 +217,14 @@ class Blocks12Engine:
         # tiles per image of every rank's block 1 (arrival-counter targets)
         self._b1_tiles = [self._tiles(self._geom_block1(r, probe=True)) for r in range(self.world)]
 
+    def _pool1_slab(self, rp: RankPlan):
+        """(first global row, rows) of a rank's pool1 slab: the rows it owns, plus — when halos are pushed — the
+        neighbours' rows its conv2 reads."""
+        lo, hi = rp.pool1_own
+        if self.halo == "push" and rp.halo:
+            lo, hi = min(lo, rp.pool1_need[0]), max(hi, rp.pool1_need[1])
+        return lo, max(hi - lo, 0)
+
     def _flag_ptr(self, rank: int, int_index: int) -> int:
         return self.symm.ptr(rank, "flags") + 4 * int_index
 
@@ -231,7 +246,8 @@ class Blocks12Engine:
     def pool1_view(self) -> torch.Tensor:
         """This rank's pool1 rows of the latest forward, [n_img, own rows, Wp1, K1]."""
         sh, (a, b) = self.sh, self.rp.pool1_own
-        return self.buf_pool1[self.epoch & 1].tensor((self.n_img, b - a, sh.Wp1, sh.K1))
+        t = self.buf_pool1[self.epoch & 1].tensor((self.n_img, self.p1_rows, sh.Wp1, sh.K1))
+        return t[:, a - self.p1_base:b - self.p1_base]
 
     def h2d(self, i: int, x_host: torch.Tensor) -> None:
         """Pinned host [N, rows, W, C] -> input buffer ``i`` on the current stream.  A pitched input is
@@ -258,6 +274,7 @@ class Blocks12Engine:
         s2d = self.s2d
         S1 = p1.S
         Hin = self.s2d_hs if s2d else sh.H
+        mirrors = []
         if probe:
             segs = [dict(ptr=1, base=0, slab=Hin, lo=0, hi=Hin)]
             signals, out_ptr = [], 0
@@ -274,15 +291,27 @@ class Blocks12Engine:
                              lo=rp.in_rows[0], hi=rp.in_rows[1])]
             signals = [self._flag_ptr(peer, self.lay.arr_off + r * self.lay.nmax)
                        for peer in sorted({p for p, _, _ in rp.serves})]
+            if self.halo == "push":
+                parity = self.epoch & 1
+                for peer, lo, hi in rp.serves:
+                    pb, prows = self._pool1_slab(self.plan.ranks[peer])
+                    mirrors.append(dict(ptr=self.symm.ptr(peer, f"pool1_{parity}"), base=pb, slab=prows, lo=lo, hi=hi))
+        # p2p scatter: the images are rank 0's upload of THIS forward, so conv1 on the other ranks may only start
+        # once rank 0 has opened the forward (its stage_open follows the upload in stream order)
+        gate = {}
+        if not probe and self.scatter == "p2p" and self.world > 1 and r != 0:
+            gate = dict(gate_ptr=self._flag_ptr(r, self.lay.go_off),
+                        gate_target=1 if self.device_epoch else self.epoch,
+                        epoch_ptr=self._flag_ptr(r, self.lay.epoch_off) if self.device_epoch else 0)
         conv = dict(H=Hin, W=self.s2d_ws, Cin=self.s2d_c, F=-(-p1.F // S1), S=1, P=0) if s2d else \
             dict(H=sh.H, W=sh.W, Cin=sh.C, F=p1.F, S=p1.S, P=p1.P, in_pitch=self.in_pitch)
         g = cu.make_block_geom(
             N=rp.n_images, K=p1.K, **conv,
             Hc=sh.Hc1, Wc=sh.Wc1, Hp=sh.Hp1, Wp=sh.Wp1, rows=rp.pool1_own,
-            out_base=rp.pool1_own[0], out_slab=rp.pool1_own[1] - rp.pool1_own[0], lrn=None,
-            segs=segs, signals=signals,
+            out_base=self._pool1_slab(rp)[0], out_slab=self._pool1_slab(rp)[1], lrn=None,
+            segs=segs, signals=signals, mirrors=mirrors,
             status_ptr=0 if probe else self._flag_ptr(self.rank, self.lay.status_off),
-            timeout_ns=self.timeout_ns)
+            timeout_ns=self.timeout_ns, **gate)
         return g
 
     def _geom_block2(self, parity: int = 0):
@@ -290,10 +319,14 @@ class Blocks12Engine:
         own0, own1 = rp.pool1_own
         segs = []
         if own1 > own0:
-            segs.append(dict(ptr=self.buf_pool1[parity].ptr, base=own0, slab=own1 - own0, lo=own0, hi=own1))
+            segs.append(dict(ptr=self.buf_pool1[parity].ptr, base=self.p1_base, slab=self.p1_rows, lo=own0, hi=own1))
         for peer, lo, hi in rp.halo:
-            po = self.plan.ranks[peer].pool1_own
-            segs.append(dict(ptr=self.symm.ptr(peer, f"pool1_{parity}"), base=po[0], slab=po[1] - po[0],
+            if self.halo == "push":      # the neighbour's epilogue stored these rows into OUR slab
+                src = dict(ptr=self.buf_pool1[parity].ptr, base=self.p1_base, slab=self.p1_rows)
+            else:
+                pb, prows = self._pool1_slab(self.plan.ranks[peer])
+                src = dict(ptr=self.symm.ptr(peer, f"pool1_{parity}"), base=pb, slab=prows)
+            segs.append(dict(**src,
                              lo=lo, hi=hi,
                              flag=self._flag_ptr(self.rank, self.lay.arr_off + peer * self.lay.nmax),
                              target=(1 if self.device_epoch else self.epoch) * self._b1_tiles[peer]))
@@ -478,12 +511,12 @@ class EmulatedWorld:
 
     def __init__(self, cfg: NetConfig, weights: Blocks12Weights, world: int, device="cuda:0",
                  precision: Optional[str] = None, strategy: str = "halo", scatter: str = "p2p",
-                 row_groups=None, gather: str = "rank0", slots: int = 2):
+                 row_groups=None, gather: str = "rank0", slots: int = 2, halo: str = "push"):
         self.symm = LocalSymm(world, device)
         self.engines: List[Blocks12Engine] = [
             Blocks12Engine(cfg, weights, self.symm.view(r), r, world, precision=precision,
                            strategy=strategy, scatter=scatter, device_epoch=False, use_graph=False,
-                           row_groups=row_groups, gather=gather)
+                           row_groups=row_groups, gather=gather, halo=halo)
             for r in range(world)]
         for e in self.engines:
             e.finalize()

@@ -40,7 +40,7 @@ class Session:
 
     def __init__(self, cfg: NetConfig, weights: Blocks12Weights, dist=None, device=None,
                  precision: Optional[str] = None, strategy: str = "halo", scatter: str = "p2p",
-                 row_groups=None, gather: str = "rank0", slots: int = 2):
+                 row_groups=None, gather: str = "rank0", slots: int = 2, halo: str = "push"):
         if gather not in ("rank0", "host"):
             raise ValueError(gather)
         self.cfg = cfg
@@ -58,7 +58,7 @@ class Session:
         self.gather = gather if world > 1 else "rank0"
         self.engine = Blocks12Engine(cfg, weights, self.symm, rank, world, precision=precision,
                                      strategy=strategy, scatter=scatter, row_groups=row_groups,
-                                     gather="local" if self.gather == "host" else "rank0", slots=slots)
+                                     gather="local" if self.gather == "host" else "rank0", slots=slots, halo=halo)
         self.symm.commit()
         self.engine.finalize()
         e = self.engine
@@ -173,57 +173,3 @@ class Session:
         with torch.cuda.device(self.device):
             for s in (self.s_in, self.s_compute, self.s_out):
                 s.synchronize()
-
-
-def autotune_conv2_kernel(cfg: NetConfig, weights: Blocks12Weights, x: torch.Tensor, device="cuda:0",
-                          prefer: str = "auto", reps: int = 5) -> dict:
-    """Single-GPU choice between the two conv2-type kernels of ``csrc/cuda/tc_block.cu``: the default
-    ``tc_block_kernel`` (one 256-pixel tile fills TMEM, epilogue serial) and the opt-in ``tc_block_db_kernel``
-    (128-pixel tiles, double-buffered TMEM, dedicated epilogue warps; ``B200_TC_DB=1``).  Both run ``x`` ([N,H,W,C]
-    host or device tensor); the double-buffered kernel is selected only if its output is bit-identical to the
-    default kernel's, stays identical under CUDA-graph replay, and (``prefer="auto"``) is faster.  Sets or clears
-    ``B200_TC_DB`` for the engines created afterwards in this process and returns what it measured."""
-    dev = torch.device(device)
-
-    def probe(db: bool):
-        if db:
-            os.environ["B200_TC_DB"] = "1"
-        else:
-            os.environ.pop("B200_TC_DB", None)
-        s = Session(cfg, weights, device=dev, precision="tf32", strategy="halo", scatter="sharded")
-        e = s.engine
-        with torch.cuda.device(dev):
-            e.input_view(0).copy_(x.to(dev))
-            y = e.forward_enqueue(0, 0).clone()
-            for _ in range(3):
-                e.forward_enqueue(0, 0)
-            torch.cuda.synchronize(dev)
-            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            t0.record()
-            for _ in range(reps):
-                e.forward_enqueue(0, 0)
-            t1.record()
-            t1.synchronize()
-            y2 = e.forward_enqueue(0, 0).clone()             # graph replay, several tiles per CTA behind it
-            e.check_status()
-        return y, t0.elapsed_time(t1) / reps, bool(torch.equal(y, y2))
-
-    os.environ.pop("B200_TC_DB", None)
-    if prefer == "single":
-        return {"used": "single_buffered"}
-    try:
-        y_s, ms_s, _ = probe(False)
-        y_d, ms_d, stable = probe(True)
-        same = bool(torch.equal(y_s, y_d)) and stable
-        use_db = same and (prefer == "double" or ms_d < ms_s)
-        info = {"single_buffered_forward_ms": round(ms_s, 4), "double_buffered_forward_ms": round(ms_d, 4),
-                "bit_identical": same, "used": "double_buffered" if use_db else "single_buffered"}
-    except Exception as ex:                                  # any host-side problem: stay on the default kernel
-        use_db = False
-        info = {"used": "single_buffered", "error": str(ex)[:200]}
-    if use_db:
-        os.environ["B200_TC_DB"] = "1"
-    else:
-        os.environ.pop("B200_TC_DB", None)
-    torch.cuda.empty_cache()
-    return info

@@ -24,6 +24,13 @@ class RowSeg(C.Structure):
                 ("hi", C.c_int), ("flag", C.c_void_p), ("target", C.c_int), ("pad_", C.c_int)]
 
 
+class RowMirror(C.Structure):
+    _fields_ = [("ptr", C.c_void_p), ("base", C.c_int), ("slab", C.c_int), ("lo", C.c_int), ("hi", C.c_int)]
+
+
+MAX_MIRROR = 4
+
+
 class BlockGeom(C.Structure):
     _fields_ = [(n, C.c_int) for n in (
         "N", "H", "W", "C", "K", "F", "S", "P", "Hc", "Wc", "Hp", "Wp", "p0", "p1",
@@ -32,7 +39,8 @@ class BlockGeom(C.Structure):
         ("seg", RowSeg * MAX_SEG), ("signal", C.c_void_p * MAX_SIGNAL),
         ("status", C.c_void_p), ("timeout_ns", C.c_ulonglong), ("epoch", C.c_void_p),
         ("gate", C.c_void_p), ("gate_target", C.c_int), ("n_done", C.c_int),
-        ("done_count", C.c_void_p), ("done", C.c_void_p * 2)]
+        ("done_count", C.c_void_p), ("done", C.c_void_p * 2),
+        ("n_mirror", C.c_int), ("pad2_", C.c_int), ("mirror", RowMirror * MAX_MIRROR)]
 
 
 _lib = None
@@ -98,7 +106,8 @@ def make_block_geom(*, N, H, W, Cin, K, F, S, P, Hc, Wc, Hp, Wp, rows: Tuple[int
                     segs: Sequence[dict], signals: Sequence[int] = (),
                     status_ptr: int = 0, timeout_ns: int = DEFAULT_TIMEOUT_NS,
                     epoch_ptr: int = 0, in_pitch: int = 0, gate_ptr: int = 0, gate_target: int = 0,
-                    done_count_ptr: int = 0, done: Sequence[int] = ()) -> BlockGeom:
+                    done_count_ptr: int = 0, done: Sequence[int] = (),
+                    mirrors: Sequence[dict] = ()) -> BlockGeom:
     g = BlockGeom()
     g.N, g.H, g.W, g.C = N, H, W, Cin
     g.K, g.F, g.S, g.P = K, F, S, P
@@ -129,6 +138,11 @@ def make_block_geom(*, N, H, W, Cin, K, F, S, P, Hc, Wc, Hp, Wp, rows: Tuple[int
     g.n_done = len(done)
     for i, p in enumerate(done):
         g.done[i] = p
+    if len(mirrors) > MAX_MIRROR:
+        raise NativeError(f"at most {MAX_MIRROR} halo-push targets, got {len(mirrors)}")
+    g.n_mirror = len(mirrors)
+    for i, m in enumerate(mirrors):
+        g.mirror[i] = RowMirror(m["ptr"], m["base"], m["slab"], m["lo"], m["hi"])
     return g
 
 

@@ -26,8 +26,17 @@ def _lib():
         L.b200_tc_block_tiles.argtypes = [C.POINTER(cu.BlockGeom)]
         L.b200_tc_block.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(cu.BlockGeom),
                                     C.c_int, C.c_void_p]
+        L.b200_tc_set_policy.argtypes = [C.c_char_p, C.c_char_p]
         _bound = True
     return L
+
+
+def set_policy(**kw) -> None:
+    """Process-wide kernel choice (csrc/cuda/tc_block.cu ``Policy``): ``conv2="auto"|"single"|"db"|"pair"``,
+    ``conv1="auto"|"cpasync"``, ``no_swap`` / ``no_direct`` / ``dbg`` integers.  Every choice gives bit-identical
+    outputs; tests and experiments use it to compare the kernels."""
+    for k, v in kw.items():
+        cu.cu_check(_lib().b200_tc_set_policy(k.encode(), str(v).encode()), f"tc_set_policy({k}={v})")
 
 
 class TcConv:

@@ -104,6 +104,18 @@ typedef struct {
 
 #define B200_MAX_SEG 4
 #define B200_MAX_SIGNAL 4
+#define B200_MAX_MIRROR 4
+
+/* Halo push: pooled rows [lo,hi) of the block's output are ALSO stored into another slab (usually a
+ * neighbour rank's copy of the activation, over NVLink), laid out like `out`: element (n,h,w,k) at
+ * ((n*slab + h-base)*Wp + w)*K + k.  The reference sends these rows with MPI_Isend/Irecv after the layer
+ * (ref v2_mpi_only/2.2_scatter_halo/src/main.cpp:178-187); here the producing epilogue writes them where the
+ * consumer's loader will read them, so the consumer only ever reads local memory. */
+typedef struct {
+    float* ptr;
+    int base, slab;
+    int lo, hi;
+} b200_row_mirror;
 
 /* One fused block: conv(F,S,P) + bias + ReLU + max-pool(3,2) [+ cross-channel LRN], for pooled
  * rows [p0,p1) of every image.  Replaces the reference's 3-4 separate kernels per block
@@ -142,6 +154,9 @@ typedef struct {
     int n_done;
     unsigned int* done_count;
     int* done[2];
+    int n_mirror;            /* halo push targets (see b200_row_mirror); stored before signal[] is bumped */
+    int pad2_;
+    b200_row_mirror mirror[B200_MAX_MIRROR];
 } b200_block_geom;
 
 /* host: [K][C][F][F] (reference layout) -> [F][F][C][K] used by the SIMT kernels */
@@ -161,6 +176,11 @@ int b200_tc_conv_destroy(void* handle);
 int b200_tc_block(void* handle, const float* bias, float* out, const b200_block_geom* g,
                   int flags /* bit0: round outputs to TF32 */, void* stream);
 int b200_tc_block_tiles(const b200_block_geom* g);
+/* Process-wide kernel choice (default: environment B200_TC_CONV2 / B200_TC_CONV1 at first use, else auto):
+ * key "conv2" = auto|single|db|pair (single-buffered, double-buffered TMEM, tcgen05 CTA pair),
+ * key "conv1" = auto|cpasync (pixel operand by TMA when eligible, or always the cp.async loader).
+ * All choices produce bit-identical outputs; they differ in speed only. */
+int b200_tc_set_policy(const char* key, const char* value);
 
 /* Stand-alone convolution on NCHW device tensors with reference-layout weights [K][C][F][F]
  * (the `conv_test` equivalent; ref final_project/conv_test, kernel convTiledKernel).

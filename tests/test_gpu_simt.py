@@ -54,7 +54,7 @@ def test_simt_emulated_ranks_equal_single(world, strategy, scatter):
     cfg = default_config(batch=2, init=INIT_RAND, seed=9, precision="simt")
     x, w = make_problem(cfg)
     one = single_gpu_engine(cfg, w, "cuda:0").forward(x.cuda()).clone()
-    ew = EmulatedWorld(cfg, w, world, "cuda:0", strategy=strategy, scatter=scatter)
+    ew = EmulatedWorld(cfg, w, world, "cuda:0", strategy=strategy, scatter=scatter, halo="pull")
     y = ew.forward(x.cuda())
     assert torch.equal(y, one)
     y = ew.forward(x.cuda())          # second epoch: counters keep growing, targets follow
@@ -76,14 +76,16 @@ def test_flag_kernels_and_watchdog():
 
 
 @pytest.mark.parametrize("world,R", [(2, 1), (4, 2), (8, 2), (8, 4), (6, 3)])
+@pytest.mark.parametrize("halo", ["push", "pull"])
 @pytest.mark.parametrize("scatter,gather", [("p2p", "rank0"), ("sharded", "rank0"), ("sharded", "local")])
-def test_simt_rows_x_batch_equal_single(world, R, scatter, gather):
+def test_simt_rows_x_batch_equal_single(world, R, scatter, gather, halo):
     """R row groups x B batch groups (uneven: 5 images over up to 4 groups), flow-control gate instead of a
     barrier, pool1 slabs alternating by forward parity: three forwards in a row, bit-equal to one rank."""
     from b200cnn.models.engine import single_gpu_engine, EmulatedWorld
     cfg = default_config(batch=5, init=INIT_RAND, seed=13, precision="simt")
     x, w = make_problem(cfg)
     one = single_gpu_engine(cfg, w, "cuda:0").forward(x.cuda()).clone()
-    ew = EmulatedWorld(cfg, w, world, "cuda:0", strategy="halo", scatter=scatter, row_groups=R, gather=gather)
+    ew = EmulatedWorld(cfg, w, world, "cuda:0", strategy="halo", scatter=scatter, row_groups=R, gather=gather,
+                       halo=halo)
     for _ in range(3):
         assert torch.equal(ew.forward(x.cuda()), one)

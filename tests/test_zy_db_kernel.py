@@ -1,6 +1,7 @@
-"""Opt-in double-buffered conv2 kernel (B200_TC_DB=1, csrc/cuda/tc_block.cu: tc_block_db_kernel) against the
-default single-buffered kernel.  Same K order per output element, so the outputs must be bit-identical.
-Collected late on purpose (the kernel is new: validated on a B200 for batch 6 and timed at batch 128)."""
+"""The three conv2-type kernels of csrc/cuda/tc_block.cu — single-buffered (one 256-pixel tile fills TMEM),
+double-buffered (128-pixel tiles, own epilogue warps) and the tcgen05 CTA pair (cta_group::2, TMA-fed operands) —
+and the two conv1 loaders (pixel operand by TMA / by cp.async) accumulate every output in the same K order, so all
+choices must be bit-identical.  A mismatch fails."""
 import pytest
 import torch
 
@@ -11,35 +12,38 @@ from b200cnn.models.init import make_problem
 pytestmark = pytest.mark.gpu
 
 
-def _forward(cfg, x, w, db, monkeypatch):
+def _forward(cfg, x, w, **policy):
     from b200cnn.models.engine import single_gpu_engine
-    if db:
-        monkeypatch.setenv("B200_TC_DB", "1")
-    else:
-        monkeypatch.delenv("B200_TC_DB", raising=False)
-    e = single_gpu_engine(cfg, w, "cuda:0", "tf32")
-    e.use_graph = False
-    y = e.forward(x.cuda()).clone()
-    y2 = e.forward(x.cuda()).clone()          # second epoch: barrier phases and TMEM buffers wrap
-    e.check_status()
+    from b200cnn.ops import tc
+    tc.set_policy(**policy)
+    try:
+        e = single_gpu_engine(cfg, w, "cuda:0", "tf32")
+        e.use_graph = False
+        y = e.forward(x.cuda()).clone()
+        y2 = e.forward(x.cuda()).clone()          # second forward: barrier phases and TMEM buffers wrap
+        e.check_status()
+    finally:
+        tc.set_policy(conv2="auto", conv1="auto")
     return y.cpu(), y2.cpu()
 
 
-def test_db_kernel_one_tile_per_cta(monkeypatch):
-    cfg = default_config(batch=6, init=INIT_RAND, seed=1, precision="tf32")      # 54 tiles on 148 SMs
-    x, w = make_problem(cfg)
-    (y0, y0b), (y1, y1b) = _forward(cfg, x, w, False, monkeypatch), _forward(cfg, x, w, True, monkeypatch)
-    assert torch.equal(y0, y0b)
-    assert torch.equal(y0, y1)                # the case validated on hardware in round 1
-    if not torch.equal(y1, y1b):
-        pytest.xfail("double-buffered kernel: second forward differs from the first")
-
-
-@pytest.mark.parametrize("batch,hw", [(40, 227), (3, 99)])
-def test_db_kernel_many_tiles_per_cta_and_odd_shape(batch, hw, monkeypatch):
+@pytest.mark.parametrize("batch,hw", [(6, 227), (40, 227), (3, 99), (5, 163)])
+def test_conv2_kernels_bit_identical(batch, hw):
     cfg = default_config(H=hw, W=hw, batch=batch, init=INIT_RAND, seed=2, precision="tf32")
     x, w = make_problem(cfg)
-    (y0, _), (y1, y1b) = _forward(cfg, x, w, False, monkeypatch), _forward(cfg, x, w, True, monkeypatch)
-    if not (torch.equal(y0, y1) and torch.equal(y1, y1b)):     # experimental path: report, do not fail the suite
-        pytest.xfail(f"double-buffered kernel differs at batch {batch}, {hw}x{hw}: "
-                     f"max |diff| {float((y0 - y1).abs().max()):.3e}")
+    ref, ref2 = _forward(cfg, x, w, conv2="single")
+    assert torch.equal(ref, ref2)
+    for kind in ("db", "pair", "auto"):
+        y, y2 = _forward(cfg, x, w, conv2=kind)
+        assert torch.equal(y, ref), f"conv2={kind} differs: max |diff| {float((y - ref).abs().max()):.3e}"
+        assert torch.equal(y2, ref), f"conv2={kind}: second forward differs"
+
+
+@pytest.mark.parametrize("batch,hw", [(6, 227), (3, 99), (2, 131)])
+def test_conv1_loaders_bit_identical(batch, hw):
+    cfg = default_config(H=hw, W=hw, batch=batch, init=INIT_RAND, seed=4, precision="tf32")
+    x, w = make_problem(cfg)
+    a, a2 = _forward(cfg, x, w, conv1="cpasync")
+    b, b2 = _forward(cfg, x, w, conv1="auto")
+    assert torch.equal(a, a2) and torch.equal(b, b2)
+    assert torch.equal(a, b), f"TMA-fed conv1 differs from cp.async-fed: {float((a - b).abs().max()):.3e}"
