@@ -268,7 +268,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_constant_
 namespace {
 
 struct TcGemm {
-    int N, K, device;
+    int N, K, device, sms;
     float* d_w;
     CUtensorMap tmap128, tmap256;                      // TMA boxes of 128 / 256 weight rows
 };
@@ -298,7 +298,10 @@ inline float round_tf32(float x) {
 }
 
 // N tile: 256 when the layer is wider than one 128 tile (B200_GEMM_BN128=1 forces the 128 kernel)
-inline int pick_bn(int N) { return (N > 128 && !getenv("B200_GEMM_BN128")) ? 256 : 128; }
+inline int pick_bn(int N) {
+    static const bool bn128 = getenv("B200_GEMM_BN128") != nullptr;     // read once, not on the launch path
+    return (N > 128 && !bn128) ? 256 : 128;
+}
 
 template <bool kConv, int kBN>
 int launch_one(const TcGemm* t, const GemmParams& p, unsigned grid, cudaStream_t stream) {
@@ -322,8 +325,7 @@ int launch_gemm(const TcGemm* t, GemmParams& p, bool conv, int ksplit, long long
     p.ksplit = (p.nkb + p.kb_per - 1) / p.kb_per;      // every split owns at least one k-block
     p.split_stride = p.ksplit > 1 ? split_stride : 0;
     p.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(bn >> 3) << 17) | ((128u >> 4) << 24);
-    static int sms = 0;
-    if (!sms) B200_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, t->device));
+    const int sms = t->sms;
     const long long total = (long long)p.tiles_m * p.tiles_n * p.ksplit;
     const unsigned grid = (unsigned)(total < sms ? total : sms);
     cudaStream_t st = (cudaStream_t)stream;
@@ -342,6 +344,7 @@ extern "C" int b200_tc_gemm_create(const float* w_nk, int N, int K, void** handl
     TcGemm* t = new TcGemm();
     t->N = N; t->K = K;
     B200_CUDA_TRY(cudaGetDevice(&t->device));
+    B200_CUDA_TRY(cudaDeviceGetAttribute(&t->sms, cudaDevAttrMultiProcessorCount, t->device));
     const int Npad = ((N + 255) / 256) * 256;                 // whole TMA boxes: rows >= N are zeros
     std::vector<float> w((size_t)Npad * K, 0.f);
     for (size_t i = 0; i < (size_t)N * K; ++i) w[i] = round_tf32(w_nk[i]);
@@ -382,6 +385,14 @@ extern "C" int b200_tc_gemm_splitk(void* handle, const float* A, int lda, int M,
     if (!t || !A || !C || M < 0 || lda < t->K || ldc < t->N || (lda & 3)) return B200_ERR_ARG;
     if ((flags & 8) && !bias) return B200_ERR_ARG;
     if (ksplit > 1 && (flags != 0 || split_stride < (long long)M * ldc)) return B200_ERR_ARG;
+    if (ksplit > 1) {       // the caller sizes its workspace and its reduce by ksplit: never run another count silently
+        const int nkb = t->K / kBK, kb_per = (nkb + ksplit - 1) / ksplit;
+        if (ksplit > nkb || (nkb + kb_per - 1) / kb_per != ksplit) {
+            set_error("tc_gemm_splitk: %d k-blocks cannot be cut into exactly %d splits of %d (that gives %d); "
+                      "ask for the effective count", nkb, ksplit, kb_per, (nkb + kb_per - 1) / kb_per);
+            return B200_ERR_ARG;
+        }
+    }
     if (M == 0) return B200_OK;
     GemmParams p;
     memset(&p, 0, sizeof(p));

@@ -47,7 +47,17 @@ def plan_splitk(M: int, N: int, bn: int, nkb: int, sms: int) -> int:
     tiles = ((M + 127) // 128) * ((N + bn - 1) // bn)
     if tiles * 2 > sms or nkb < 16:
         return 1
-    return max(1, min(sms // tiles, nkb // 8))
+    return effective_splitk(nkb, max(1, min(sms // tiles, nkb // 8)))
+
+
+def effective_splitk(nkb: int, ks: int) -> int:
+    """The split count the kernel really runs for a request of ``ks``: every split covers ceil(nkb / ks) k-blocks,
+    so fewer splits may be enough (81 k-blocks in 10 splits of 9 are 9 splits).  The workspace and the reduce must
+    use THIS number — a reduce over the requested count would add a slab nobody wrote (and the C entry point
+    refuses a count it would have to change)."""
+    ks = max(1, min(int(ks), int(nkb)))
+    kb_per = -(-nkb // ks)
+    return -(-nkb // kb_per)
 
 
 class TcLinear:
@@ -78,7 +88,7 @@ class TcLinear:
             flags: int = 0) -> None:
         if bias is not None:
             flags |= BIAS
-        ks = 1 if (flags & ACCUMULATE) else self.splitk_for(M)
+        ks = 1 if (flags & ACCUMULATE) else effective_splitk(self.nkb, self.splitk_for(M))
         if ks > 1:                       # partial sums into a workspace, then a deterministic reduce + epilogue
             need = ks * M * self.N
             if self._ws is None or self._ws.numel() < need:

@@ -99,7 +99,7 @@ def test_full_alexnet_implicit_conv_equals_im2col(monkeypatch):
     assert torch.equal(p0, p1)
 
 
-@pytest.mark.parametrize("M,N,K", [(256, 1000, 4096), (64, 512, 9216), (130, 4096, 1024)])
+@pytest.mark.parametrize("M,N,K", [(256, 1000, 4096), (64, 512, 9216), (130, 4096, 1024), (128, 256, 2592)])
 def test_tc_gemm_splitk_matches_plain_and_is_deterministic(M, N, K, monkeypatch):
     """Split-K (partials + fixed-order reduce) vs the unsplit kernel and vs fp32 matmul; two runs bit-equal."""
     from b200cnn.ops import ext
@@ -119,3 +119,23 @@ def test_tc_gemm_splitk_matches_plain_and_is_deterministic(M, N, K, monkeypatch)
     o0 = lin(a.cuda(), b.cuda(), relu=True).cpu()
     assert _rel(o1, ref) < 4e-3 and _rel(o0, ref) < 4e-3
     assert _rel(o1, o0) < 1e-4                          # fp32 summation order differs, nothing else
+
+
+def test_tc_gemm_splitk_refuses_a_count_it_would_change():
+    """K = 2592 is 81 k-blocks: 10 splits would run as 9; the workspace/reduce contract is by count, so the
+    C entry point refuses instead of leaving a slab unwritten (the Python wrapper asks for the effective count)."""
+    import ctypes as C
+    from b200cnn.ops import ext, cuda as cu
+    from b200cnn.ops._ctypes import fptr
+    w = torch.randn((256, 2592)) * 0.02
+    lin = ext.TcLinear(w, "cuda:0")
+    a = torch.randn((128, 2592), device="cuda")
+    ws = torch.empty(10 * 128 * 256, device="cuda")
+    rc = ext._lib().b200_tc_gemm_splitk(lin._h, fptr(a), 2592, 128, None, fptr(ws), 256, 0, 10, 128 * 256,
+                                        cu.current_stream_ptr())
+    assert rc == -1
+    assert ext.effective_splitk(lin.nkb, 10) == 9
+    rc = ext._lib().b200_tc_gemm_splitk(lin._h, fptr(a), 2592, 128, None, fptr(ws), 256, 0, 9, 128 * 256,
+                                        cu.current_stream_ptr())
+    assert rc == 0
+    torch.cuda.synchronize()

@@ -101,7 +101,14 @@ def test_decomposed_more_ranks_than_rows():
 
 def test_splitk_and_batch_shard_plans():
     """Host-side plans of the full-network extension (pure arithmetic, no GPU)."""
-    from b200cnn.ops.ext import plan_splitk
+    from b200cnn.ops.ext import plan_splitk, effective_splitk
+    # 81 k-blocks (K = 2592) asked in 10 splits run as 9 splits of 9: workspace and reduce must use 9
+    assert effective_splitk(81, 10) == 9 and effective_splitk(81, 9) == 9 and effective_splitk(8, 16) == 8
+    for nkb in range(1, 200):
+        for ks in range(1, 40):
+            e = effective_splitk(nkb, ks)
+            assert effective_splitk(nkb, e) == e and e <= max(1, min(ks, nkb))
+    assert plan_splitk(128, 256, 256, 81, 148) == effective_splitk(81, plan_splitk(128, 256, 256, 81, 148))
     from b200cnn.runners.full import batch_shard
     # FC6 at batch 256 on 148 SMs: 2 x 16 tiles of 128x256 -> 4 splits of 72 k-blocks
     assert plan_splitk(256, 4096, 256, 288, 148) == 4
