@@ -150,6 +150,16 @@ extern "C" int b200_conv_nchw(const float* in_nchw, const float* w_kcff, const f
 // time the entry point is called on a given device, with that device current, and cached per
 // device.  That first call therefore does a little extra runtime work; make it before any stream
 // capture you intend to do around later calls.
+//
+// When the 8 MiB come into being.  The CUDA runtime loads a module's code and its __device__ data
+// on a GPU lazily: on the first kernel launch or symbol lookup from that module on that GPU.  So the
+// array is NOT allocated by this entry point, but the first call into this file on a device may be
+// the moment the driver sets the module (array included) up there.  A host whose pool is about to
+// take all remaining memory must therefore make ONE warm-up call per device (any call into this
+// file: this entry point or b200_conv_nchw) BEFORE its pool reserves the GPU; after that, calls here
+// neither allocate nor free anything (tests/test_zz_no_alloc.py checks the free-memory figure after
+// such a warm-up).  The cached address does not survive cudaDeviceReset(): a process that resets a
+// device must not call this entry point on it again.
 #define B200_CONV_NCHW_STATIC_SCRATCH_BYTES (8u << 20)
 
 static __device__ __align__(256) unsigned char g_conv_nchw_static_scratch[B200_CONV_NCHW_STATIC_SCRATCH_BYTES];

@@ -9,6 +9,8 @@ launchers under ``final_project/`` still expose ``make GPU_ARCH_FLAGS=...``.
 """
 from __future__ import annotations
 
+import contextlib
+import fcntl
 import glob
 import os
 import shutil
@@ -50,15 +52,47 @@ def _run(cmd, what):
     return p.stdout
 
 
+@contextlib.contextmanager
+def _build_lock():
+    """One builder at a time per checkout: every rank of a torchrun / bin/mpirun job imports this module, and
+    without the lock they would all run nvcc into the same lib/obj/*.o and link half-written objects.  The
+    staleness test is repeated under the lock, so the ranks that waited find a fresh library and build nothing."""
+    os.makedirs(LIB_DIR, exist_ok=True)
+    with open(os.path.join(LIB_DIR, ".build.lock"), "w") as f:
+        fcntl.flock(f, fcntl.LOCK_EX)
+        try:
+            yield
+        finally:
+            fcntl.flock(f, fcntl.LOCK_UN)
+
+
+CPU_WARN = ["-Wall", "-Wextra", "-Werror"]          # the CPU library builds warning-free; keep it that way
+
+
 def build_cpu(force: bool = False) -> str:
     srcs = sorted(glob.glob(os.path.join(REPO_ROOT, "csrc", "cpu", "*.cpp")))
-    if force or _stale(CPU_LIB, srcs):
-        os.makedirs(LIB_DIR, exist_ok=True)
-        tmp = CPU_LIB + f".tmp{os.getpid()}"
-        _run(["g++", "-std=c++17", "-O3", "-ffp-contract=off", "-fopenmp", "-fPIC", "-shared",
-              "-Wall", "-Wextra", "-I", INC_DIR, "-o", tmp] + srcs, "CPU library")
-        os.replace(tmp, CPU_LIB)
+    if not (force or _stale(CPU_LIB, srcs)):
+        return CPU_LIB
+    with _build_lock():
+        if force or _stale(CPU_LIB, srcs):
+            tmp = CPU_LIB + f".tmp{os.getpid()}"
+            _run(["g++", "-std=c++17", "-O3", "-ffp-contract=off", "-fopenmp", "-fPIC", "-shared"] + CPU_WARN +
+                 ["-I", INC_DIR, "-o", tmp] + srcs, "CPU library")
+            os.replace(tmp, CPU_LIB)
     return CPU_LIB
+
+
+def build_cpu_sanitized(out_dir: str) -> str:
+    """``libb200cnn_cpu.so`` with AddressSanitizer + UndefinedBehaviourSanitizer (scripts/sanitize_host.sh loads it
+    into a test run with LD_PRELOAD=libasan): the host-side counterpart of compute-sanitizer, which is closed on
+    the GPU pool.  The reference ships a .clang-tidy it never runs (ref final_project/v4_mpi_cuda/.clang-tidy:4)."""
+    srcs = sorted(glob.glob(os.path.join(REPO_ROOT, "csrc", "cpu", "*.cpp")))
+    os.makedirs(out_dir, exist_ok=True)
+    lib = os.path.join(out_dir, "libb200cnn_cpu.so")
+    _run(["g++", "-std=c++17", "-O1", "-g", "-fno-omit-frame-pointer", "-ffp-contract=off", "-fopenmp", "-fPIC",
+          "-shared", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined"] + CPU_WARN +
+         ["-I", INC_DIR, "-o", lib] + srcs, "sanitized CPU library")
+    return lib
 
 
 def nvcc_path():
@@ -72,8 +106,15 @@ def build_cuda(force: bool = False, verbose: bool = False) -> str:
     """nvcc cross-compiles sm_100a without a GPU.  One translation unit per .cu, linked into
     one shared object; -lineinfo keeps ncu's source page usable."""
     srcs = cuda_sources()
-    nvcc = nvcc_path()
     if not (force or _stale(CUDA_LIB, srcs)):
+        return CUDA_LIB
+    with _build_lock():
+        return _build_cuda_locked(srcs, force, verbose)
+
+
+def _build_cuda_locked(srcs, force: bool, verbose: bool) -> str:
+    nvcc = nvcc_path()
+    if not (force or _stale(CUDA_LIB, srcs)):         # another rank built it while we waited for the lock
         return CUDA_LIB
     if nvcc is None:
         if os.path.exists(CUDA_LIB):

@@ -114,6 +114,14 @@ def init(device: Optional[str] = None, timeout_s: int = 600) -> DistContext:
     use_cuda = (device != "cpu") and torch.cuda.is_available()
     if use_cuda:
         ndev = torch.cuda.device_count()
+        # One GPU per rank: the device-side waits of the multi-GPU forward spin on peers' flags and would
+        # deadlock (until the watchdog) if two ranks shared a device.  More ranks than GPUs is the job of the
+        # single-device emulation (runners/v4.py::_oversubscribed), never of a silent ``local % ndev``.
+        local_world = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("OMPI_COMM_WORLD_LOCAL_SIZE", world)))
+        if world > 1 and local_world > ndev and os.environ.get("B200_ALLOW_SHARED_GPU") != "1":
+            raise RuntimeError(f"[Rank {rank}] {local_world} ranks on this node but only {ndev} visible GPU(s): ranks "
+                               f"that wait on each other's device flags must not share a GPU (run the emulated path, "
+                               f"e.g. runners.v4 does it automatically, or set CUDA_VISIBLE_DEVICES / -np accordingly)")
         dev = torch.device("cuda", local % max(ndev, 1))
         torch.cuda.set_device(dev)
     else:

@@ -198,7 +198,10 @@ int b200_conv_nchw(const float* in_nchw, const float* w_kcff, const float* bias,
  * array built into the library (held by every GPU that loads it).  Problems needing more scratch
  * than b200_conv_nchw_noalloc_max_scratch_bytes() are refused with B200_ERR_RANGE.  All calls on one
  * GPU share that array: calls that overlap on the GPU race, so order them.  The first call on each
- * device resolves the array's address; issue it before any stream capture. */
+ * device resolves the array's address; issue it before any stream capture.  The array is part of the
+ * library's device image, which the CUDA runtime sets up on a GPU at the first call into the library on
+ * that GPU: make one warm-up call per device BEFORE a memory pool takes the rest of the GPU; from then on
+ * the entry point neither allocates nor frees.  Not usable on a device after cudaDeviceReset(). */
 long long b200_conv_nchw_noalloc_max_scratch_bytes(void);
 int b200_conv_nchw_noalloc(const float* in_nchw, const float* w_kcff, const float* bias, float* out_nchw,
                            int N, int C, int H, int W, int K, int F, int S, int P, void* stream);

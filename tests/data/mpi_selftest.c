@@ -54,6 +54,7 @@ int main(int argc, char** argv) {
     if (rank == 0) { for (int r = 1; r < size; ++r) { int o; MPI_Recv(&o, 1, MPI_INT, r, 99, MPI_COMM_WORLD, MPI_STATUS_IGNORE); allok &= o; }
                      printf("mpishim selftest np=%d: %s\n", size, allok ? "PASSED" : "FAILED"); }
     else MPI_Send(&ok, 1, MPI_INT, 0, 99, MPI_COMM_WORLD);
+    free(cnt); free(disp); free(full); free(mine); free(nums);
     MPI_Finalize();
     return allok ? 0 : 1;
 }

@@ -65,6 +65,8 @@ def test_noalloc_matches_allocating_entry_point_twice_in_a_row():
         assert _call(L.b200_conv_nchw, x, w, b, want, S, P) == 0, L.b200_last_error()
         torch.cuda.synchronize()
         if i == 1:
+            # by now the library's device image (the 8 MiB array included) is set up on this GPU: case 0 was the
+            # warm-up call the header asks for, so from here on free memory must not move
             free_before = torch.cuda.mem_get_info()[0]
         assert _call(L.b200_conv_nchw_noalloc, x, w, b, got, S, P) == 0, L.b200_last_error()
         torch.cuda.synchronize()
