@@ -35,15 +35,18 @@ def _render(name: str, hw: str) -> str:
         return f.read().replace("{{HW}}", hw)
 
 
-def scaffold(n: int, force: bool = False) -> int:
+def scaffold(n: int, force: bool = False, native: bool = False) -> int:
+    """``native``: the compiled C skeleton (templates/template.c.template + Makefile.native.template, MPI subset of
+    baseline/mpishim) instead of the Python one — the counterpart of ref templates/template.c.template."""
     d = hw_dir(n)
     hw = f"hw{n}"
     if os.path.exists(d) and not force:
         print(f"{d} exists (use --force to overwrite)")
         return 1
     os.makedirs(os.path.join(d, "src"), exist_ok=True)
-    files = {"Makefile": _render("Makefile.template", hw),
-             "src/template.py": _render("template.py.template", hw),
+    files = {"Makefile": _render("Makefile.native.template" if native else "Makefile.template", hw),
+             ("src/template.c" if native else "src/template.py"):
+                 _render("template.c.template" if native else "template.py.template", hw),
              "summary.md": f"# {hw.upper()} summary\n\n- approach:\n- results:\n- issues:\n"}
     if n >= 4:
         files["src/template.cu"] = _render("template.cu.template", hw)
@@ -107,6 +110,8 @@ def main(argv=None) -> int:
         a.add_argument("n", type=int)
         if c == "scaffold":
             a.add_argument("--force", action="store_true")
+            a.add_argument("--native", action="store_true",
+                           help="compiled C skeleton (MPI subset of baseline/mpishim) instead of the Python one")
         if c in ("test", "run"):
             a.add_argument("--sizes", default="")
             a.add_argument("--counts", default="")
@@ -117,7 +122,7 @@ def main(argv=None) -> int:
     ns = ap.parse_args(argv)
     ints = lambda s: [int(x) for x in s.split(",") if x]
     if ns.cmd == "scaffold":
-        return scaffold(ns.n, ns.force)
+        return scaffold(ns.n, ns.force, ns.native)
     if ns.cmd == "test":
         return test(ns.n, ints(ns.sizes), ints(ns.counts), ns.timeout)
     if ns.cmd == "package":

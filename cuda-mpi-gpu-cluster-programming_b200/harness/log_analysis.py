@@ -106,6 +106,7 @@ class Warehouse:
         c.execute("CREATE TABLE IF NOT EXISTS run_logs(relpath TEXT, ts TEXT, version TEXT, np INT, total_time_s REAL)")
         c.execute("CREATE TABLE IF NOT EXISTS source_stats(relpath TEXT PRIMARY KEY, loc INT, func_cnt INT, include_cnt INT, cuda_kernel_cnt INT)")
         c.executescript("""
+            DROP VIEW IF EXISTS efficiency; DROP VIEW IF EXISTS speedup;
             DROP VIEW IF EXISTS perf_runs; DROP VIEW IF EXISTS best_runs;
             CREATE VIEW perf_runs AS
               SELECT ts, version, np, total_time_s FROM summary_runs WHERE total_time_s IS NOT NULL
@@ -113,6 +114,14 @@ class Warehouse:
               SELECT ts, version, np, total_time_s FROM run_logs WHERE total_time_s IS NOT NULL;
             CREATE VIEW best_runs AS
               SELECT version, np, MIN(total_time_s) AS total_time_s FROM perf_runs GROUP BY version, np;
+            -- per-version strong scaling, as the reference's notebook defines it (ref analysis.md:222-240):
+            -- S = best time of the SAME version at np = 1 / best time at np;  E = S / np
+            CREATE VIEW speedup AS
+              SELECT b.version AS version, b.np AS np, base.t1 / b.total_time_s AS S
+              FROM best_runs b JOIN (SELECT version, MIN(total_time_s) AS t1 FROM best_runs WHERE np = 1 GROUP BY version) base
+                   ON base.version = b.version
+              WHERE b.total_time_s > 1e-9;
+            CREATE VIEW efficiency AS SELECT version, np, S / np AS E FROM speedup WHERE np > 0;
         """)
         c.commit()
 
@@ -277,6 +286,104 @@ def svg_bars(path: Path, labels, vals, title, ylabel, ymax=1.1):
     path.write_text("\n".join(el))
 
 
+def svg_grouped_bars(path: Path, groups, series, values, title, ylabel, notes=None):
+    """Bars of ``values[g][s]`` grouped by ``groups`` with one colour per ``series`` (the notebook's CV chart:
+    version on the x axis, np as hue, n as annotation; ref analysis.md:2305-2355)."""
+    colours = ["#1f77b4", "#ff7f0e", "#2ca02c", "#d62728", "#9467bd", "#8c564b"]
+    w, h = max(520, 90 + 34 * len(groups) * max(len(series), 1)), 360
+    vmax = max([v for g in groups for v in values[g].values() if v == v] + [1e-9]) * 1.15
+    el = _svg_axes(w, h, title, "", ylabel)
+    gw = (w - 80) / max(len(groups), 1)
+    bw = gw * 0.8 / max(len(series), 1)
+    for gi, g in enumerate(groups):
+        for si, sname in enumerate(series):
+            v = values[g].get(sname)
+            if v is None or v != v:
+                continue
+            x = 55 + gi * gw + si * bw
+            bh = (h - 100) * v / vmax
+            el.append(f'<rect x="{x:.1f}" y="{h-70-bh:.1f}" width="{bw*0.92:.1f}" height="{bh:.1f}" fill="{colours[si % 6]}"/>')
+            lab = f"{v:.2f}" + (f" (n={notes[g][sname]})" if notes and notes.get(g, {}).get(sname) else "")
+            el.append(f'<text x="{x+bw*0.46:.1f}" y="{h-74-bh:.1f}" text-anchor="middle" font-size="9">{lab}</text>')
+        el.append(f'<text x="{55+gi*gw+gw*0.4:.1f}" y="{h-52}" text-anchor="middle" font-size="10">{_label(str(g))}</text>')
+    for si, sname in enumerate(series):
+        el.append(f'<rect x="{60+si*70}" y="{h-30}" width="10" height="10" fill="{colours[si % 6]}"/>')
+        el.append(f'<text x="{74+si*70}" y="{h-21}" font-size="10">np={sname}</text>')
+    el.append("</svg>")
+    path.write_text("\n".join(el))
+
+
+def svg_radar(path: Path, axes, rows, title):
+    """Radar chart: ``rows`` = {name: [value per axis in 0..1]} (ref analysis.md:2357-2460: NP1 performance, max
+    speed-up, max efficiency and code volume per version, each min-max normalised over the versions)."""
+    import math
+    colours = ["#1f77b4", "#ff7f0e", "#2ca02c", "#d62728", "#9467bd", "#8c564b"]
+    w, h, cx, cy, R = 560, 460, 250, 240, 170
+    el = [f'<svg xmlns="http://www.w3.org/2000/svg" width="{w}" height="{h}" font-family="sans-serif" font-size="11">',
+          f'<rect width="{w}" height="{h}" fill="white"/>',
+          f'<text x="{w/2}" y="18" text-anchor="middle" font-size="14">{title}</text>']
+    k = len(axes)
+    pt = lambda i, r: (cx + R * r * math.sin(2 * math.pi * i / k), cy - R * r * math.cos(2 * math.pi * i / k))
+    for ring in (0.25, 0.5, 0.75, 1.0):
+        el.append('<polygon fill="none" stroke="#ccc" points="' + " ".join("%.1f,%.1f" % pt(i, ring) for i in range(k)) + '"/>')
+    for i, a in enumerate(axes):
+        x, y = pt(i, 1.0)
+        el.append(f'<line x1="{cx}" y1="{cy}" x2="{x:.1f}" y2="{y:.1f}" stroke="#bbb"/>')
+        lx, ly = pt(i, 1.13)
+        el.append(f'<text x="{lx:.1f}" y="{ly:.1f}" text-anchor="middle">{a}</text>')
+    for ri, (name, vals) in enumerate(rows.items()):
+        c = colours[ri % 6]
+        el.append(f'<polygon fill="{c}" fill-opacity="0.15" stroke="{c}" stroke-width="2" points="' +
+                  " ".join("%.1f,%.1f" % pt(i, max(0.0, min(1.0, v))) for i, v in enumerate(vals)) + '"/>')
+        el.append(f'<rect x="{w-140}" y="{40+ri*18}" width="10" height="10" fill="{c}"/>')
+        el.append(f'<text x="{w-125}" y="{49+ri*18}">{name}</text>')
+    el.append("</svg>")
+    path.write_text("\n".join(el))
+
+
+def svg_scatter(path: Path, pts, title, xlabel, ylabel):
+    """Labelled scatter (LOC vs best time per version; ref analysis.md 'LOC vs performance')."""
+    w, h = 520, 340
+    xmax = max([p[0] for p in pts] + [1]) * 1.1
+    ymax = max([p[1] for p in pts] + [1e-9]) * 1.15
+    el = _svg_axes(w, h, title, xlabel, ylabel)
+    for x, y, lab in pts:
+        px, py = 50 + (w - 65) * x / xmax, (h - 40) - (h - 70) * y / ymax
+        el.append(f'<circle cx="{px:.1f}" cy="{py:.1f}" r="4" fill="#d62728"/>')
+        el.append(f'<text x="{px+6:.1f}" y="{py-5:.1f}" font-size="10">{lab} ({x:g} LOC, {y:.3g} s)</text>')
+    el.append("</svg>")
+    path.write_text("\n".join(el))
+
+
+def radar_table(wh: "Warehouse") -> pd.DataFrame:
+    """Per canonical version: NP1 performance (1 / median time at np = 1), max speed-up and max efficiency over np
+    (median based, baseline V1 Serial), log10 of the lines of code; raw values and min-max normalised columns."""
+    import math
+    st = wh.run_stats(canonical=True)
+    if st.empty:
+        return pd.DataFrame()
+    try:
+        sp = wh.speedup("median", canonical=True)
+    except SystemExit:
+        sp = pd.DataFrame(columns=["version", "np", "S", "E"])
+    loc = loc_vs_perf(wh)
+    rows = []
+    for v in sorted(st.version.dropna().unique()):
+        one = st[(st.version == v) & (st.np == 1)]
+        s = sp[sp.version == v]
+        l = loc[loc.version == v]["loc"] if not loc.empty else []
+        rows.append(dict(version=v,
+                         np1_perf=1.0 / float(one.median_s.iloc[0]) if len(one) and one.median_s.iloc[0] > 0 else float("nan"),
+                         max_speedup=float(s.S.max()) if len(s) else float("nan"),
+                         max_efficiency=float(s.E.max()) if len(s) else float("nan"),
+                         log10_loc=math.log10(float(l.iloc[0])) if len(l) and l.iloc[0] and l.iloc[0] == l.iloc[0] else float("nan")))
+    d = pd.DataFrame(rows)
+    for c in ("np1_perf", "max_speedup", "max_efficiency", "log10_loc"):
+        lo, hi = d[c].min(), d[c].max()
+        d[c + "_norm"] = ((d[c] - lo) / (hi - lo)) if hi > lo else 0.5
+    return d
+
+
 def _label(v: str) -> str:
     return v.replace("V2 2.1-broadcast-all", "V2 Broadcast").replace("V2 2.2-scatter-halo", "V2 Scatter")
 
@@ -294,7 +401,7 @@ def main(argv=None) -> int:
     a = sub.add_parser("scorecard")
     sub.add_parser("locperf")
     a = sub.add_parser("legacy-graphs"); a.add_argument("csv"); a.add_argument("--outdir", default=str(PLOTS_DIR))
-    a = sub.add_parser("plot"); a.add_argument("plots", nargs="+", choices=["speedup", "efficiency"])
+    a = sub.add_parser("plot"); a.add_argument("plots", nargs="+", choices=["speedup", "efficiency", "cv", "radar", "locperf"])
     a.add_argument("--outdir", default=str(PLOTS_DIR))
     a = sub.add_parser("export"); a.add_argument("view"); a.add_argument("outfile")
     ns = ap.parse_args(argv)
@@ -348,8 +455,31 @@ def main(argv=None) -> int:
             svg_bars(out / "efficiency.svg", [f"{_label(v)} np={int(n)}" for v, n in zip(s.version, s.np)],
                      list(s.E), "Strong-scaling efficiency", "Efficiency E")
             print(f"plot -> {out}/efficiency.svg")
+        if "cv" in ns.plots:             # runtime variability: CV = sd / mean per (version, np), n annotated
+            st = wh.run_stats(canonical=True).dropna(subset=["cv"])
+            groups = sorted(st.version.unique())
+            series = sorted(int(n) for n in st.np.unique())
+            vals = {g: {int(r.np): float(r.cv) for r in st[st.version == g].itertuples()} for g in groups}
+            notes = {g: {int(r.np): int(r.n) for r in st[st.version == g].itertuples()} for g in groups}
+            svg_grouped_bars(out / "runtime_cv.svg", groups, series, vals, "Runtime CV (lower = more stable)",
+                             "CV = sd / mean", notes)
+            print(f"plot -> {out}/runtime_cv.svg")
+        if "radar" in ns.plots:
+            rt = radar_table(wh)
+            if not rt.empty:
+                cols = ["np1_perf_norm", "max_speedup_norm", "max_efficiency_norm", "log10_loc_norm"]
+                svg_radar(out / "radar.svg", ["NP1 perf", "max speed-up", "max efficiency", "code volume"],
+                          {r.version: [0.0 if v != v else float(v) for v in (getattr(r, c) for c in cols)]
+                           for r in rt.itertuples()}, "Versions compared (min-max normalised)")
+                print(f"plot -> {out}/radar.svg")
+        if "locperf" in ns.plots:
+            lp = loc_vs_perf(wh).dropna(subset=["loc", "best_s"])
+            if not lp.empty:
+                svg_scatter(out / "loc_vs_perf.svg", [(float(r.loc), float(r.best_s), r.version) for r in lp.itertuples()],
+                            "Code volume vs best time", "lines of code", "best time (s)")
+                print(f"plot -> {out}/loc_vs_perf.svg")
     elif ns.cmd == "export":
-        special = {"run_stats": wh.run_stats, "speedup": lambda: wh.speedup("best")}
+        special = {"run_stats": wh.run_stats, "speedup": lambda: wh.speedup("best"), "radar": lambda: radar_table(wh)}
         try:
             df = special[ns.view]() if ns.view in special else wh.df(f"SELECT * FROM {ns.view}")
         except Exception as e:

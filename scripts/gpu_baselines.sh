@@ -12,6 +12,9 @@ NG=$(nvidia-smi -L | wc -l)
 R=baseline/_ref/src/final_project
 echo "== ref V1 (CPU, 3 runs)"; for i in 1 2 3; do $R/v1_serial/template | grep "completed in"; done | tee $OUT/ref_v1.log
 echo "== ref V3 (5 runs)"; for i in 1 2 3 4 5; do $R/v3_cuda_only/template | head -1; done | tee $OUT/ref_v3.log
+echo "== reference forward functions in a warm loop (128 images after 3 warm-up calls; baseline/ref_loop)"
+make -C baseline/ref_loop > $OUT/ref_loop_build.log 2>&1 || tail -3 $OUT/ref_loop_build.log
+for v in v3 v4; do [ -x baseline/ref_loop/ref_loop_$v ] && baseline/ref_loop/ref_loop_$v 128 3; done | tee $OUT/ref_loop.log
 for np in 1 2 4 8; do
   [ $np -le $NG ] || continue
   echo "== ref V4 np=$np (one GPU per rank)"

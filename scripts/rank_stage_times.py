@@ -56,6 +56,8 @@ for world in [int(v) for v in os.environ.get("WORLDS", "1,2,4,8").split(",")]:
         if key in seen or not e.rp.active:
             continue
         seen.add(key)
+        if os.environ.get("NOSIG") == "1":          # experiment: block 1 without arrival signals / halo push
+            e.rp.serves = []
         g1 = e._geom_block1(e.rank)
         g2 = e._geom_block2(e.epoch & 1)
         t1 = timeit(lambda: e.stage_block1(0))

@@ -121,3 +121,18 @@ echo "CSV=$CSV_SUMMARY_FILE FLAGS=$DETECTED_GPU_ARCH_FLAGS"
     assert rows[1]["BuildMessage"] == "Dir not found" and rows[1]["OverallStatusSymbol"] == "✘"
     assert rows[2]["ExecutionTime_ms"] == "1.5" and rows[2]["OutputFirst5Values"] == "1 2 3"
     assert os.path.exists(os.path.join(os.path.dirname(csv_path), "run_v1_serial_np1.log"))
+
+
+def test_hw_native_skeleton_builds_and_passes_under_mpirun(monkeypatch, tmp_path):
+    """`scaffold --native` lays down a C skeleton that compiles to ./template and passes the HW test matrix
+    (counterpart of ref templates/template.c.template, which needs an MPI the image does not have)."""
+    import shutil
+    from b200cnn.harness import hw
+    d = hw.hw_dir(97)
+    shutil.rmtree(d, ignore_errors=True)
+    try:
+        assert hw.scaffold(97, native=True) == 0
+        assert os.path.exists(os.path.join(d, "src", "template.c"))
+        assert hw.test(97, sizes=[128, 256], counts=[1, 2, 4], timeout=60) == 0
+    finally:
+        shutil.rmtree(d, ignore_errors=True)

@@ -120,3 +120,27 @@ def test_scorecard_pools_canonical_names(tmp_path):
     sp = wh.speedup("median", canonical=True).set_index(["version", "np"])
     assert abs(sp.loc[("V2.2 ScatterHalo", 4), "S"] - 0.78 / 0.25) < 1e-9
     assert abs(sp.loc[("V4 MPI+CUDA", 2), "E"] - 0.78 / 0.1505 / 2) < 1e-9
+
+
+def test_sql_views_and_notebook_figures(tmp_path):
+    """The notebook's per-version `speedup` / `efficiency` SQL views (ref analysis.md:222-240) and its CV, radar
+    and LOC-vs-performance figures (ref analysis.md:2305-2460), generated as SVG from the warehouse."""
+    root = _make_tree(tmp_path)
+    db = tmp_path / "wh.sqlite"
+    wh = la.Warehouse(db)
+    wh.ingest(root)
+    sp = wh.df("SELECT * FROM speedup WHERE version = 'V4 MPI+CUDA' ORDER BY np")
+    assert list(sp.np) == [1, 4] and abs(sp.S.iloc[0] - 1.0) < 1e-12          # per-version baseline: S(np=1) = 1
+    assert abs(sp.S.iloc[1] - 1.8) < 1e-9                                     # 0.180 s / 0.100 s
+    ef = wh.df("SELECT E FROM efficiency WHERE version = 'V4 MPI+CUDA' AND np = 4")
+    assert abs(ef.E.iloc[0] - 0.45) < 1e-9
+    rt = la.radar_table(wh)
+    assert {"np1_perf_norm", "max_speedup_norm", "max_efficiency_norm", "log10_loc_norm"} <= set(rt.columns)
+    out = tmp_path / "plots"
+    rc = la.main(["--db", str(db), "plot", "cv", "radar", "locperf", "--outdir", str(out)])
+    assert rc == 0
+    for f in ("runtime_cv.svg", "radar.svg"):
+        txt = (out / f).read_text()
+        assert txt.startswith("<svg") and txt.rstrip().endswith("</svg>")
+    assert "V1 Serial" in (out / "radar.svg").read_text()
+    assert "n=2" in (out / "runtime_cv.svg").read_text()                       # V1 Serial np=1 has two runs
