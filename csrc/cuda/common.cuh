@@ -56,6 +56,20 @@ __device__ __forceinline__ bool wait_flag_ge(const int* flag, int target, int* s
         __nanosleep(64);
     }
 }
+// Arrival signals of one finished tile that produced pooled rows [r0, r1): called by ONE thread after a barrier
+// that follows the tile's last store (local and pushed).  red.release.sys orders those stores (made visible to
+// this thread by the barrier) before the bump at system scope; no separate fence is needed.
+__device__ __forceinline__ bool tile_signals(const b200_block_geom& g, int r0, int r1) {
+    for (int i = 0; i < g.n_signal; ++i)
+        if (g.signal_hi[i] <= g.signal_lo[i] || (r0 < g.signal_hi[i] && r1 > g.signal_lo[i])) return true;
+    return false;
+}
+__device__ __forceinline__ void tile_signal(const b200_block_geom& g, int n, int r0, int r1) {
+    for (int i = 0; i < g.n_signal; ++i)
+        if (g.signal_hi[i] <= g.signal_lo[i] || (r0 < g.signal_hi[i] && r1 > g.signal_lo[i]))
+            red_release_sys_add(g.signal[i] + n, 1);
+}
+
 // Flow-control gate and completion notice of a block launch (b200_block_geom::gate / done*).
 // gate: called by ONE thread per CTA before the CTA-wide barrier that ends the kernel prologue.
 __device__ __forceinline__ void block_gate_wait(const b200_block_geom& g) {

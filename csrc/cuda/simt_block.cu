@@ -200,10 +200,7 @@ simt_block_kernel(const float* __restrict__ wt,    // [F][F*C][K]
     if (g.n_signal > 0 || g.done_count) {
         __syncthreads();
         if (threadIdx.x == 0) {
-            if (g.n_signal > 0) {
-                __threadfence_system();
-                for (int i = 0; i < g.n_signal; ++i) red_release_sys_add(g.signal[i] + n, 1);
-            }
+            tile_signal(g, n, pr0, min(pr0 + PR, g.p1));
             block_done_signal(g);
         }
     }
@@ -229,6 +226,18 @@ extern "C" int b200_simt_block_tiles(const b200_block_geom* g) {
     const int rows = g->p1 - g->p0;
     if (rows <= 0) return 0;
     return cdiv(rows, PR) * cdiv(g->Wp, PC) * kgroups_for(g->K);
+}
+
+extern "C" int b200_simt_block_tiles_rows(const b200_block_geom* g, int lo, int hi) {
+    if (!g) return B200_ERR_ARG;
+    TileShape ts = pick_tile(g);
+    const int PR = (ts.tr - 1) / 2, PC = (ts.tc - 1) / 2;
+    int n = 0;
+    for (int r0 = g->p0; r0 < g->p1; r0 += PR) {
+        const int r1 = r0 + PR < g->p1 ? r0 + PR : g->p1;
+        if (hi <= lo || (r0 < hi && r1 > lo)) ++n;
+    }
+    return n * cdiv(g->Wp, PC) * kgroups_for(g->K);
 }
 
 extern "C" int b200_simt_block(const float* wt, const float* bias, float* out,

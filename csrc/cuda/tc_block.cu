@@ -187,10 +187,7 @@ __device__ __forceinline__ void epilogue_pool_lrn(const TcParams& p, uint32_t tm
         }
     }
     bar_group<kBar, kWarps>();                                // cbuf / pbuf free again, all stores issued
-    if (g.n_signal > 0 && te == 0) {                          // producer side of the halo flags
-        __threadfence_system();
-        for (int i = 0; i < g.n_signal; ++i) red_release_sys_add(g.signal[i] + n, 1);
-    }
+    if (g.n_signal > 0 && te == 0) tile_signal(g, n, pr0, min(pr0 + p.PR, g.p1));   // producer side of the halo flags
 }
 
 // pooled-pixel table (cbuf offset of the window origin, (pi,pj)) and the zero borders of the LRN rows
@@ -475,7 +472,8 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
 //     warps 10-13 are the epilogue: warp q owns TMEM lane quarter q = channels 32q..32q+31, drains
 //     three conv rows at a time through a private smem strip, max-pools and stores — no CTA-wide
 //     barrier anywhere in the epilogue.
-constexpr int kSwThreads = 448;
+constexpr int kSwThreads = 576;                     // 8 producer + MMA + TMA + 8 epilogue warps
+constexpr int kSwEpiWarps = 8;                      // two per TMEM lane quarter: even / odd pooled rows
 constexpr int kSwWStageBytes = 128 * 128;            // weight stage: 128 rows (K_out rows valid) x 128 B
 
 struct SwParams {
@@ -532,7 +530,7 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(tfull_bar + 8 * b, 1);
-            mbar_init(tempty_bar + 8 * b, 4);
+            mbar_init(tempty_bar + 8 * b, kSwEpiWarps);
         }
         fence_mbar_init();
         block_gate_wait(g);
@@ -753,9 +751,10 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
         // ======================================= epilogue warps ==========================
         const int q = warp & 3;                                // a warp can only touch TMEM lane quarter warp%4;
                                                                // quarter q == channels 32q..32q+31
+        const int half = (warp - 10) >> 2;                     // two warps per quarter: even / odd pooled rows
         const bool live = q * 32 < KO;
         const int ch = q * 32 + lane;
-        float* strip = reinterpret_cast<float*>(gbase + sp.strip_off + q * sp.strip_bytes);
+        float* strip = reinterpret_cast<float*>(gbase + sp.strip_off + (half * 4 + q) * sp.strip_bytes);
         const float bch = s_bias[ch];
         int buf = 0;
         uint32_t bphase = 0;
@@ -767,7 +766,7 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
             mbar_wait(tfull_bar + 8 * buf, bphase);
             tc_fence_after();
             if (live) {
-                for (int pr = 0; pr < p.PR; ++pr) {
+                for (int pr = half; pr < p.PR; pr += 2) {
                     // conv rows 2pr..2pr+2 = slots [col0, col0 + 3*TC); load whole 32-column groups
                     const int col0 = 2 * pr * p.TC;
                     int start = col0;
@@ -781,6 +780,21 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                     }
                     __syncwarp();
                     const int prg = pr0 + pr;
+                    const bool row_ok = prg < g.p1 && prg < g.Hp && ch < KO;
+                    float* orow = out + (((size_t)n * g.out_slab + (prg - g.out_base)) * g.Wp) * KO + ch;
+                    // halo push: this row's copy in the neighbours' slabs (nullptr: not read by that neighbour)
+                    float* mrow[B200_MAX_MIRROR] = {nullptr, nullptr, nullptr, nullptr};
+                    bool pushed = false;
+                    if (g.n_mirror > 0) {                       // kernel-uniform: single-GPU launches skip all of it
+#pragma unroll
+                        for (int m = 0; m < B200_MAX_MIRROR; ++m) {
+                            const bool in = m < g.n_mirror && prg >= g.mirror[m].lo && prg < g.mirror[m].hi;
+                            if (in)
+                                mrow[m] = g.mirror[m].ptr +
+                                          (((size_t)n * g.mirror[m].slab + (prg - g.mirror[m].base)) * g.Wp) * KO + ch;
+                            pushed |= in;
+                        }
+                    }
                     for (int pc = 0; pc < p.PC; ++pc) {
                         const float* c0p = strip + (shift + 2 * pc) * kCbufPitch + lane;
                         float mx = -INFINITY;
@@ -791,12 +805,13 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                         float val = fmaxf(mx + bch, 0.f);
                         if (p.round_out) val = to_tf32(val);
                         const int pcg = pc0 + pc;
-                        if (prg < g.p1 && prg < g.Hp && pcg < g.Wp && ch < KO) {
-                            out[(((size_t)n * g.out_slab + (prg - g.out_base)) * g.Wp + pcg) * KO + ch] = val;
-                            for (int m = 0; m < g.n_mirror; ++m)   // halo push: the neighbour's copy of this row
-                                if (prg >= g.mirror[m].lo && prg < g.mirror[m].hi)
-                                    out_ptr_at(g.mirror[m].ptr, n, g.mirror[m].slab, g.mirror[m].base, prg, g.Wp, pcg,
-                                               KO)[ch] = val;
+                        if (row_ok && pcg < g.Wp) {
+                            orow[(size_t)pcg * KO] = val;
+                            if (pushed) {                       // warp-uniform: only boundary rows take this path
+#pragma unroll
+                                for (int m = 0; m < B200_MAX_MIRROR; ++m)
+                                    if (mrow[m]) mrow[m][(size_t)pcg * KO] = val;
+                            }
                         }
                     }
                     __syncwarp();
@@ -805,12 +820,10 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty_bar + 8 * buf);
-            if (g.n_signal > 0) {                              // all four warps' stores, then one signal
-                asm volatile("bar.sync 2, 128;" ::: "memory");
-                if (q == 0 && lane == 0) {
-                    __threadfence_system();
-                    for (int i = 0; i < g.n_signal; ++i) red_release_sys_add(g.signal[i] + n, 1);
-                }
+            const int tr0 = pr0, tr1 = min(pr0 + p.PR, g.p1);
+            if (g.n_signal > 0 && tile_signals(g, tr0, tr1)) {   // all eight warps' stores, then one signal (CTA-uniform)
+                asm volatile("bar.sync 2, 256;" ::: "memory");
+                if (warp == 11 && lane == 0) tile_signal(g, n, tr0, tr1);   // quarter 3 has no channels when K_out = 96
             }
             if (++buf == 2) { buf = 0; bphase ^= 1; }
         }
@@ -1412,7 +1425,7 @@ int fill_swapped(const b200_block_geom* g, SwParams* sp, int flags) {
     p.patch_off = (uint32_t)stages;
     sp->strip_off = (uint32_t)((stages + patch_bytes + 15) & ~(size_t)15);
     sp->strip_bytes = (uint32_t)(32 * sp->nload * kCbufPitch * 4);
-    sp->sw_ctl_off = (uint32_t)((sp->strip_off + 4 * (size_t)sp->strip_bytes + 15) & ~(size_t)15);
+    sp->sw_ctl_off = (uint32_t)((sp->strip_off + kSwEpiWarps * (size_t)sp->strip_bytes + 15) & ~(size_t)15);
     // D = channels x pixels: M = 128 (K_out rows padded), N = pixel slots
     sp->sw_idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)((128 * p.nacc) >> 3) << 17) | ((128u >> 4) << 24);
     const size_t total = 1024 + sp->sw_ctl_off + 112 + kRowTab * 8 + 128 * 4 + 64;
@@ -1669,6 +1682,29 @@ extern "C" int b200_tc_set_policy(const char* key, const char* value) {
     else if (!strcmp(key, "dbg")) q.dbg = atoi(value);
     else return B200_ERR_ARG;
     return B200_OK;
+}
+
+// tiles per image that produce at least one pooled row of [lo,hi): the arrival-counter target of a reader that
+// only waits for those rows (b200_block_geom::signal_lo / signal_hi)
+extern "C" int b200_tc_block_tiles_rows(const b200_block_geom* g, int lo, int hi) {
+    if (!g) return B200_ERR_ARG;
+    if (g->p1 <= g->p0) return 0;
+    TcParams p;
+    bool have = false;
+    if (db_requested(g) || pair_requested(g)) {
+        DbParams dp;
+        if (fill_db(g, &dp, 0) == B200_OK) { p = dp.t; have = true; }
+    }
+    if (!have) {
+        int rc = fill_params(g, &p, 0);
+        if (rc != B200_OK) return rc;
+    }
+    int n = 0;
+    for (int r0 = g->p0; r0 < g->p1; r0 += p.PR) {
+        const int r1 = r0 + p.PR < g->p1 ? r0 + p.PR : g->p1;
+        if (hi <= lo || (r0 < hi && r1 > lo)) ++n;
+    }
+    return n * p.tiles_c;
 }
 
 extern "C" int b200_tc_block_tiles(const b200_block_geom* g) {

@@ -113,6 +113,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
         : "memory");
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void bar_producers() {     // named barrier 1: the 8 producer warps
     asm volatile("bar.sync 1, 256;" ::: "memory");
 }
@@ -198,6 +208,37 @@ __device__ __forceinline__ void tma2_load_4d(uint32_t dst, const CUtensorMap* ma
         " [%0], [%1, {%2, %3, %4, %5}], [%6];"
         ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(bar & kPeerBitMask)
         : "memory");
+}
+
+// ---- cross-CTA exchange inside a CTA pair (channel-split kernel): DSMEM stores + a cluster-scope mbarrier ----
+// `addr` is a shared::cta window address of THIS CTA; the partner's copy of the same location differs in bit 24.
+constexpr uint32_t kPartnerBit = 0x01000000u;
+__device__ __forceinline__ void st_partner_f32(uint32_t addr, float v) {
+    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr ^ kPartnerBit), "f"(v) : "memory");
+}
+// one arrival on the partner's barrier; releases this thread's (and, through a preceding CTA barrier, its CTA's)
+// earlier writes — DSMEM stores included — at cluster scope
+__device__ __forceinline__ void mbar_arrive_partner_release(uint32_t bar) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar ^ kPartnerBit) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+    if (mbar_try_wait_cluster(bar, parity)) return;
+    const unsigned long long t0 = globaltimer_ns();
+    unsigned spins = 0;
+    while (!mbar_try_wait_cluster(bar, parity)) {
+        if ((++spins & 0xFFF) == 0 && globaltimer_ns() - t0 > kSpinTimeoutNs) asm volatile("trap;");
+    }
 }
 
 // K-major, 128B-swizzled operand tile: 8-row groups of 1024 B, rows 128 B apart inside a group.

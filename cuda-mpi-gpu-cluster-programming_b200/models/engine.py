@@ -214,8 +214,10 @@ class Blocks12Engine:
         self.out = self.outs[0]
         self._active = [r for r in range(self.world) if self.plan.ranks[r].active]
         self.flags_t = self.buf_flags.tensor((self.lay.count,), torch.int32)
-        # tiles per image of every rank's block 1 (arrival-counter targets)
-        self._b1_tiles = [self._tiles(self._geom_block1(r, probe=True)) for r in range(self.world)]
+        # arrival-counter targets: tiles per image of the peer's block 1 that produce the rows read from it
+        self._b1_tiles = {}
+        for peer, lo, hi in self.rp.halo:
+            self._b1_tiles[peer] = self._tiles_rows(self._geom_block1(peer, probe=True), lo, hi)
 
     def _pool1_slab(self, rp: RankPlan):
         """(first global row, rows) of a rank's pool1 slab: the rows it owns, plus — when halos are pushed — the
@@ -228,11 +230,11 @@ class Blocks12Engine:
     def _flag_ptr(self, rank: int, int_index: int) -> int:
         return self.symm.ptr(rank, "flags") + 4 * int_index
 
-    def _tiles(self, g) -> int:
+    def _tiles_rows(self, g, lo: int, hi: int) -> int:
         if self.precision == "simt":
-            return cu.simt_block_tiles(g)
+            return cu.simt_block_tiles_rows(g, lo, hi)
         from ..ops import tc
-        return tc.block_tiles(g)
+        return tc.block_tiles_rows(g, lo, hi)
 
     # ---- geometry ------------------------------------------------------------------------------
     def input_view(self, i: int = 0) -> torch.Tensor:
@@ -274,7 +276,7 @@ class Blocks12Engine:
         s2d = self.s2d
         S1 = p1.S
         Hin = self.s2d_hs if s2d else sh.H
-        mirrors = []
+        mirrors, signal_rows = [], []
         if probe:
             segs = [dict(ptr=1, base=0, slab=Hin, lo=0, hi=Hin)]
             signals, out_ptr = [], 0
@@ -289,8 +291,10 @@ class Blocks12Engine:
             else:
                 segs = [dict(ptr=self.buf_in[in_idx].ptr, base=self.in_base, slab=self.in_rows,
                              lo=rp.in_rows[0], hi=rp.in_rows[1])]
-            signals = [self._flag_ptr(peer, self.lay.arr_off + r * self.lay.nmax)
-                       for peer in sorted({p for p, _, _ in rp.serves})]
+            # one arrival counter per reader, bumped only by the tiles that produce the rows it reads
+            served = sorted(rp.serves)
+            signals = [self._flag_ptr(peer, self.lay.arr_off + r * self.lay.nmax) for peer, _, _ in served]
+            signal_rows = [(lo, hi) for _, lo, hi in served]
             if self.halo == "push":
                 parity = self.epoch & 1
                 for peer, lo, hi in rp.serves:
@@ -309,7 +313,7 @@ class Blocks12Engine:
             N=rp.n_images, K=p1.K, **conv,
             Hc=sh.Hc1, Wc=sh.Wc1, Hp=sh.Hp1, Wp=sh.Wp1, rows=rp.pool1_own,
             out_base=self._pool1_slab(rp)[0], out_slab=self._pool1_slab(rp)[1], lrn=None,
-            segs=segs, signals=signals, mirrors=mirrors,
+            segs=segs, signals=signals, signal_rows=signal_rows, mirrors=mirrors,
             status_ptr=0 if probe else self._flag_ptr(self.rank, self.lay.status_off),
             timeout_ns=self.timeout_ns, **gate)
         return g

@@ -40,6 +40,7 @@ class BlockGeom(C.Structure):
         ("status", C.c_void_p), ("timeout_ns", C.c_ulonglong), ("epoch", C.c_void_p),
         ("gate", C.c_void_p), ("gate_target", C.c_int), ("n_done", C.c_int),
         ("done_count", C.c_void_p), ("done", C.c_void_p * 2),
+        ("signal_lo", C.c_int * MAX_SIGNAL), ("signal_hi", C.c_int * MAX_SIGNAL),
         ("n_mirror", C.c_int), ("pad2_", C.c_int), ("mirror", RowMirror * MAX_MIRROR)]
 
 
@@ -55,6 +56,7 @@ def lib():
         L.b200_simt_block.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.POINTER(BlockGeom), C.c_void_p]
         L.b200_simt_block_tiles.argtypes = [C.POINTER(BlockGeom)]
+        L.b200_simt_block_tiles_rows.argtypes = [C.POINTER(BlockGeom), C.c_int, C.c_int]
         L.b200_symm_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
         L.b200_symm_free.argtypes = [C.c_void_p]
         L.b200_ipc_export.argtypes = [C.c_void_p, C.c_char_p]
@@ -107,7 +109,7 @@ def make_block_geom(*, N, H, W, Cin, K, F, S, P, Hc, Wc, Hp, Wp, rows: Tuple[int
                     status_ptr: int = 0, timeout_ns: int = DEFAULT_TIMEOUT_NS,
                     epoch_ptr: int = 0, in_pitch: int = 0, gate_ptr: int = 0, gate_target: int = 0,
                     done_count_ptr: int = 0, done: Sequence[int] = (),
-                    mirrors: Sequence[dict] = ()) -> BlockGeom:
+                    mirrors: Sequence[dict] = (), signal_rows: Sequence[Tuple[int, int]] = ()) -> BlockGeom:
     g = BlockGeom()
     g.N, g.H, g.W, g.C = N, H, W, Cin
     g.K, g.F, g.S, g.P = K, F, S, P
@@ -126,6 +128,8 @@ def make_block_geom(*, N, H, W, Cin, K, F, S, P, Hc, Wc, Hp, Wp, rows: Tuple[int
     g.n_signal = len(signals)
     for i, p in enumerate(signals):
         g.signal[i] = p
+        lo, hi = signal_rows[i] if i < len(signal_rows) else (0, 0)      # (0, 0): every tile signals
+        g.signal_lo[i], g.signal_hi[i] = lo, hi
     g.status = status_ptr or None
     g.timeout_ns = timeout_ns
     g.epoch = epoch_ptr or None
@@ -153,6 +157,10 @@ def simt_block(w_ffck: torch.Tensor, bias: torch.Tensor, out_ptr: int, g: BlockG
 
 def simt_block_tiles(g: BlockGeom) -> int:
     return int(lib().b200_simt_block_tiles(C.byref(g)))
+
+
+def simt_block_tiles_rows(g: BlockGeom, lo: int, hi: int) -> int:
+    return int(lib().b200_simt_block_tiles_rows(C.byref(g), lo, hi))
 
 
 def flag_signal(targets: Sequence[int], add: int = 1) -> None:

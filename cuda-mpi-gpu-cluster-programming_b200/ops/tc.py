@@ -26,6 +26,7 @@ def _lib():
         L.b200_tc_block_tiles.argtypes = [C.POINTER(cu.BlockGeom)]
         L.b200_tc_block.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(cu.BlockGeom),
                                     C.c_int, C.c_void_p]
+        L.b200_tc_block_tiles_rows.argtypes = [C.POINTER(cu.BlockGeom), C.c_int, C.c_int]
         L.b200_tc_set_policy.argtypes = [C.c_char_p, C.c_char_p]
         _bound = True
     return L
@@ -67,4 +68,12 @@ def block_tiles(g: cu.BlockGeom) -> int:
     n = int(_lib().b200_tc_block_tiles(C.byref(g)))
     if n < 0:
         cu.cu_check(n, "tc_block_tiles")
+    return n
+
+
+def block_tiles_rows(g: cu.BlockGeom, lo: int, hi: int) -> int:
+    """Tiles per image that produce a pooled row of [lo, hi): arrival target of a reader of those rows."""
+    n = int(_lib().b200_tc_block_tiles_rows(C.byref(g), lo, hi))
+    if n < 0:
+        cu.cu_check(n, "tc_block_tiles_rows")
     return n

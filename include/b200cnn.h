@@ -154,6 +154,10 @@ typedef struct {
     int n_done;
     unsigned int* done_count;
     int* done[2];
+    /* signal[i] is bumped only by tiles that produce a pooled row in [signal_lo[i], signal_hi[i]) — the rows its
+     * reader waits for — so interior tiles pay no system-scope release; hi <= lo means "every tile".  The
+     * reader's target per image is b200_*_block_tiles_rows(g, lo, hi) per forward. */
+    int signal_lo[B200_MAX_SIGNAL], signal_hi[B200_MAX_SIGNAL];
     int n_mirror;            /* halo push targets (see b200_row_mirror); stored before signal[] is bumped */
     int pad2_;
     b200_row_mirror mirror[B200_MAX_MIRROR];
@@ -167,6 +171,8 @@ int b200_pack_weights_ffck(const float* w_kcff, float* w_ffck, int K, int C, int
 int b200_simt_block(const float* w_ffck, const float* bias, float* out,
                     const b200_block_geom* g, void* stream);
 int b200_simt_block_tiles(const b200_block_geom* g);
+/* tiles per image that produce at least one pooled row of [lo,hi) (see signal_lo/signal_hi) */
+int b200_simt_block_tiles_rows(const b200_block_geom* g, int lo, int hi);
 
 /* tcgen05 / TMEM / TMA tensor-core path (TF32 operands, fp32 accumulate); same b200_block_geom.
  * A handle owns one layer's weights on the device, K-major [K][Kpad], TF32-rounded, plus the TMA
@@ -176,6 +182,7 @@ int b200_tc_conv_destroy(void* handle);
 int b200_tc_block(void* handle, const float* bias, float* out, const b200_block_geom* g,
                   int flags /* bit0: round outputs to TF32 */, void* stream);
 int b200_tc_block_tiles(const b200_block_geom* g);
+int b200_tc_block_tiles_rows(const b200_block_geom* g, int lo, int hi);
 /* Process-wide kernel choice (default: environment B200_TC_CONV2 / B200_TC_CONV1 at first use, else auto):
  * key "conv2" = auto|single|db|pair (single-buffered, double-buffered TMEM, tcgen05 CTA pair),
  * key "conv1" = auto|cpasync (pixel operand by TMA when eligible, or always the cp.async loader).
