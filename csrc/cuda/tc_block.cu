@@ -1227,6 +1227,253 @@ tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_co
     if (threadIdx.x == 0) block_done_signal(g);
 }
 
+// ------------------------------------------ channel-split CTA-pair kernel (K_out = 256, stride 1) ----
+// The pair kernel above gives each CTA its own 128-pixel tile, so a rank's 7 x 13 pooled block (7/13 of an image at 8
+// GPUs) needs 5 tiles and 32 images do not fit one round of 74 pairs.  Here the pair shares ONE tile of up to 256 pixel
+// slots and splits the CHANNELS instead — the tcgen05 pair issues D[256 channels x 256 pixels] = W[256 x K] * X^T:
+//   A operand = weights, M = 256: CTA r stages (and gets the accumulator rows of) channels 128r .. 128r+127
+//   B operand = im2col pixels, N = 256: CTA r stages the pixel rows [r*HR, (r+1)*HR) of the tile (HR x TC <= 128 slots,
+//               one TMA box per filter tap and 32 input channels, zero fill outside the slab)
+//   D in each CTA's TMEM = its 128 channels (lanes) x 256 pixel slots (columns), double buffered (2 x 256 columns).
+// A tile is (2PR+1) x (2PC+1) conv pixels = PR x PC pooled outputs (8 x 15 + 7 x 15 pixels for 7 x 7 pooled): the whole
+// half-image of a rank is 2 tiles, a whole 27 x 27 image 4.
+// Epilogue (4 warps, lane = channel): three conv rows at a time from TMEM through a per-warp strip, max-pool along the
+// columns, +bias, ReLU into pbuf[pooled pixel][channel].  LRN's window of 5 channels crosses the CTA boundary at channels
+// 127|128: each CTA pushes its two edge channels into the partner's halo buffer (DSMEM stores) and the two epilogues meet
+// on a cluster-scope mbarrier once per tile; then LRN and 512 B-per-pixel stores of the CTA's channel half.
+// Every TMA load here reads this GPU's memory only (fill_cs refuses anything else) and none is a multicast load.
+//   warp 0: TMA (both CTAs)   warp 1: TMEM owner (both), MMA issuer (leader)   warps 2-5: epilogue
+constexpr int kCsThreads = 192;
+constexpr int kCsEpiWarp0 = 2;
+constexpr int kCsMaxStages = 5;
+constexpr int kCsPixStageBytes = 128 * 128;           // 128 pixel slots x 32 floats
+constexpr int kCsWStageBytes = 128 * 128;             // 128 weight rows x 32 floats
+constexpr int kCsStripFloats = 3 * 16 * kCbufPitch;   // three conv rows x 16 columns per epilogue warp
+constexpr int kCsPbufPitch = 128 + 4;                 // [2 lower-halo | 128 channels | 2 upper-halo]
+
+struct CsParams {
+    TcParams t;                                       // PR, PC, TR = 2PR+1, TC = 2PC+1 (<= 16), tiles, nkb, stages
+    int HR;                                           // pixel rows staged per CTA (PR + 1)
+    uint32_t strip_off, pbuf_off, xh_off, cs_ctl_off;
+    uint32_t pix_bytes;                               // bytes of one pixel box (32 x TC x HR floats)
+    uint32_t idesc2;                                  // M = 256, N = 256
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kCsThreads, 1)
+tc_block_cs_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_constant__ CUtensorMap tmapX,
+                   const __grid_constant__ CsParams cp, const float* __restrict__ bias, float* __restrict__ out) {
+    extern __shared__ uint8_t smem_raw[];
+    const TcParams& p = cp.t;
+    const b200_block_geom& g = p.g;
+    const uint32_t rank = cluster_ctarank();                  // 0 = leader; also this CTA's channel half
+
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
+    const int NS = p.stages;
+    const uint32_t w_off = NS * kCsPixStageBytes;             // pixel stages first, then weight stages
+    const uint32_t full_bar = base + cp.cs_ctl_off;           // [8]  leader's copy is the live one
+    const uint32_t empty_bar = full_bar + 64;                 // [8]  per CTA (multicast commit)
+    const uint32_t tfull_bar = full_bar + 128;                // [2]  per CTA (multicast commit)
+    const uint32_t tempty_bar = full_bar + 144;               // [2]  leader's copy, 8 arrivals (4 warps x 2 CTAs)
+    const uint32_t xbar = full_bar + 160;                     // [2]  per CTA, by tile parity: the partner's halo pushes landed
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + cp.cs_ctl_off + 176);
+    float* s_bias = reinterpret_cast<float*>(gbase + cp.cs_ctl_off + 192);       // 128 floats
+    float* pbuf = reinterpret_cast<float*>(gbase + cp.pbuf_off);
+    float* xh = reinterpret_cast<float*>(gbase + cp.xh_off);  // [2 tile parities][kMaxPooled][2] halo channels from the partner
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NS; ++s) {
+            mbar_init(full_bar + 8 * s, 1);
+            mbar_init(empty_bar + 8 * s, 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(tfull_bar + 8 * b, 1);
+            mbar_init(tempty_bar + 8 * b, 8);
+            mbar_init(xbar + 8 * b, 1);
+        }
+        fence_mbar_init();
+        block_gate_wait(g);
+    }
+    for (int i = threadIdx.x; i < 128; i += kCsThreads) s_bias[i] = bias[128 * rank + i];
+    if (warp == 1) tmem_alloc2(smem_u32(tmem_slot), 512);
+    tc_fence_before();
+    cluster_sync_all();                                       // both CTAs' barriers and TMEM exist
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int tiles_per_img = p.tiles_r * p.tiles_c;
+    const long long npairs = gridDim.x >> 1, pair_id = blockIdx.x >> 1;
+
+    if (warp == 0) {
+        // ======================================= TMA issuer ==============================
+        int stage = 0;
+        uint32_t phase = 0;
+        for (long long w = pair_id; w < p.total_tiles; w += npairs) {
+            const int n = (int)(w / tiles_per_img);
+            const int rem = (int)(w - (long long)n * tiles_per_img);
+            const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
+            const int cr0 = 2 * (g.p0 + tr_i * p.PR), cc0 = 2 * (tc_i * p.PC);
+            const int ir0 = cr0 - g.P;                          // first input row of the tile (stride 1)
+            if (p.any_flag) {                                   // pushed halo rows of image n have landed?
+                if (lane == 0) {
+                    const int IRT = p.TR - 1 + g.F;
+                    for (int s = 0; s < g.nseg; ++s)
+                        if (g.seg[s].flag && ir0 < g.seg[s].hi && ir0 + IRT > g.seg[s].lo)
+                            wait_flag_ge(g.seg[s].flag + n, g.seg[s].target * (g.epoch ? *g.epoch : 1), g.status,
+                                         g.timeout_ns);
+                    fence_proxy_async_global();                 // peer's generic stores -> our TMA reads
+                }
+                __syncwarp();
+            }
+            const int y0 = ir0 - g.seg[0].base + (int)rank * cp.HR;   // slab-relative row of this CTA's filter row 0
+            int fy = 0, fx = 0, cch = 0;
+            for (int kb = 0; kb < p.nkb; ++kb) {
+                mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+                if (lane == 0) {
+                    const uint32_t fb = full_bar + 8 * stage;
+                    if (rank == 0) mbar_arrive_expect_tx(fb, 2u * (cp.pix_bytes + (uint32_t)kCsWStageBytes));
+                    tma2_load_4d(base + stage * kCsPixStageBytes, &tmapX, cch * kBlockK, cc0 + fx - g.P, y0 + fy, n, fb);
+                    tma2_load_2d(base + w_off + stage * kCsWStageBytes, &tmapW, kb * kBlockK, (int)rank * 128, fb);
+                }
+                __syncwarp();
+                if (++fx == g.F) { fx = 0; if (++fy == g.F) { fy = 0; ++cch; } }
+                if (++stage == NS) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        // ======================================= MMA issuer (leader CTA only) ============
+        if (rank == 0) {
+            int stage = 0, buf = 0;
+            uint32_t phase = 0, bphase = 0;
+            for (long long w = pair_id; w < p.total_tiles; w += npairs) {
+                mbar_wait(tempty_bar + 8 * buf, bphase ^ 1);    // both CTAs' epilogues have drained this buffer
+                tc_fence_after();
+                for (int kb = 0; kb < p.nkb; ++kb) {
+                    mbar_wait(full_bar + 8 * stage, phase);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint64_t dw = make_smem_desc(base + w_off + stage * kCsWStageBytes);
+                        const uint64_t dx = make_smem_desc(base + stage * kCsPixStageBytes);
+#pragma unroll
+                        for (int ks = 0; ks < kBlockK / 8; ++ks)
+                            umma2_tf32(tmem_base + (uint32_t)(buf * 256), dw + 2 * ks, dx + 2 * ks, cp.idesc2,
+                                       (kb | ks) != 0 ? 1u : 0u);
+                        umma2_commit_mc(empty_bar + 8 * stage, 3);       // frees the stage in both CTAs
+                        if (kb == p.nkb - 1) umma2_commit_mc(tfull_bar + 8 * buf, 3);
+                    }
+                    __syncwarp();
+                    if (++stage == NS) { stage = 0; phase ^= 1; }
+                }
+                if (++buf == 2) { buf = 0; bphase ^= 1; }
+            }
+        }
+    } else {
+        // ======================================= epilogue warps ==========================
+        const int q = warp & 3;                                // TMEM lane quarter = channels 32q..32q+31 of this CTA
+        const int te = (warp - kCsEpiWarp0) * 32 + lane;       // thread index inside the epilogue group
+        const int cl = q * 32 + lane;                          // channel inside the CTA's half
+        const int N = g.K;                                     // 256
+        float* strip = reinterpret_cast<float*>(gbase + cp.strip_off) + q * kCsStripFloats;
+        const float bch = s_bias[cl];
+        const int PP = p.PR * p.PC;
+        const bool do_lrn = g.lrn.N_lrn > 0;
+        const float al = g.lrn.mode == B200_LRN_ALPHA_OVER_N ? g.lrn.alpha / (float)max(g.lrn.N_lrn, 1) : g.lrn.alpha;
+        const float nbeta = -g.lrn.beta;
+        // conv row ri of the tile sits in TMEM columns col(ri) .. col(ri)+TC-1 of the buffer; 16 columns are loaded from
+        // min(col, 240), so tile column 0 lands in strip column col - start
+        auto row_col = [&](int ri) { const int h = ri >= cp.HR ? 1 : 0; return 128 * h + (ri - h * cp.HR) * p.TC; };
+        auto row_shift = [&](int ri) { const int c = row_col(ri); return c + 16 > 256 ? c - (256 - 16) : 0; };
+        int buf = 0, it = 0;
+        uint32_t bphase = 0;
+        for (long long w = pair_id; w < p.total_tiles; w += npairs, ++it) {
+            const int n = (int)(w / tiles_per_img);
+            const int rem = (int)(w - (long long)n * tiles_per_img);
+            const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
+            const int pr0 = g.p0 + tr_i * p.PR, pc0 = tc_i * p.PC;
+            float* xh_t = xh + (it & 1) * (kMaxPooled * 2);     // this tile's halo buffer (by parity: the partner may
+                                                               // already push the next tile's while we read this one)
+            mbar_wait(tfull_bar + 8 * buf, bphase);
+            tc_fence_after();
+            for (int pr = 0; pr < p.PR; ++pr) {
+                // conv rows 2pr, 2pr+1, 2pr+2 live in row buffers (row % 3); the first is left over from pr-1
+                for (int ri = (pr == 0 ? 0 : 2 * pr + 1); ri <= 2 * pr + 2; ++ri) {
+                    const int start = row_col(ri) - row_shift(ri);
+                    const int rb = ri % 3;
+                    uint32_t r[16];
+                    tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * 256 + start), r);
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) strip[(rb * 16 + c) * kCbufPitch + lane] = __uint_as_float(r[c]);
+                }
+                __syncwarp();
+                const int prg = pr0 + pr;
+                const int b0 = (2 * pr) % 3, b1 = (2 * pr + 1) % 3, b2 = (2 * pr + 2) % 3;
+                const float* s0 = strip + (b0 * 16 + row_shift(2 * pr)) * kCbufPitch + lane;
+                const float* s1 = strip + (b1 * 16 + row_shift(2 * pr + 1)) * kCbufPitch + lane;
+                const float* s2 = strip + (b2 * 16 + row_shift(2 * pr + 2)) * kCbufPitch + lane;
+                for (int pc = 0; pc < p.PC; ++pc) {
+                    const int o = 2 * pc * kCbufPitch;
+                    float mx = fmaxf(fmaxf(s0[o], s0[o + kCbufPitch]), s0[o + 2 * kCbufPitch]);
+                    mx = fmaxf(mx, fmaxf(fmaxf(s1[o], s1[o + kCbufPitch]), s1[o + 2 * kCbufPitch]));
+                    mx = fmaxf(mx, fmaxf(fmaxf(s2[o], s2[o + kCbufPitch]), s2[o + 2 * kCbufPitch]));
+                    float val = fmaxf(mx + bch, 0.f);           // relu(max(x)+b) == max(relu(x+b))
+                    const int pp = pr * p.PC + pc;
+                    if (do_lrn) {
+                        pbuf[pp * kCsPbufPitch + 2 + cl] = val;
+                        // LRN window halo: channels 128,129 go to CTA 0's upper halo, 126,127 to CTA 1's lower halo
+                        if (rank == 1 && cl < 2) st_partner_f32(smem_u32(xh_t + pp * 2 + cl), val);
+                        if (rank == 0 && cl >= 126) st_partner_f32(smem_u32(xh_t + pp * 2 + (cl - 126)), val);
+                    } else {
+                        const int pcg = pc0 + pc;
+                        if (p.round_out) val = to_tf32(val);
+                        if (prg < g.p1 && prg < g.Hp && pcg < g.Wp)
+                            out_ptr_at(out, n, g.out_slab, g.out_base, prg, g.Wp, pcg, N)[128 * rank + cl] = val;
+                    }
+                }
+                __syncwarp();
+            }
+            // every tcgen05.ld of this warp has completed: hand the accumulator back before the LRN pass
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(tempty_bar + 8 * buf);
+            if (do_lrn) {
+                bar_epilogue();                                 // pbuf is whole; this CTA's halo pushes are issued
+                // two barriers used alternately: the partner can only arrive for tile t+2 after it has seen OUR arrival
+                // for t+1, which we issue after this wait — so a barrier never runs two phases ahead of its waiter
+                const uint32_t xb = xbar + 8 * (it & 1);
+                if (te == 0) mbar_arrive_partner_release(xb);   // ... and now visible to the partner
+                mbar_wait_cluster(xb, (uint32_t)((it >> 1) & 1)); // the partner's pushes into OUR halo have landed
+                for (int i = te; i < PP * 2; i += 128) {        // halo columns of the pbuf rows (zeros at the layer's edges)
+                    const int pp = i >> 1, j = i & 1;
+                    pbuf[pp * kCsPbufPitch + j] = rank == 1 ? xh_t[i] : 0.f;
+                    pbuf[pp * kCsPbufPitch + 130 + j] = rank == 0 ? xh_t[i] : 0.f;
+                }
+                bar_epilogue();
+                for (int pp = 0; pp < PP; ++pp) {               // thread = channel: 512 B per pixel and CTA
+                    const int pi = pp / p.PC, pj = pp - pi * p.PC;
+                    const int prg = pr0 + pi, pcg = pc0 + pj;
+                    const float* px = pbuf + pp * kCsPbufPitch + te;     // channel te sits at px[2]
+                    const float a0 = px[0], a1 = px[1], a2 = px[2], a3 = px[3], a4 = px[4];
+                    const float ss = fmaf(a0, a0, fmaf(a1, a1, fmaf(a2, a2, fmaf(a3, a3, a4 * a4))));
+                    float val = a2 * exp2f(nbeta * __log2f(g.lrn.k + al * ss));
+                    if (p.round_out) val = to_tf32(val);
+                    if (prg < g.p1 && prg < g.Hp && pcg < g.Wp)
+                        out_ptr_at(out, n, g.out_slab, g.out_base, prg, g.Wp, pcg, N)[128 * rank + te] = val;
+                }
+                bar_epilogue();                                 // pbuf free for the next tile
+            }
+            if (++buf == 2) { buf = 0; bphase ^= 1; }
+        }
+    }
+
+    tc_fence_before();
+    cluster_sync_all();                                       // both CTAs are done with both TMEMs and barriers
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc2(tmem_base, 512);
+    }
+    if (threadIdx.x == 0) block_done_signal(g);
+}
+
 // --------------------------------------------------------------------------- host ----
 // Which kernel serves a layer is a process-wide policy, decided ONCE (environment at first use, or
 // b200_tc_set_policy) and never by a getenv on the launch path:
@@ -1237,7 +1484,7 @@ tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_co
 //     eligible, else cp.async;  "cpasync" forces the LSU loader.  Both loaders use one K order, so they are
 //     bit-identical.
 struct Policy {
-    int conv2 = 0;        // 0 auto, 1 single-buffered, 2 double-buffered, 3 pair
+    int conv2 = 0;        // 0 auto, 1 single-buffered, 2 double-buffered, 3 pair, 4 channel-split pair
     int conv1_tma = 1;    // 1 auto (TMA when eligible), 0 cp.async only
     int no_swap = 0;      // conv1-type layers through the generic kernel (experiments)
     int no_direct = 0;    // conv1: shared-memory patch instead of the direct loader (experiments)
@@ -1249,6 +1496,7 @@ int parse_conv2(const char* v) {
     if (!strcmp(v, "single")) return 1;
     if (!strcmp(v, "db")) return 2;
     if (!strcmp(v, "pair")) return 3;
+    if (!strcmp(v, "cs")) return 4;
     return 0;
 }
 
@@ -1435,7 +1683,7 @@ int fill_swapped(const b200_block_geom* g, SwParams* sp, int flags) {
 
 // double-buffered kernel: layout [A stages | B stages | 2 cbuf | pbuf | ctl]
 // conv2-type layers run 128-pixel tiles (db / pair kernels) unless the single-buffered kernel is forced
-inline bool db_requested(const b200_block_geom* g) { return !is_patch_mode(g->C) && policy().conv2 != 1; }
+inline bool db_requested(const b200_block_geom* g) { return !is_patch_mode(g->C) && policy().conv2 != 1; }   // incl. cs fallback
 
 int fill_db(const b200_block_geom* g, DbParams* dp, int flags) {
     if (is_patch_mode(g->C)) return B200_ERR_UNSUPPORTED;
@@ -1568,6 +1816,79 @@ int fill_pair(const TcConv* t, const b200_block_geom* g, PairParams* pp, CUtenso
         return B200_ERR_UNSUPPORTED;
     return B200_OK;
 }
+
+// channel-split pair kernel: layout [pixel stages | weight stages | 4 strips | pbuf | halo exchange | ctl]
+inline bool cs_requested(const b200_block_geom* g) {
+    return !is_patch_mode(g->C) && policy().conv2 == 4;
+}
+
+int fill_cs(const TcConv* t, const b200_block_geom* g, CsParams* cp, CUtensorMap* tmapX, int flags) {
+    if (is_patch_mode(g->C) || !t->half_ok || g->S != 1 || g->K != 256 || t->sms < 2) return B200_ERR_UNSUPPORTED;
+    if (g->lrn.N_lrn != 0 && g->lrn.N_lrn != 5) return B200_ERR_UNSUPPORTED;   // halo of two channels per side
+    if (g->n_signal != 0 || g->n_mirror != 0) return B200_ERR_UNSUPPORTED;     // a tile's stores come from two CTAs
+    if (!one_local_slab(t, g)) return B200_ERR_UNSUPPORTED;                    // TMA reads this GPU's memory only
+    memset(cp, 0, sizeof(*cp));
+    TcParams& p = cp->t;
+    p.g = *g;
+    // tile plan: PR x PC pooled per tile, each CTA stages HR = PR+1 pixel rows of TC = 2PC+1 <= 16 columns
+    const int rows = g->p1 - g->p0, pairs = t->sms / 2;
+    long best_waves = -1, best_tiles = 0;
+    int best_slots = 0;
+    for (int PR = 1; PR <= rows && PR <= 31; ++PR)
+        for (int PC = 1; PC <= 7 && PC <= g->Wp; ++PC) {
+            const int HR = PR + 1, TC = 2 * PC + 1;
+            if (HR * TC > 128 || PR * PC > kMaxPooled) continue;
+            const long tiles = (long)cdiv(rows, PR) * cdiv(g->Wp, PC);
+            const long waves = (tiles * g->N + pairs - 1) / pairs;
+            const int slots = 2 * HR * TC;
+            if (best_waves < 0 || waves < best_waves || (waves == best_waves && (tiles < best_tiles ||
+                (tiles == best_tiles && slots < best_slots)))) {
+                best_waves = waves; best_tiles = tiles; best_slots = slots;
+                p.PR = PR; p.PC = PC; p.TR = 2 * PR + 1; p.TC = TC; p.nacc = 1;
+                p.tiles_r = cdiv(rows, PR); p.tiles_c = cdiv(g->Wp, PC);
+                cp->HR = HR;
+            }
+        }
+    if (best_waves < 0) return B200_ERR_UNSUPPORTED;
+    p.nkb = num_kblocks(g->F, g->C);
+    p.round_out = flags & 1;
+    p.dbg = 0;
+    p.total_tiles = (long long)g->N * p.tiles_r * p.tiles_c;
+    for (int s = 0; s < g->nseg; ++s)
+        if (g->seg[s].flag) p.any_flag = 1;
+    cp->pix_bytes = (uint32_t)(kBlockK * p.TC * cp->HR * 4);
+    const size_t strips = 4 * (size_t)kCsStripFloats * 4;
+    const size_t pbuf_bytes = (size_t)kMaxPooled * kCsPbufPitch * 4;
+    const size_t xh_bytes = 2 * (size_t)kMaxPooled * 2 * 4;
+    const size_t ctl = 192 + 128 * 4 + 64;
+    const long avail = 226 * 1024 - 1024 - (long)(strips + pbuf_bytes + xh_bytes + ctl);
+    int stages = (int)(avail / (kCsPixStageBytes + kCsWStageBytes));
+    if (stages > kCsMaxStages) stages = kCsMaxStages;
+    if (stages < 2) return B200_ERR_UNSUPPORTED;
+    p.stages = stages;
+    cp->strip_off = (uint32_t)(stages * (kCsPixStageBytes + kCsWStageBytes));
+    cp->pbuf_off = cp->strip_off + (uint32_t)strips;
+    cp->xh_off = cp->pbuf_off + (uint32_t)pbuf_bytes;
+    cp->cs_ctl_off = cp->xh_off + (uint32_t)xh_bytes;
+    p.tmem_cols = 512;
+    cp->idesc2 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(256 >> 3) << 17) | ((256u >> 4) << 24);
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return B200_ERR_UNSUPPORTED;
+    const int pitch = g->in_pitch ? g->in_pitch : g->W * g->C;
+    const int slab = g->seg[0].slab;
+    if (slab <= 0 || (pitch * 4) % 16 != 0) return B200_ERR_UNSUPPORTED;
+    cuuint64_t dims[4] = {(cuuint64_t)g->C, (cuuint64_t)g->W, (cuuint64_t)slab, (cuuint64_t)g->N};
+    cuuint64_t strides[3] = {(cuuint64_t)g->C * 4, (cuuint64_t)pitch * 4, (cuuint64_t)slab * pitch * 4};
+    cuuint32_t box[4] = {(cuuint32_t)kBlockK, (cuuint32_t)p.TC, (cuuint32_t)cp->HR, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    if (enc(tmapX, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)g->seg[0].ptr, dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return B200_ERR_UNSUPPORTED;
+    return B200_OK;
+}
+
+size_t smem_bytes_cs(const CsParams& cp) { return 1024 + (size_t)cp.cs_ctl_off + 192 + 128 * 4 + 64; }
 
 size_t smem_bytes_pair(const PairParams& pp) {
     return 1024 + (size_t)pp.pair_ctl_off + 176 + kMaxPooled * 8 + (size_t)pp.t.g.K * 4 + 64;
@@ -1760,7 +2081,20 @@ extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const 
             return B200_OK;
         }
     }
-    if (pair_requested(g)) {
+    if (cs_requested(g)) {
+        CsParams cp;
+        CUtensorMap tmapX;
+        if (fill_cs(t, g, &cp, &tmapX, flags) == B200_OK) {     // else fall through to the pair / db kernels
+            const size_t smem = smem_bytes_cs(cp);
+            B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_cs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            long long ctas = 2 * cp.t.total_tiles;
+            if (ctas > (sms & ~1)) ctas = sms & ~1;
+            tc_block_cs_kernel<<<(unsigned)ctas, kCsThreads, smem, (cudaStream_t)stream>>>(t->tmap_half, tmapX, cp, bias, out);
+            B200_CUDA_TRY(cudaGetLastError());
+            return B200_OK;
+        }
+    }
+    if (pair_requested(g) || cs_requested(g)) {
         PairParams pp;
         CUtensorMap tmapA;
         memset(&pp, 0, sizeof(pp));
