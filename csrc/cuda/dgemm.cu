@@ -76,12 +76,105 @@ dgemm_rows_kernel(const double* __restrict__ A, const double* __restrict__ B, do
         }
 }
 
+
+// ---- pipelined kernel: 128 x 128 x 16 tiles, cp.async 16 B copies through a 4-stage ring, 8 warps of 64 x 32 ----
+// The kernel above stages tiles with plain LDG -> STS and synchronises every 16-deep k-step.  This one keeps four
+// k-steps in flight with cp.async (no registers, no stall between issue and use; B may still be a peer pointer: the
+// copies then cross NVLink), reads conflict-free fragments (row pitches = 8 words mod 32), and gives every warp a
+// 64 x 32 block = 32 DMMAs per 12 fragment loads.  Needs n even and 16 B-aligned pointers (two doubles per copy).
+constexpr int PM = 128, PN = 128, PK = 16, PSTAGES = 4;
+constexpr int PA_PITCH = PK + 4;                       // doubles: 40 words = 8 mod 32
+constexpr int PB_PITCH = PN + 4;                       // doubles: 264 words = 8 mod 32
+constexpr int PSTAGE_DOUBLES = PM * PA_PITCH + PK * PB_PITCH;
+
+__device__ __forceinline__ void cp16(double* dst, const double* src, bool ok) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(ok ? 16u : 0u) : "memory");
+}
+
+__global__ void __launch_bounds__(256, 1)
+dgemm_rows_pipelined_kernel(const double* __restrict__ A, const double* __restrict__ B, double* __restrict__ C,
+                            int rows, int n) {
+    extern __shared__ __align__(16) double smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int wm = warp >> 2, wn = warp & 3;                 // 2 x 4 warps -> 64 x 32 per warp
+    const int row0 = blockIdx.y * PM, col0 = blockIdx.x * PN;
+    const int nk = (n + PK - 1) / PK;
+
+    auto issue = [&](int kt) {                               // one k-step into ring slot kt % PSTAGES
+        double* sA = smem + (kt % PSTAGES) * PSTAGE_DOUBLES;
+        double* sB = sA + PM * PA_PITCH;
+        const int k0 = kt * PK;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int e = tid + 256 * i;                     // 1024 chunks of 2 doubles per operand
+            const int ar = e >> 3, ac = (e & 7) * 2;         // A: 128 rows x 8 chunks
+            const bool aok = row0 + ar < rows && k0 + ac < n;
+            cp16(sA + ar * PA_PITCH + ac, A + (size_t)(aok ? row0 + ar : 0) * n + (aok ? k0 + ac : 0), aok);
+            const int br = e >> 6, bc = (e & 63) * 2;        // B: 16 rows x 64 chunks
+            const bool bok = k0 + br < n && col0 + bc < n;
+            cp16(sB + br * PB_PITCH + bc, B + (size_t)(bok ? k0 + br : 0) * n + (bok ? col0 + bc : 0), bok);
+        }
+    };
+
+    double acc[8][4][2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    for (int s = 0; s < PSTAGES - 1; ++s) {                  // prologue: PSTAGES-1 steps in flight
+        if (s < nk) issue(s);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    for (int kt = 0; kt < nk; ++kt) {
+        asm volatile("cp.async.wait_group %0;" ::"n"(PSTAGES - 2) : "memory");   // step kt has landed (this thread's part)
+        __syncthreads();                                     // ... everybody's part; slot (kt-1) % PSTAGES is free
+        if (kt + PSTAGES - 1 < nk) issue(kt + PSTAGES - 1);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        const double* sA = smem + (kt % PSTAGES) * PSTAGE_DOUBLES;
+        const double* sB = sA + PM * PA_PITCH;
+#pragma unroll
+        for (int ks = 0; ks < PK / 4; ++ks) {
+            double a[8], b[4];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a[i] = sA[(wm * 64 + i * 8 + (lane >> 2)) * PA_PITCH + ks * 4 + (lane & 3)];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = sB[(ks * 4 + (lane & 3)) * PB_PITCH + wn * 32 + j * 8 + (lane >> 2)];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[i][j], a[i], b[j]);
+        }
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int r = row0 + wm * 64 + i * 8 + (lane >> 2);
+            const int c = col0 + wn * 32 + j * 8 + (lane & 3) * 2;
+            if (r < rows && c + 1 < n)                       // n is even here: a pair is in or out as a whole
+                *reinterpret_cast<double2*>(C + (size_t)r * n + c) = make_double2(acc[i][j][0], acc[i][j][1]);
+        }
+}
+
 }  // namespace
 
 extern "C" int b200_dgemm_rows(const double* A, const double* B, double* C, int rows, int n,
                                void* stream) {
     if (!A || !B || !C || rows < 0 || n <= 0) return B200_ERR_ARG;
     if (rows == 0) return B200_OK;
+    const bool aligned = ((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) % 16 == 0 && n % 2 == 0;
+    if (aligned && rows >= 64 && n >= 128) {                 // pipelined 128 x 128 kernel; tiny problems stay on the 64 x 64 one
+        const size_t smem = (size_t)PSTAGES * PSTAGE_DOUBLES * sizeof(double);
+        B200_CUDA_TRY(cudaFuncSetAttribute(dgemm_rows_pipelined_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)smem));
+        dim3 pg((n + PN - 1) / PN, (rows + PM - 1) / PM);
+        dgemm_rows_pipelined_kernel<<<pg, 256, smem, (cudaStream_t)stream>>>(A, B, C, rows, n);
+        B200_CUDA_TRY(cudaGetLastError());
+        return B200_OK;
+    }
     dim3 grid((n + BN - 1) / BN, (rows + BM - 1) / BM);
     dgemm_rows_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(A, B, C, rows, n);
     B200_CUDA_TRY(cudaGetLastError());

@@ -71,6 +71,36 @@ __global__ void splitk_reduce(const float* __restrict__ ws, int ksplit, size_t s
     }
 }
 
+// out[r][c] = act(sum_k parts[k][r*ld_in + c] + bias[c]), summed in k order.  parts[k] may be peer-mapped pointers:
+// the owner of a shard PULLS every rank's partial sums over NVLink and adds them in rank order — a reduce-scatter
+// that is deterministic (no atomics, fixed order) and needs no zeroed accumulator.
+struct PeerParts { const float* p[16]; int n; };
+__global__ void peer_reduce(PeerParts parts, size_t rows, int cols, int ld_in, const float* __restrict__ bias,
+                            float* __restrict__ out, int ld, int flags) {
+    const int c4n = cols >> 2;
+    const size_t total = rows * (size_t)c4n;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t r = i / c4n; const int c = (int)(i % c4n) * 4;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int k = 0; k < parts.n; ++k) {
+            const float4 a = *reinterpret_cast<const float4*>(parts.p[k] + r * ld_in + c);
+            v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+        }
+        float o[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            if (flags & 8) o[j] += bias[c + j];
+            if (flags & 1) o[j] = fmaxf(o[j], 0.f);
+            if (flags & 2) {
+                unsigned u;
+                asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(o[j]));
+                o[j] = __uint_as_float(u);
+            }
+        }
+        *reinterpret_cast<float4*>(out + r * ld + c) = make_float4(o[0], o[1], o[2], o[3]);
+    }
+}
+
 // one warp per row
 __global__ void softmax_rows(const float* __restrict__ x, float* __restrict__ y, int rows, int cols, int ld) {
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
@@ -206,6 +236,23 @@ extern "C" int b200_splitk_reduce(const float* ws, int ksplit, long long stride,
     if (rows == 0) return B200_OK;
     splitk_reduce<<<nblocks((size_t)rows * cols), 256, 0, (cudaStream_t)stream>>>(ws, ksplit, (size_t)stride,
                                                                                (size_t)rows, cols, bias, out, ld, flags);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+// flags: 1 ReLU, 2 round to TF32, 8 add bias (same bits as b200_tc_gemm); cols, ld_in and ld multiples of 4
+extern "C" int b200_peer_reduce(const float* const* parts, int n, long long rows, int cols, int ld_in,
+                                const float* bias, float* out, int ld, int flags, void* stream) {
+    if (!parts || !out || n < 1 || n > 16 || rows < 0 || cols <= 0 || (cols & 3) || (ld_in & 3) || (ld & 3) ||
+        ld_in < cols || ld < cols)
+        return B200_ERR_ARG;
+    if ((flags & 8) && !bias) return B200_ERR_ARG;
+    if (rows == 0) return B200_OK;
+    PeerParts pp;
+    pp.n = n;
+    for (int i = 0; i < n; ++i) { if (!parts[i]) return B200_ERR_ARG; pp.p[i] = parts[i]; }
+    peer_reduce<<<nblocks((size_t)rows * (cols / 4)), 256, 0, (cudaStream_t)stream>>>(pp, (size_t)rows, cols, ld_in, bias,
+                                                                                    out, ld, flags);
     B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;
 }

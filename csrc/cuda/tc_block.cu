@@ -1477,9 +1477,10 @@ tc_block_cs_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_const
 // --------------------------------------------------------------------------- host ----
 // Which kernel serves a layer is a process-wide policy, decided ONCE (environment at first use, or
 // b200_tc_set_policy) and never by a getenv on the launch path:
-//   conv2-type layers (C % 32 == 0):  auto = CTA-pair kernel where its TMA-fed operands apply (stride 1, one
-//     local slab), else the double-buffered kernel;  "single" / "db" / "pair" force one (pair still falls back
-//     to db on geometries it cannot take)
+//   conv2-type layers (C % 32 == 0):  auto = the channel-split CTA-pair kernel where it applies (256 output
+//     channels, stride 1, one local slab), else the pixel-split CTA-pair kernel (stride 1, one local slab), else
+//     the double-buffered kernel;  "single" / "db" / "pair" / "cs" force one (the pair kernels still fall back
+//     on geometries they cannot take)
 //   conv1-type layers (C % 32 != 0, K_out <= 128): auto = pixel operand by TMA when the input slab is local and
 //     eligible, else cp.async;  "cpasync" forces the LSU loader.  Both loaders use one K order, so they are
 //     bit-identical.
@@ -1819,7 +1820,7 @@ int fill_pair(const TcConv* t, const b200_block_geom* g, PairParams* pp, CUtenso
 
 // channel-split pair kernel: layout [pixel stages | weight stages | 4 strips | pbuf | halo exchange | ctl]
 inline bool cs_requested(const b200_block_geom* g) {
-    return !is_patch_mode(g->C) && policy().conv2 == 4;
+    return !is_patch_mode(g->C) && (policy().conv2 == 0 || policy().conv2 == 4);
 }
 
 int fill_cs(const TcConv* t, const b200_block_geom* g, CsParams* cp, CUtensorMap* tmapX, int flags) {

@@ -242,7 +242,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_constant_
                             if (p.flags & 8) v += p.bias[nb + c];
                             if (p.flags & 1) v = fmaxf(v, 0.f);
                             if (p.flags & 2) v = to_tf32(v);
-                            if (p.flags & 4) atomicAdd(crow + c, v);      // RED.ADD.F32 (local or peer)
+                            if (p.flags & 4) atomicAdd_system(crow + c, v);   // RED.ADD.F32 at system scope: C may be a peer's
                             else crow[c] = v;
                         }
                     }

@@ -115,9 +115,14 @@ class TPClassifier:
         self.fc8 = [ext.TcLinear(w.w8[o0:o0 + on, s * hs:(s + 1) * hs].contiguous(), dev) for s in range(world)]
         self.b8 = w.b8[o0:o0 + on].to(dev).contiguous()
         f4 = 4
-        self.buf_x5 = symm.alloc("tp_x5", batch * feat * f4 if rank == 0 else 256)
+        # features: every rank holds a full-size buffer and fills the rows of the images whose conv3-5 it ran
+        # (``x5_sources``); by default everything sits on rank 0
+        self.buf_x5 = symm.alloc("tp_x5", batch * feat * f4)
+        self.x5_sources = [(0, 0, batch)]                  # (rank, first image, end image)
         self.buf_y6 = symm.alloc("tp_y6", batch * hs * f4)
         self.buf_y7 = symm.alloc("tp_y7", batch * hs * f4)
+        # FC7 partial products of this rank for every output shard s: [world][batch][hs]; shard owners pull them
+        self.buf_part = symm.alloc("tp_part", world * batch * hs * f4 if world > 1 else 256)
         self.buf_logits = symm.alloc("tp_logits", batch * 1000 * f4 if rank == 0 else 256)
         self.buf_bar = symm.alloc("tp_bar", (world + 4) * 4)
         self._bar_n = 0
@@ -136,27 +141,32 @@ class TPClassifier:
         return self.buf_x5.tensor((self.B, self.feat))
 
     # -- phases (a real rank runs them back to back with barriers; the emulation interleaves ranks) --
-    def phase_zero(self) -> None:
-        if self.world > 1:
-            self.buf_y7.tensor((self.B, self.hs)).zero_()
+    def phase_fc6(self) -> None:
+        """All-gather fused into the GEMM's loader: the feature rows are read straight out of the buffers of the
+        ranks that produced them (one launch per source: the A operand is one pointer + row stride)."""
+        for src, i0, i1 in self.x5_sources:
+            if i1 > i0:
+                self.fc6.run(self.symm.ptr(src, "tp_x5") + 4 * i0 * self.feat, self.feat, i1 - i0,
+                             self.buf_y6.ptr + 4 * i0 * self.hs, self.hs, self.b6, ext.RELU | ext.ROUND_TF32)
 
-    def phase_fc6(self) -> None:         # all-gather fused: A is rank 0's feature buffer
-        self.fc6.run(self.symm.ptr(0, "tp_x5"), self.feat, self.B, self.buf_y6.ptr, self.hs, self.b6,
-                     ext.RELU | ext.ROUND_TF32)
-
-    def phase_fc7(self) -> None:         # reduce-scatter fused: red.add into the owner's shard
+    def phase_fc7(self) -> None:
+        """Row-parallel FC7: this rank's slice of the hidden vector gives a partial product for EVERY output shard.
+        They are stored locally (plain stores); the shard owners pull and add them in rank order
+        (``phase_fc7_finish``) — a reduce-scatter without atomics, bit-reproducible."""
         if self.world == 1:              # nothing to reduce: bias + ReLU in the GEMM epilogue
             self.fc7[0].run(self.buf_y6.ptr, self.hs, self.B, self.buf_y7.ptr, self.hs, self.b7,
                             ext.RELU | ext.ROUND_TF32)
             return
         for s in range(self.world):
-            self.fc7[s].run(self.buf_y6.ptr, self.hs, self.B, self.symm.ptr(s, "tp_y7"), self.hs, None,
-                            ext.ACCUMULATE)
+            self.fc7[s].run(self.buf_y6.ptr, self.hs, self.B, self.buf_part.ptr + 4 * s * self.B * self.hs, self.hs,
+                            None, 0)
 
     def phase_fc7_finish(self) -> None:
         if self.world == 1:
             return
-        ext.bias_act_(self.buf_y7.ptr, self.b7, self.B, self.hs, self.hs, relu=True)
+        mine = 4 * self.rank * self.B * self.hs
+        ext.peer_reduce_([self.symm.ptr(k, "tp_part") + mine for k in range(self.world)], self.B, self.hs, self.hs,
+                         self.b7, self.buf_y7.ptr, self.hs, ext.RELU | ext.ROUND_TF32)
 
     def phase_fc8(self) -> None:         # pulls every peer's shard; writes its logits columns on rank 0
         c = self.symm.ptr(0, "tp_logits") + 4 * self.out_off[self.rank]
@@ -172,7 +182,7 @@ class TPClassifier:
     def forward(self) -> Optional[torch.Tensor]:
         """Features must already be in rank 0's ``x5_view()``."""
         with torch.cuda.device(self.device):
-            self.phase_zero(); self.barrier()
+            self.barrier()               # every rank's feature rows have landed
             self.phase_fc6()
             self.phase_fc7(); self.barrier()
             self.phase_fc7_finish(); self.barrier()
@@ -209,7 +219,6 @@ class FullAlexNet:
         with torch.cuda.device(self.device):
             self.tp[0].x5_view().copy_(self.features(x))
             T = self.tp
-            for t in T: t.phase_zero()
             for t in T: t.phase_fc6()
             for t in T: t.phase_fc7()
             for t in T: t.phase_fc7_finish()

@@ -41,7 +41,7 @@ class Session:
     def __init__(self, cfg: NetConfig, weights: Blocks12Weights, dist=None, device=None,
                  precision: Optional[str] = None, strategy: str = "halo", scatter: str = "p2p",
                  row_groups=None, gather: str = "rank0", slots: int = 2, halo: str = "push"):
-        if gather not in ("rank0", "host"):
+        if gather not in ("rank0", "host", "local"):    # "local": rows stay on the rank that computed them (no D2H)
             raise ValueError(gather)
         self.cfg = cfg
         self.dist = dist
@@ -58,7 +58,7 @@ class Session:
         self.gather = gather if world > 1 else "rank0"
         self.engine = Blocks12Engine(cfg, weights, self.symm, rank, world, precision=precision,
                                      strategy=strategy, scatter=scatter, row_groups=row_groups,
-                                     gather="local" if self.gather == "host" else "rank0", slots=slots, halo=halo)
+                                     gather="rank0" if self.gather == "rank0" else "local", slots=slots, halo=halo)
         self.symm.commit()
         self.engine.finalize()
         e = self.engine
@@ -82,6 +82,8 @@ class Session:
             if rank == 0:
                 self.h_out = self.shared.views
             self.d2h_bytes = e.out_imgs * e.out_rows * sh.Wp2 * sh.K2 * 4
+        elif self.gather == "local":
+            self.d2h_bytes = 0
         else:
             if rank == 0:
                 self.h_out = [torch.empty(full, dtype=torch.float32, pin_memory=True) for _ in range(slots)]
@@ -131,7 +133,7 @@ class Session:
             with torch.cuda.stream(self.s_compute):
                 out = e.forward_enqueue(i, i)
                 self.ev_compute[i].record(self.s_compute)
-            if out is not None:
+            if out is not None and self.gather != "local":
                 self.s_out.wait_event(self.ev_compute[i])
                 with torch.cuda.stream(self.s_out):
                     if self.shared is not None:      # my rows of my images -> their place in the shared tensor

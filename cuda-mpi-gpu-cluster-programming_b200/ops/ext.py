@@ -28,6 +28,8 @@ def _lib():
         L.b200_splitk_reduce.argtypes = [C.c_void_p, C.c_int, C.c_longlong, C.c_longlong, C.c_int, C.c_void_p,
                                          C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.b200_tc_gemm_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.b200_peer_reduce.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_longlong, C.c_int, C.c_int, C.c_void_p,
+                                       C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.b200_tc_conv_gemm.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 7 + [C.c_void_p, C.c_void_p, C.c_int,
                                                                                  C.c_int, C.c_void_p]
         L.b200_im2col_nhwc.argtypes = [C.c_void_p, C.c_void_p] + [C.c_int] * 7 + [C.c_void_p]
@@ -133,6 +135,17 @@ class TcLinear:
                 self._h = None
         except Exception:
             pass
+
+
+def peer_reduce_(parts, rows: int, cols: int, ld_in: int, bias: Optional[torch.Tensor], out_ptr: int, ld: int,
+                 flags: int = 0) -> None:
+    """out[r, c] = act(sum_k parts[k][r, c] + bias[c]) with the partial matrices addressed by raw (possibly
+    peer-mapped) pointers, added in list order: the deterministic reduce-scatter of the tensor-parallel FC7."""
+    arr = (C.c_void_p * len(parts))(*parts)
+    if bias is not None:
+        flags |= BIAS
+    cu.cu_check(_lib().b200_peer_reduce(arr, len(parts), rows, cols, ld_in, fptr(bias) if bias is not None else None,
+                                        C.c_void_p(out_ptr), ld, flags, cu.current_stream_ptr()), "peer_reduce")
 
 
 def im2col(x: torch.Tensor, F: int, S: int, P: int) -> torch.Tensor:

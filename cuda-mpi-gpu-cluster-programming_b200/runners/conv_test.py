@@ -2,9 +2,13 @@
 sources are missing; recovered behaviour: NCHW direct convolution, prints
 ``Convolution Test Output (first 10 values):``).
 
-Runs the framework's NCHW adaptor (csrc/cuda/conv_nchw.cu) on a deterministic ramp input and, since
-the reference program checks nothing, additionally compares against the CPU oracle and prints
-PASSED/FAILED after the reference's line."""
+On a GPU the convolution runs on the tensor cores by default: an NCHW -> NHWC adaptor (channels zero-padded to a
+multiple of 32) in front of the tcgen05 implicit-GEMM convolution the full network uses
+(``b200_tc_conv_gemm``: TMA-fed weights, im2col rows gathered by the loader, fp32 accumulate in TMEM), and the
+inverse adaptor behind it — the stand-alone driver over the framework's conv kernels that SURVEY K9 asks for.
+``--exact`` keeps the scalar FP32 adaptor (csrc/cuda/conv_nchw.cu, bit-comparable to the oracle to 1e-5).  Since
+the reference program checks nothing, the result is compared against the CPU oracle and PASSED/FAILED is printed
+after the reference's line (TF32 operands: tolerance 4e-3 of the largest output, as in tests/test_gpu_tc.py)."""
 from __future__ import annotations
 
 import argparse
@@ -16,29 +20,49 @@ from ..ops import cpu as cpu_ops
 from ..utils import logfmt as L
 
 
+def conv_nchw_tc(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor, S: int, P: int) -> torch.Tensor:
+    """NCHW convolution on the tcgen05 implicit-GEMM kernel.  ``x`` [N,C,H,W] on the GPU, ``w`` [K,C,F,F] and ``b``
+    [K] on the host.  Channels are zero-padded to a multiple of 32 (the kernel's k-block) in the layout adaptor."""
+    from ..ops import ext
+    N, C, H, W = x.shape
+    K, _, F, _ = w.shape
+    Cp = -(-C // 32) * 32
+    xh = torch.zeros((N, H, W, Cp), dtype=torch.float32, device=x.device)
+    xh[..., :C] = x.permute(0, 2, 3, 1)
+    wp = torch.zeros((K, F, F, Cp), dtype=torch.float32)
+    wp[..., :C] = w.permute(0, 2, 3, 1)
+    lin = ext.TcLinear(wp.reshape(K, F * F * Cp), x.device)
+    y = lin.conv(xh, F, S, P, b.to(x.device).contiguous())            # [N, Ho, Wo, K]
+    return y.permute(0, 3, 1, 2).contiguous()
+
+
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser(prog="conv_test")
     for name, dv in (("n", 1), ("c", 3), ("h", 32), ("w", 32), ("k", 8), ("f", 3), ("s", 1), ("p", 0)):
         ap.add_argument(f"--{name}", type=int, default=dv)
     ap.add_argument("--cpu", action="store_true", help="oracle only (no GPU)")
+    ap.add_argument("--exact", action="store_true", help="GPU: scalar FP32 kernel instead of the tensor-core path")
     ns = ap.parse_args(argv)
     x = (torch.arange(ns.n * ns.c * ns.h * ns.w, dtype=torch.float32).reshape(ns.n, ns.c, ns.h, ns.w) % 17) * 0.1
     w = ((torch.arange(ns.k * ns.c * ns.f * ns.f, dtype=torch.float32).reshape(ns.k, ns.c, ns.f, ns.f) % 7) - 3) * 0.01
     b = torch.zeros(ns.k)
     ref, _ = cpu_ops.conv(x.permute(0, 2, 3, 1).contiguous(), w, b, ns.f, ns.s, ns.p)
     ref = ref.permute(0, 3, 1, 2).contiguous()
+    tol = 1e-5
     if ns.cpu or not torch.cuda.is_available():
         out, how = ref, "cpu-oracle"
-    else:
+    elif ns.exact:
         from ..ops import cuda as cu
-        out, how = cu.conv_nchw(x.cuda(), w.cuda(), b.cuda(), ns.s, ns.p).cpu(), "gpu"
+        out, how = cu.conv_nchw(x.cuda(), w.cuda(), b.cuda(), ns.s, ns.p).cpu(), "gpu-fp32-simt"
+    else:
+        out, how, tol = conv_nchw_tc(x.cuda(), w, b, ns.s, ns.p).cpu(), "gpu-tf32-tcgen05", 4e-3
     flat = out.reshape(-1)
     L.emit("Convolution Test Output (first 10 values): " + " ".join(L.cxx_float(v) for v in flat[:10].tolist()))
     err = (out - ref).abs().max().item() / max(ref.abs().max().item(), 1e-30)
     L.emit(f"Output Shape (NCHW): {'x'.join(str(s) for s in out.shape)}")
     L.emit(f"max_rel_err_vs_cpu_oracle={L.cxx_float(err)} backend={how}")
-    L.emit("Convolution Test: " + ("PASSED" if err < 1e-5 else "FAILED"))
-    return 0 if err < 1e-5 else 1
+    L.emit("Convolution Test: " + ("PASSED" if err < tol else "FAILED"))
+    return 0 if err < tol else 1
 
 
 if __name__ == "__main__":

@@ -2,17 +2,17 @@
 
     mpirun -np N python -m b200cnn.runners.full --batch 256
 
-Blocks 1-2 run row-decomposed across the N GPUs with the fused peer-memory kernels (exactly as V4/V5).
-Conv3-5 + Pool5 work on 13x13 maps, too small to split by rows, so they are sharded by BATCH: after a
-device-side barrier every rank copies its images of the gathered LRN2 tensor out of rank 0's buffer over
-NVLink (one pass; the implicit-GEMM loader would otherwise re-read each pixel nine times over the link),
-runs the three implicit-GEMM convolutions and the pool locally and stores its feature rows straight into rank
-0's FC input buffer (B200_FULL_CONV_SHARD=rank0: rank 0 does all of it, the round-1 baseline).  FC6-8 run
-tensor-parallel over all N GPUs through peer memory (models/alexnet_full.py: TPClassifier).
+Blocks 1-2 run decomposed across the N GPUs (rows, or ``--row-groups``: rows x batch) with the fused peer-memory
+kernels, every rank KEEPING the rows it computed (gather="local").  Conv3-5 + Pool5 work on 13x13 maps, too small to
+split by rows, so they are sharded by BATCH inside each group of ranks that split one image set: after a device-side
+barrier a rank collects, for its share of the images, the row blocks the other members computed (one pass of peer
+reads over NVLink), runs the three implicit-GEMM convolutions and the pool locally and keeps its feature rows.
+Nothing is funnelled through rank 0: FC6 reads every rank's feature rows from where they are (all-gather fused into
+the GEMM loader), FC7's partial products are added by the shard owners in rank order (deterministic reduce-scatter
+by pull), FC8 writes its logits columns into rank 0's buffer (models/alexnet_full.py: TPClassifier).
 Prints V4-style lines; the "values" are the first 10 class probabilities of image 0."""
 from __future__ import annotations
 
-import os
 import sys
 import time
 
@@ -48,47 +48,61 @@ def main(argv=None) -> int:
         fail(bdist.env_rank_world()[0], "the full-network runner needs one GPU per rank")
     ctx = bdist.init()
     x, w12 = make_problem(cfg)
+    from .v4 import _row_groups
+    from ..parallel.planner import split_rows
     sess = Session(cfg, w12, dist=ctx if ctx.world > 1 else None, device=ctx.device, precision=cfg.precision,
-                   strategy=ns.strategy, scatter="sharded")
-    sh = sess.engine.sh
+                   strategy=ns.strategy, scatter="sharded", row_groups=_row_groups(ns), gather="local")
+    e = sess.engine
+    sh, plan, rp = e.sh, e.plan, e.rp
     feat = ((sh.Hp2 - 3) // 2 + 1) * ((sh.Wp2 - 3) // 2 + 1) * 256
     w = make_full_weights(w12, seed=cfg.seed, feat=feat)
     tp = TPClassifier(w, sess.symm, ctx.rank, ctx.world, cfg.batch, feat)
     sess.symm.commit()
-    shard = ctx.world > 1 and os.environ.get("B200_FULL_CONV_SHARD", "batch") == "batch"
-    b0, b1 = batch_shard(cfg.batch, ctx.rank, ctx.world) if shard else (0, cfg.batch if ctx.rank == 0 else 0)
+    # Conv3-5 + pool5 by batch: the ranks that split the rows of one image set share its images out among themselves;
+    # a rank collects, for ITS images, the row blocks the other members computed (peer reads of their output slabs)
+    def share_of(q):
+        members = [m for m in plan.ranks if m.batch_group == q.batch_group]
+        lo, hi = split_rows(q.n_images, len(members))[q.row_group]
+        return q.images[0] + lo, q.images[0] + hi
+    b0, b1 = share_of(rp)
+    tp.x5_sources = [(q.rank,) + share_of(q) for q in plan.ranks]
+    members = [m for m in plan.ranks if m.batch_group == rp.batch_group and m.out_rows[1] > m.out_rows[0]]
     convs = [ConvGemm(w.w3, w.b3, ctx.device, 1), ConvGemm(w.w4, w.b4, ctx.device, 1),
              ConvGemm(w.w5, w.b5, ctx.device, 1)] if b1 > b0 else None
-    if shard:
-        with torch.cuda.device(ctx.device):
-            # rank 0's gathered LRN2 tensor and FC input, addressed through their peer mappings
-            y_all = DevBuf(sess.symm.ptr(0, "out0"), cfg.batch * sh.Hp2 * sh.Wp2 * 256 * 4,
-                           ctx.device).tensor((cfg.batch, sh.Hp2, sh.Wp2, 256))
-            x5_all = DevBuf(sess.symm.ptr(0, "tp_x5"), cfg.batch * feat * 4, ctx.device).tensor((cfg.batch, feat))
-            y_loc = torch.empty((max(b1 - b0, 1), sh.Hp2, sh.Wp2, 256), dtype=torch.float32, device=ctx.device)
-    lo, hi = sess.input_rows
-    xin = x[:, lo:hi].contiguous().pin_memory() if hi > lo else None
+    row_bytes = sh.Wp2 * 256 * 4
+    with torch.cuda.device(ctx.device):
+        z_in = torch.empty((max(b1 - b0, 1), sh.Hp2, sh.Wp2, 256), dtype=torch.float32, device=ctx.device)
+        parts = []                           # (rows, view of the member's output slab restricted to my images)
+        for m in members:
+            r0, r1 = m.out_rows
+            if ctx.world == 1:
+                break
+            slab = DevBuf(sess.symm.ptr(m.rank, "out0"), m.n_images * (r1 - r0) * row_bytes,
+                          ctx.device).tensor((m.n_images, r1 - r0, sh.Wp2, 256))
+            parts.append((r0, r1, slab[b0 - m.images[0]:b1 - m.images[0]]))
+        x5_mine = tp.x5_view()[b0:b1]
+    xin = sess.my_input(x)
+    xin = xin.contiguous().pin_memory() if xin is not None else None
 
     def load():                              # this rank's input rows: pinned host -> resident device buffer
         if xin is not None:
-            sess.engine.h2d(0, xin)
+            e.h2d(0, xin)
 
     def compute():
-        e = sess.engine
         y = e.forward_enqueue(0, 0)
-        if shard:
-            tp.barrier()                     # rank 0 is past its completion wait: the gathered tensor is whole
-            if b1 > b0:
-                z = y_loc[:b1 - b0]
-                z.copy_(y_all[b0:b1])
-                for c in convs:
-                    z = c(z)
-                x5_all[b0:b1].copy_(ext.maxpool(z, 3, 2).reshape(b1 - b0, -1))
-        elif ctx.rank == 0:
+        if ctx.world > 1:
+            tp.barrier()                     # every member's block 2 is finished: its output slab is whole
+        if b1 > b0:
+            if ctx.world > 1:
+                for r0, r1, src in parts:
+                    z_in[:b1 - b0, r0:r1].copy_(src)
+                z = z_in[:b1 - b0]
+            else:
+                z = y
             for c in convs:
-                y = c(y)
-            tp.x5_view().copy_(ext.maxpool(y, 3, 2).reshape(cfg.batch, -1))
-        return tp.forward()              # opens with a barrier: every rank's feature rows have landed
+                z = c(z)
+            x5_mine.copy_(ext.maxpool(z, 3, 2).reshape(b1 - b0, -1))
+        return tp.forward()                  # opens with a barrier: every rank's feature rows are in place
 
     def timed(fn, iters):
         torch.cuda.synchronize(ctx.device); ctx.barrier()
@@ -117,7 +131,7 @@ def main(argv=None) -> int:
         _, ems = timed(step, ns.iters)                   # plus the pinned H2D of the inputs every step
         kv = dict(device_forward_ms_warm=dms, images_per_s_warm=cfg.batch / (dms / 1e3),
                   with_h2d_forward_ms_warm=ems, with_h2d_images_per_s_warm=cfg.batch / (ems / 1e3))
-    sess.engine.check_status()
+    e.check_status()
     if ctx.rank == 0:
         p = probs.cpu()
         for line in L.v4_shape_values(cfg.batch, 1, 1000, p.reshape(-1)[:10].tolist()):
@@ -125,7 +139,7 @@ def main(argv=None) -> int:
         L.emit(L.v4_time(ms, "Full (spatial conv + TP FC)"))
         for line in L.extras(fnv=fnv1a64(p), wall_ms=ms, np=ctx.world, batch=cfg.batch,
                              prob_row_sum=float(p[0].sum()), argmax0=int(p[0].argmax()),
-                             conv_shard="batch" if shard else "rank0", **kv):
+                             decomposition=f"{plan.row_groups}x{plan.batch_groups}", **kv):
             L.emit(line)
     ctx.finalize()
     return 0

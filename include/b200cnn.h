@@ -184,7 +184,8 @@ int b200_tc_block(void* handle, const float* bias, float* out, const b200_block_
 int b200_tc_block_tiles(const b200_block_geom* g);
 int b200_tc_block_tiles_rows(const b200_block_geom* g, int lo, int hi);
 /* Process-wide kernel choice (default: environment B200_TC_CONV2 / B200_TC_CONV1 at first use, else auto):
- * key "conv2" = auto|single|db|pair (single-buffered, double-buffered TMEM, tcgen05 CTA pair),
+ * key "conv2" = auto|single|db|pair|cs (single-buffered, double-buffered TMEM, tcgen05 CTA pair splitting the
+ * pixels, CTA pair splitting the channels),
  * key "conv1" = auto|cpasync (pixel operand by TMA when eligible, or always the cp.async loader).
  * All choices produce bit-identical outputs; they differ in speed only. */
 int b200_tc_set_policy(const char* key, const char* value);
@@ -237,6 +238,11 @@ int b200_tc_gemm_splitk(void* handle, const float* A, int lda, int M, const floa
 int b200_splitk_reduce(const float* ws, int ksplit, long long stride, long long rows, int cols,
                        const float* bias, float* out, int ld, int flags, void* stream);
 int b200_tc_gemm_info(void* handle, int* nkb, int* bn);
+/* Reduce-scatter by pull: out[r][c] = act(sum_k parts[k][r*ld_in + c] + bias[c]), k = 0..n-1 in order (n <= 16).
+ * parts[k] may be peer-mapped pointers (every rank's partial products of the shard this rank owns): deterministic,
+ * no atomics, no zeroed accumulator.  flags as b200_tc_gemm (1 ReLU, 2 round to TF32, 8 bias). */
+int b200_peer_reduce(const float* const* parts, int n, long long rows, int cols, int ld_in, const float* bias,
+                     float* out, int ld, int flags, void* stream);
 /* Convolution as an implicit GEMM on the same kernel: x is NHWC [N][H][W][C] with C % 32 == 0 (may be a
  * peer pointer); the handle holds [K_out][F*F*C] weights in (fy, fx, c) order; out is [N*Ho*Wo][ldc].
  * The producer warps gather the im2col rows on the fly (zero fill outside the image); no col buffer. */

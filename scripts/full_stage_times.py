@@ -57,7 +57,7 @@ def main():
     t.x5_view().copy_(feat)
 
     def fc():
-        t.phase_zero(); t.phase_fc6(); t.phase_fc7(); t.phase_fc7_finish(); t.phase_fc8(); t.phase_softmax()
+        t.phase_fc6(); t.phase_fc7(); t.phase_fc7_finish(); t.phase_fc8(); t.phase_softmax()
     print(f"fc6-8 + softmax {timed(fc, reps):8.1f} us")
     print(f"whole forward (default path) {timed(lambda: net.forward(xd), reps):9.1f} us")
 

@@ -1,5 +1,6 @@
-"""The three conv2-type kernels of csrc/cuda/tc_block.cu — single-buffered (one 256-pixel tile fills TMEM),
-double-buffered (128-pixel tiles, own epilogue warps) and the tcgen05 CTA pair (cta_group::2, TMA-fed operands) —
+"""The four conv2-type kernels of csrc/cuda/tc_block.cu — single-buffered (one 256-pixel tile fills TMEM),
+double-buffered (128-pixel tiles, own epilogue warps), the tcgen05 CTA pair that splits the pixels and the one that
+splits the channels (cta_group::2, TMA-fed operands, LRN halo channels over DSMEM) —
 and the two conv1 loaders (pixel operand by TMA / by cp.async) accumulate every output in the same K order, so all
 choices must be bit-identical.  A mismatch fails."""
 import pytest
@@ -33,7 +34,7 @@ def test_conv2_kernels_bit_identical(batch, hw):
     x, w = make_problem(cfg)
     ref, ref2 = _forward(cfg, x, w, conv2="single")
     assert torch.equal(ref, ref2)
-    for kind in ("db", "pair", "auto"):
+    for kind in ("db", "pair", "cs", "auto"):
         y, y2 = _forward(cfg, x, w, conv2=kind)
         assert torch.equal(y, ref), f"conv2={kind} differs: max |diff| {float((y - ref).abs().max()):.3e}"
         assert torch.equal(y2, ref), f"conv2={kind}: second forward differs"
