@@ -39,7 +39,7 @@ def build_shim(cuda: bool):
     cmd = ["gcc", "-O2", "-fPIC", "-shared", "-o", out, src, "-lpthread"]
     if cuda and os.path.exists("/usr/local/cuda/include/cuda_runtime.h"):
         cmd = ["gcc", "-O2", "-fPIC", "-shared", "-DB200_MPISHIM_CUDA", "-I/usr/local/cuda/include", "-o", out,
-               src, "-L/usr/local/cuda/lib64", "-Wl,-rpath,/usr/local/cuda/lib64", "-lcudart", "-lpthread"]
+               src, "-L/usr/local/cuda/lib64", "-Wl,-rpath,/usr/local/cuda/lib64", "-lcudart", "-lpthread", "-ldl"]
     subprocess.check_call(cmd)
     return out
 

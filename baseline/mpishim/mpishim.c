@@ -16,6 +16,7 @@
 
 #ifdef B200_MPISHIM_CUDA
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 #endif
 
 static int g_rank = 0, g_size = 1, g_init = 0;
@@ -26,6 +27,7 @@ static int* g_kfd;   /* g_kfd[s]: my own write end of s -> me, never written: ke
                         while the real writer has not opened it yet (a rank that finished MPI_Init early
                         would otherwise see "no writer" = end of file in its first receive) */
 static pthread_mutex_t* g_wlock;
+static pthread_mutex_t* g_rlock;   /* per source: one reader at a time (send threads read their ACKs from the same pipe) */
 
 typedef struct pend { int tag; int64_t n; char* data; struct pend* next; } pend;
 static pend** g_pending;   /* per source: messages read while looking for another tag */
@@ -90,8 +92,67 @@ static void* stage_out(const void* buf, int64_t bytes) {   /* device -> host bou
 #endif
 }
 
+/* ---- device-to-device transport ("CUDA-aware" path of the V5 reconstruction) --------------------------------
+ * A device send buffer is not copied through the pipe: the sender ships a CUDA IPC handle of the allocation that
+ * holds it (+ offset, length) and waits for an ACK; the receiver maps the allocation once (cached) and copies
+ * straight from the sender's GPU into its own buffer with cudaMemcpy (peer copy over NVLink when the destination is
+ * device memory).  The base of the allocation comes from the driver's cuMemGetAddressRange, looked up with dlopen so
+ * the shim still loads on machines without a driver.  Anything that cannot take this path (no driver, host buffers)
+ * falls back to the pinned bounce buffer above. */
+#define TAG_ACK 0x7fff0003
+static void raw_recv(void* buf, int64_t bytes, int src, int tag);
+#ifdef B200_MPISHIM_CUDA
+typedef struct { cudaIpcMemHandle_t h; uint64_t off; uint64_t bytes; } ipc_msg;
+typedef int (*range_fn)(unsigned long long*, size_t*, unsigned long long);
+static int dev_range(const void* p, void** base, size_t* size) {
+    static range_fn fn = NULL; static int tried = 0;
+    if (!tried) {
+        tried = 1;
+        void* lib = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL);
+        if (lib) fn = (range_fn)dlsym(lib, "cuMemGetAddressRange_v2");
+    }
+    unsigned long long b = 0; size_t n = 0;
+    if (!fn || fn(&b, &n, (unsigned long long)(uintptr_t)p) != 0) return 0;
+    *base = (void*)(uintptr_t)b; *size = n; return 1;
+}
+static struct { cudaIpcMemHandle_t h; void* ptr; } g_ipc[64];
+static int g_nipc = 0;
+static pthread_mutex_t g_ipc_mu = PTHREAD_MUTEX_INITIALIZER;
+static void* ipc_map(const cudaIpcMemHandle_t* h) {
+    pthread_mutex_lock(&g_ipc_mu);
+    for (int i = 0; i < g_nipc; ++i)
+        if (!memcmp(&g_ipc[i].h, h, sizeof *h)) { void* p = g_ipc[i].ptr; pthread_mutex_unlock(&g_ipc_mu); return p; }
+    void* p = NULL;
+    if (cudaIpcOpenMemHandle(&p, *h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+        fprintf(stderr, "[Rank %d] mpishim: cudaIpcOpenMemHandle failed: %s\n", g_rank, cudaGetErrorString(cudaGetLastError()));
+        exit(74);
+    }
+    if (g_nipc < 64) { g_ipc[g_nipc].h = *h; g_ipc[g_nipc].ptr = p; ++g_nipc; }
+    pthread_mutex_unlock(&g_ipc_mu);
+    return p;
+}
+#endif
+
 static void raw_send(const void* buf, int64_t bytes, int dest, int tag) {
     void* bounce = NULL;
+#ifdef B200_MPISHIM_CUDA
+    if (bytes > 0 && g_size > 1 && is_device_ptr(buf)) {
+        void* base = NULL; size_t size = 0; ipc_msg m;
+        if (dev_range(buf, &base, &size) && cudaIpcGetMemHandle(&m.h, base) == cudaSuccess) {
+            m.off = (uint64_t)((const char*)buf - (const char*)base); m.bytes = (uint64_t)bytes;
+            int32_t hdr_tag = tag; int64_t hdr_n = -(int64_t)sizeof m;       /* negative length = IPC descriptor */
+            cudaDeviceSynchronize();                                         /* the data must be there before the peer reads it */
+            pthread_mutex_lock(&g_wlock[dest]);
+            full_write(g_wfd[dest], &hdr_tag, 4);
+            full_write(g_wfd[dest], &hdr_n, 8);
+            full_write(g_wfd[dest], &m, sizeof m);
+            pthread_mutex_unlock(&g_wlock[dest]);
+            raw_recv(NULL, 0, dest, TAG_ACK);                                /* buffer reusable once the peer has copied */
+            return;
+        }
+        (void)cudaGetLastError();
+    }
+#endif
     if (bytes > 0 && is_device_ptr(buf)) { bounce = stage_out(buf, bytes); buf = bounce; }
     int32_t hdr_tag = tag; int64_t hdr_n = bytes;
     pthread_mutex_lock(&g_wlock[dest]);
@@ -113,14 +174,28 @@ static void deliver(void* buf, int64_t want, const char* data, int64_t n) {
     memcpy(buf, data, (size_t)n);
 }
 
+#define TAG_MATCH(want, got) ((want) == (got) || ((want) == MPI_ANY_TAG && (got) != TAG_ACK))
+
+#ifdef B200_MPISHIM_CUDA
+static void send_ack(int dest) {
+    int32_t hdr_tag = TAG_ACK; int64_t hdr_n = 0;
+    pthread_mutex_lock(&g_wlock[dest]);
+    full_write(g_wfd[dest], &hdr_tag, 4);
+    full_write(g_wfd[dest], &hdr_n, 8);
+    pthread_mutex_unlock(&g_wlock[dest]);
+}
+#endif
+
 static void raw_recv(void* buf, int64_t bytes, int src, int tag) {
+    pthread_mutex_lock(&g_rlock[src]);
     /* 1. something already buffered from this source with this tag? */
     pend** pp = &g_pending[src];
     while (*pp) {
-        if (tag == MPI_ANY_TAG || (*pp)->tag == tag) {
+        if (TAG_MATCH(tag, (*pp)->tag)) {
             pend* m = *pp; *pp = m->next;
             deliver(buf, bytes, m->data, m->n);
             free(m->data); free(m);
+            pthread_mutex_unlock(&g_rlock[src]);
             return;
         }
         pp = &(*pp)->next;
@@ -130,9 +205,32 @@ static void raw_recv(void* buf, int64_t bytes, int src, int tag) {
         int32_t t; int64_t n;
         full_read(g_rfd[src], &t, 4);
         full_read(g_rfd[src], &n, 8);
-        char* data = (char*)malloc((size_t)(n > 0 ? n : 1));
-        full_read(g_rfd[src], data, n);
-        if (tag == MPI_ANY_TAG || t == tag) { deliver(buf, bytes, data, n); free(data); return; }
+        char* data = NULL;
+#ifdef B200_MPISHIM_CUDA
+        if (n < 0) {                     /* IPC descriptor: the payload stays on the sender's GPU until we copy it */
+            ipc_msg m;
+            full_read(g_rfd[src], &m, sizeof m);
+            const char* peer = (const char*)ipc_map(&m.h) + m.off;
+            n = (int64_t)m.bytes;
+            if (TAG_MATCH(tag, t)) {
+                if (n > bytes) { fprintf(stderr, "[Rank %d] mpishim: message truncated (%lld > %lld)\n", g_rank,
+                                         (long long)n, (long long)bytes); exit(73); }
+                if (cudaMemcpy(buf, peer, (size_t)n, cudaMemcpyDefault) != cudaSuccess) die("cudaMemcpy (peer)");
+                send_ack(src);
+                pthread_mutex_unlock(&g_rlock[src]);
+                return;
+            }
+            /* not the message we are looking for: take a host copy now, so its sender is released at once */
+            data = (char*)malloc((size_t)(n > 0 ? n : 1));
+            if (cudaMemcpy(data, peer, (size_t)n, cudaMemcpyDeviceToHost) != cudaSuccess) die("cudaMemcpy (peer->host)");
+            send_ack(src);
+        } else
+#endif
+        {
+            data = (char*)malloc((size_t)(n > 0 ? n : 1));
+            full_read(g_rfd[src], data, n);
+            if (TAG_MATCH(tag, t)) { deliver(buf, bytes, data, n); free(data); pthread_mutex_unlock(&g_rlock[src]); return; }
+        }
         pend* m = (pend*)malloc(sizeof(pend));
         m->tag = t; m->n = n; m->data = data; m->next = NULL;
         pend** q = &g_pending[src];
@@ -154,6 +252,8 @@ int MPI_Init(int* argc, char*** argv) {
     g_wfd = (int*)calloc(g_size, sizeof(int)); g_rfd = (int*)calloc(g_size, sizeof(int));
     g_kfd = (int*)calloc(g_size, sizeof(int));
     g_wlock = (pthread_mutex_t*)calloc(g_size, sizeof(pthread_mutex_t));
+    g_rlock = (pthread_mutex_t*)calloc(g_size, sizeof(pthread_mutex_t));
+    for (int i = 0; i < g_size; ++i) pthread_mutex_init(&g_rlock[i], NULL);
     g_pending = (pend**)calloc(g_size, sizeof(pend*));
     for (int i = 0; i < g_size; ++i) { pthread_mutex_init(&g_wlock[i], NULL); g_wfd[i] = g_rfd[i] = g_kfd[i] = -1; }
     if (g_size > 1) {

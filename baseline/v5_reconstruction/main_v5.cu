@@ -6,7 +6,8 @@
 // and keeps V4's decomposition (row scatter, F/2 input halo, heuristic trim — including its lossy
 // output), but every MPI buffer is a device pointer: no std::vector staging, no
 // vector::insert, no D2H/H2D around the exchange.  "CUDA-aware MPI" is baseline/mpishim built with
-// -DB200_MPISHIM_CUDA (device pointers are detected and bounced through pinned memory).
+// -DB200_MPISHIM_CUDA: a device send buffer travels as a CUDA IPC handle and the receiver copies it straight from the
+// sender's GPU into its own buffer (cudaMemcpy peer copy over NVLink) — a real device-to-device transport.
 #include <mpi.h>
 #include <cuda_runtime.h>
 
