@@ -1246,7 +1246,7 @@ tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_co
 // columns, +bias, ReLU into pbuf[pooled pixel][channel].  LRN's window of 5 channels crosses the CTA boundary at channels
 // 127|128: each CTA pushes its two edge channels into the partner's halo buffer (DSMEM stores) and the two epilogues meet
 // on a cluster-scope mbarrier once per tile; then LRN and 512 B-per-pixel stores of the CTA's channel half.
-// Every TMA load here reads this GPU's memory only (fill_cs refuses anything else) and none is a multicast load.
+// Every tensor map here covers this GPU's memory only (fill_cs refuses anything else).
 //   warp 0: TMA (both CTAs)   warp 1: TMEM owner (both), MMA issuer (leader)   warps 2-5: epilogue
 constexpr int kCsThreads = 192;
 constexpr int kCsEpiWarp0 = 2;
@@ -1317,15 +1317,21 @@ tc_block_cs_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_const
 
     if (warp == 0) {
         // ======================================= TMA issuer ==============================
+        // Pixel boxes run ONE box ahead of the weight stream (a box serves F k-blocks and takes longer to land than a
+        // weight stage): box j+1 — the next tile's first box after the last one — is requested before the weights of
+        // box j.
         int ws = 0, ps = 0;
         uint32_t wphase = 0, pphase = 0;
-        for (long long w = pair_id; w < p.total_tiles; w += npairs) {
-            const int n = (int)(w / tiles_per_img);
+        const int boxes = p.nkb / g.F;                          // (channel chunk, fx) pairs per tile
+        int n = 0, cc0 = 0, y0 = 0;
+        auto open_tile = [&](long long w) {                     // decode + wait for pushed halo rows of the tile
+            n = (int)(w / tiles_per_img);
             const int rem = (int)(w - (long long)n * tiles_per_img);
             const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
-            const int cr0 = 2 * (g.p0 + tr_i * p.PR), cc0 = 2 * (tc_i * p.PC);
+            const int cr0 = 2 * (g.p0 + tr_i * p.PR);
+            cc0 = 2 * (tc_i * p.PC);
             const int ir0 = cr0 - g.P;                          // first input row of the tile (stride 1)
-            if (p.any_flag) {                                   // pushed halo rows of image n have landed?
+            if (p.any_flag) {
                 if (lane == 0) {
                     const int IRT = p.TR - 1 + g.F;
                     for (int s = 0; s < g.nseg; ++s)
@@ -1336,28 +1342,34 @@ tc_block_cs_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_const
                 }
                 __syncwarp();
             }
-            const int y0 = ir0 - g.seg[0].base + (int)rank * cp.HR;   // slab-relative first row of this CTA's box
-            int fy = 0, fx = 0, cch = 0;
-            for (int kb = 0; kb < p.nkb; ++kb) {
-                if (fy == 0) {                                  // a new (channel chunk, fx): one pixel box for F k-blocks
-                    mbar_wait(pempty_bar + 8 * ps, pphase ^ 1);
+            y0 = ir0 - g.seg[0].base + (int)rank * cp.HR;       // slab-relative first row of this CTA's boxes
+        };
+        auto issue_box = [&](int j) {                           // box j of the open tile: chunk j / F, filter column j % F
+            mbar_wait(pempty_bar + 8 * ps, pphase ^ 1);
+            if (lane == 0) {
+                const uint32_t fb = pfull_bar + 8 * ps;
+                if (rank == 0) mbar_arrive_expect_tx(fb, 2u * cp.pstage_bytes);
+                tma2_load_4d(base + ps * cp.pstage_bytes, &tmapX, (j / g.F) * kBlockK, cc0 + (j % g.F) - g.P, y0, n, fb);
+            }
+            __syncwarp();
+            if (++ps == kCsPStages) { ps = 0; pphase ^= 1; }
+        };
+        if (pair_id < p.total_tiles) { open_tile(pair_id); issue_box(0); }
+        for (long long w = pair_id; w < p.total_tiles; w += npairs) {
+            for (int j = 0; j < boxes; ++j) {
+                if (j + 1 < boxes) issue_box(j + 1);
+                else if (w + npairs < p.total_tiles) { open_tile(w + npairs); issue_box(0); }
+                for (int fy = 0; fy < g.F; ++fy) {
+                    const int kb = j * g.F + fy;
+                    mbar_wait(wempty_bar + 8 * ws, wphase ^ 1);
                     if (lane == 0) {
-                        const uint32_t fb = pfull_bar + 8 * ps;
-                        if (rank == 0) mbar_arrive_expect_tx(fb, 2u * cp.pstage_bytes);
-                        tma2_load_4d(base + ps * cp.pstage_bytes, &tmapX, cch * kBlockK, cc0 + fx - g.P, y0, n, fb);
+                        const uint32_t fb = wfull_bar + 8 * ws;
+                        if (rank == 0) mbar_arrive_expect_tx(fb, 2u * (uint32_t)kCsWStageBytes);
+                        tma2_load_2d(base + w_off + ws * kCsWStageBytes, &tmapW, kb * kBlockK, (int)rank * 128, fb);
                     }
                     __syncwarp();
-                    if (++ps == kCsPStages) { ps = 0; pphase ^= 1; }
+                    if (++ws == kCsWStages) { ws = 0; wphase ^= 1; }
                 }
-                mbar_wait(wempty_bar + 8 * ws, wphase ^ 1);
-                if (lane == 0) {
-                    const uint32_t fb = wfull_bar + 8 * ws;
-                    if (rank == 0) mbar_arrive_expect_tx(fb, 2u * (uint32_t)kCsWStageBytes);
-                    tma2_load_2d(base + w_off + ws * kCsWStageBytes, &tmapW, kb * kBlockK, (int)rank * 128, fb);
-                }
-                __syncwarp();
-                if (++fy == g.F) { fy = 0; if (++fx == g.F) { fx = 0; ++cch; } }
-                if (++ws == kCsWStages) { ws = 0; wphase ^= 1; }
             }
         }
     } else if (warp == 1) {
