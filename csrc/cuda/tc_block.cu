@@ -207,9 +207,8 @@ __device__ __forceinline__ void epilogue_tables(const TcParams& p, int2* ptab, f
 // kPatch = false ("vec" mode, C % 32 == 0: conv2..5): a k-block is 32 channels of one filter tap;
 //   every A row is 128 contiguous bytes of the activation -> cp.async 16 B straight into the
 //   swizzled stage, completion tracked by the stage's mbarrier (cp.async.mbarrier.arrive.noinc).
-//   K order (channel-chunk, fx, fy, c%32), fy fastest: consecutive k-blocks of a tile are the same pixel box moved
-//   down by one input row, which is what lets the channel-split pair kernel keep ONE box of HR+F-1 rows in shared
-//   memory for F k-blocks; every vec-mode kernel uses this order, so they all stay bit-identical.
+//   K order (channel-chunk, fy, fx, c%32): consecutive k-blocks re-read neighbouring pixels, so
+//   the small L1 that is left catches most of the im2col re-reads (local and NVLink-mapped rows).
 // kPatch = true  (conv1, C = 3): the input patch of the tile is staged ONCE in shared memory (one
 //   pull over NVLink in p2p-scatter mode instead of (F/S)^2 re-reads), then expanded to A with
 //   LDS.128 -> cvt.rna.tf32 -> STS.128.  K order (fy, [fx,c] padded to a multiple of 4): for a fixed
@@ -352,7 +351,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
             const char* rp8[8];                                 // vec: row pointers for the current fy
             uint32_t vm[8];                                     // vec: xmask, or 0 when the row is padding
             for (int kb = 0; kb < ((p.dbg & 8) ? 0 : p.nkb); ++kb) {
-                if (!kPatch) {                                  // the filter ROW changes with every k-block
+                if (!kPatch && fx == 0) {
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
                         rp8[i] = reinterpret_cast<const char*>(rowtab[rsel[i] + fy]);
@@ -390,7 +389,7 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
                     cp_async_mbar_arrive_noinc(fb);            // arrives when this thread's copies land
                 }
                 if (!kPatch) {
-                    if (++fy == g.F) { fy = 0; if (++fx == g.F) { fx = 0; ++cch; } }
+                    if (++fx == g.F) { fx = 0; if (++fy == g.F) { fy = 0; ++cch; } }
                 }
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
@@ -958,7 +957,7 @@ tc_block_db_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_const
             const char* rp4[4];
             uint32_t vm[4];
             for (int kb = 0; kb < p.nkb; ++kb) {
-                {                                               // the filter ROW changes with every k-block
+                if (fx == 0) {
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         rp4[i] = reinterpret_cast<const char*>(rowtab[rsel[i] + fy]);
@@ -974,7 +973,7 @@ tc_block_db_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_const
                     cp_async16(a_dst + i * 4096u, rp4[i] + (cbyte[i] + off), nb);
                 }
                 cp_async_mbar_arrive_noinc(full_bar + 8 * stage);
-                if (++fy == g.F) { fy = 0; if (++fx == g.F) { fx = 0; ++cch; } }
+                if (++fx == g.F) { fx = 0; if (++fy == g.F) { fy = 0; ++cch; } }
                 if (++stage == NS) { stage = 0; phase ^= 1; }
             }
         }
@@ -1158,7 +1157,7 @@ tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_co
                                  (int)rank * (N / 2), fb);
                 }
                 __syncwarp();
-                if (++fy == g.F) { fy = 0; if (++fx == g.F) { fx = 0; ++cch; } }
+                if (++fx == g.F) { fx = 0; if (++fy == g.F) { fy = 0; ++cch; } }
                 if (++stage == NS) { stage = 0; phase ^= 1; }
             }
         }
@@ -1233,15 +1232,11 @@ tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_co
 // GPUs) needs 5 tiles and 32 images do not fit one round of 74 pairs.  Here the pair shares ONE tile of up to 256 pixel
 // slots and splits the CHANNELS instead — the tcgen05 pair issues D[256 channels x 256 pixels] = W[256 x K] * X^T:
 //   A operand = weights, M = 256: CTA r stages (and gets the accumulator rows of) channels 128r .. 128r+127
-//   B operand = im2col pixels, N = 256: CTA r supplies the pixel rows [r*HR, (r+1)*HR) of the tile, 16 slots per row
+//   B operand = im2col pixels, N = 256: CTA r stages the pixel rows [r*HR, (r+1)*HR) of the tile (HR x TC <= 128 slots,
+//               one TMA box per filter tap and 32 input channels, zero fill outside the slab)
 //   D in each CTA's TMEM = its 128 channels (lanes) x 256 pixel slots (columns), double buffered (2 x 256 columns).
-// A tile is (2PR+1) x (2PC+1) conv pixels = PR x PC pooled outputs (PR, PC <= 7: 15 x 15 pixels in 2 x 8 rows of 16
-// slots): the half-image of a rank at 8 GPUs is 2 tiles, a whole 27 x 27 image 4.
-// Pixel operand reuse.  With K ordered (channel chunk, fx, fy) the F k-blocks of one (chunk, fx) are the same pixel box
-// moved down one input row at a time.  So ONE TMA box of HR+F-1 rows x 16 pixels x 32 channels is loaded per (chunk, fx)
-// and the F MMAs steps read it through shared-memory descriptors that start fy rows (fy x 2 KB: whole 1 KB swizzle
-// atoms, because a row is 16 slots) further down: the pixel traffic into the SM drops F-fold minus the F-1 extra rows
-// (12 instead of 40 rows per 5 k-blocks for conv2), which is what the pixel-split pair kernel was bound by.
+// A tile is (2PR+1) x (2PC+1) conv pixels = PR x PC pooled outputs (8 x 15 + 7 x 15 pixels for 7 x 7 pooled): the whole
+// half-image of a rank is 2 tiles, a whole 27 x 27 image 4.
 // Epilogue (4 warps, lane = channel): three conv rows at a time from TMEM through a per-warp strip, max-pool along the
 // columns, +bias, ReLU into pbuf[pooled pixel][channel].  LRN's window of 5 channels crosses the CTA boundary at channels
 // 127|128: each CTA pushes its two edge channels into the partner's halo buffer (DSMEM stores) and the two epilogues meet
@@ -1250,18 +1245,17 @@ tc_block_pair_kernel(const __grid_constant__ CUtensorMap tmapBh, const __grid_co
 //   warp 0: TMA (both CTAs)   warp 1: TMEM owner (both), MMA issuer (leader)   warps 2-5: epilogue
 constexpr int kCsThreads = 192;
 constexpr int kCsEpiWarp0 = 2;
-constexpr int kCsWStages = 5;                          // weight ring (one stage per k-block)
-constexpr int kCsPStages = 3;                          // pixel-box ring (one box per F k-blocks)
-constexpr int kCsTCB = 16;                             // pixel slots per tile row in shared memory / TMEM
+constexpr int kCsMaxStages = 5;
+constexpr int kCsPixStageBytes = 128 * 128;           // 128 pixel slots x 32 floats
 constexpr int kCsWStageBytes = 128 * 128;             // 128 weight rows x 32 floats
 constexpr int kCsStripFloats = 3 * 16 * kCbufPitch;   // three conv rows x 16 columns per epilogue warp
 constexpr int kCsPbufPitch = 128 + 4;                 // [2 lower-halo | 128 channels | 2 upper-halo]
 
 struct CsParams {
-    TcParams t;                                       // PR, PC (<= 7), TR = 2PR+1, TC = 2PC+1, tiles, nkb
-    int HR;                                           // pixel rows supplied per CTA (PR + 1 <= 8)
-    uint32_t pstage_bytes;                            // one pixel box: (HR + F - 1) rows x 16 slots x 128 B
-    uint32_t w_off, strip_off, pbuf_off, xh_off, cs_ctl_off;
+    TcParams t;                                       // PR, PC, TR = 2PR+1, TC = 2PC+1 (<= 16), tiles, nkb, stages
+    int HR;                                           // pixel rows staged per CTA (PR + 1)
+    uint32_t strip_off, pbuf_off, xh_off, cs_ctl_off;
+    uint32_t pix_bytes;                               // bytes of one pixel box (32 x TC x HR floats)
     uint32_t idesc2;                                  // M = 256, N = 256
 };
 
@@ -1275,28 +1269,23 @@ tc_block_cs_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_const
 
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
-    const uint32_t w_off = cp.w_off;                          // pixel boxes first, then weight stages
-    const uint32_t wfull_bar = base + cp.cs_ctl_off;          // [8]  leader's copy is the live one
-    const uint32_t wempty_bar = wfull_bar + 64;               // [8]  per CTA (multicast commit)
-    const uint32_t tfull_bar = wfull_bar + 128;               // [2]  per CTA (multicast commit)
-    const uint32_t tempty_bar = wfull_bar + 144;              // [2]  leader's copy, 8 arrivals (4 warps x 2 CTAs)
-    const uint32_t xbar = wfull_bar + 160;                    // [2]  per CTA, by tile parity: the partner's halo pushes landed
-    const uint32_t pfull_bar = wfull_bar + 176;               // [4]  leader's copy: both CTAs' pixel boxes have landed
-    const uint32_t pempty_bar = wfull_bar + 208;              // [4]  per CTA (multicast commit)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + cp.cs_ctl_off + 240);
-    float* s_bias = reinterpret_cast<float*>(gbase + cp.cs_ctl_off + 256);       // 128 floats
+    const int NS = p.stages;
+    const uint32_t w_off = NS * kCsPixStageBytes;             // pixel stages first, then weight stages
+    const uint32_t full_bar = base + cp.cs_ctl_off;           // [8]  leader's copy is the live one
+    const uint32_t empty_bar = full_bar + 64;                 // [8]  per CTA (multicast commit)
+    const uint32_t tfull_bar = full_bar + 128;                // [2]  per CTA (multicast commit)
+    const uint32_t tempty_bar = full_bar + 144;               // [2]  leader's copy, 8 arrivals (4 warps x 2 CTAs)
+    const uint32_t xbar = full_bar + 160;                     // [2]  per CTA, by tile parity: the partner's halo pushes landed
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + cp.cs_ctl_off + 176);
+    float* s_bias = reinterpret_cast<float*>(gbase + cp.cs_ctl_off + 192);       // 128 floats
     float* pbuf = reinterpret_cast<float*>(gbase + cp.pbuf_off);
     float* xh = reinterpret_cast<float*>(gbase + cp.xh_off);  // [2 tile parities][kMaxPooled][2] halo channels from the partner
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kCsWStages; ++s) {
-            mbar_init(wfull_bar + 8 * s, 1);
-            mbar_init(wempty_bar + 8 * s, 1);
-        }
-        for (int s = 0; s < kCsPStages; ++s) {
-            mbar_init(pfull_bar + 8 * s, 1);
-            mbar_init(pempty_bar + 8 * s, 1);
+        for (int s = 0; s < NS; ++s) {
+            mbar_init(full_bar + 8 * s, 1);
+            mbar_init(empty_bar + 8 * s, 1);
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(tfull_bar + 8 * b, 1);
@@ -1317,21 +1306,15 @@ tc_block_cs_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_const
 
     if (warp == 0) {
         // ======================================= TMA issuer ==============================
-        // Pixel boxes run ONE box ahead of the weight stream (a box serves F k-blocks and takes longer to land than a
-        // weight stage): box j+1 — the next tile's first box after the last one — is requested before the weights of
-        // box j.
-        int ws = 0, ps = 0;
-        uint32_t wphase = 0, pphase = 0;
-        const int boxes = p.nkb / g.F;                          // (channel chunk, fx) pairs per tile
-        int n = 0, cc0 = 0, y0 = 0;
-        auto open_tile = [&](long long w) {                     // decode + wait for pushed halo rows of the tile
-            n = (int)(w / tiles_per_img);
+        int stage = 0;
+        uint32_t phase = 0;
+        for (long long w = pair_id; w < p.total_tiles; w += npairs) {
+            const int n = (int)(w / tiles_per_img);
             const int rem = (int)(w - (long long)n * tiles_per_img);
             const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
-            const int cr0 = 2 * (g.p0 + tr_i * p.PR);
-            cc0 = 2 * (tc_i * p.PC);
+            const int cr0 = 2 * (g.p0 + tr_i * p.PR), cc0 = 2 * (tc_i * p.PC);
             const int ir0 = cr0 - g.P;                          // first input row of the tile (stride 1)
-            if (p.any_flag) {
+            if (p.any_flag) {                                   // pushed halo rows of image n have landed?
                 if (lane == 0) {
                     const int IRT = p.TR - 1 + g.F;
                     for (int s = 0; s < g.nseg; ++s)
@@ -1342,66 +1325,44 @@ tc_block_cs_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_const
                 }
                 __syncwarp();
             }
-            y0 = ir0 - g.seg[0].base + (int)rank * cp.HR;       // slab-relative first row of this CTA's boxes
-        };
-        auto issue_box = [&](int j) {                           // box j of the open tile: chunk j / F, filter column j % F
-            mbar_wait(pempty_bar + 8 * ps, pphase ^ 1);
-            if (lane == 0) {
-                const uint32_t fb = pfull_bar + 8 * ps;
-                if (rank == 0) mbar_arrive_expect_tx(fb, 2u * cp.pstage_bytes);
-                tma2_load_4d(base + ps * cp.pstage_bytes, &tmapX, (j / g.F) * kBlockK, cc0 + (j % g.F) - g.P, y0, n, fb);
-            }
-            __syncwarp();
-            if (++ps == kCsPStages) { ps = 0; pphase ^= 1; }
-        };
-        if (pair_id < p.total_tiles) { open_tile(pair_id); issue_box(0); }
-        for (long long w = pair_id; w < p.total_tiles; w += npairs) {
-            for (int j = 0; j < boxes; ++j) {
-                if (j + 1 < boxes) issue_box(j + 1);
-                else if (w + npairs < p.total_tiles) { open_tile(w + npairs); issue_box(0); }
-                for (int fy = 0; fy < g.F; ++fy) {
-                    const int kb = j * g.F + fy;
-                    mbar_wait(wempty_bar + 8 * ws, wphase ^ 1);
-                    if (lane == 0) {
-                        const uint32_t fb = wfull_bar + 8 * ws;
-                        if (rank == 0) mbar_arrive_expect_tx(fb, 2u * (uint32_t)kCsWStageBytes);
-                        tma2_load_2d(base + w_off + ws * kCsWStageBytes, &tmapW, kb * kBlockK, (int)rank * 128, fb);
-                    }
-                    __syncwarp();
-                    if (++ws == kCsWStages) { ws = 0; wphase ^= 1; }
+            const int y0 = ir0 - g.seg[0].base + (int)rank * cp.HR;   // slab-relative row of this CTA's filter row 0
+            int fy = 0, fx = 0, cch = 0;
+            for (int kb = 0; kb < p.nkb; ++kb) {
+                mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+                if (lane == 0) {
+                    const uint32_t fb = full_bar + 8 * stage;
+                    if (rank == 0) mbar_arrive_expect_tx(fb, 2u * (cp.pix_bytes + (uint32_t)kCsWStageBytes));
+                    tma2_load_4d(base + stage * kCsPixStageBytes, &tmapX, cch * kBlockK, cc0 + fx - g.P, y0 + fy, n, fb);
+                    tma2_load_2d(base + w_off + stage * kCsWStageBytes, &tmapW, kb * kBlockK, (int)rank * 128, fb);
                 }
+                __syncwarp();
+                if (++fx == g.F) { fx = 0; if (++fy == g.F) { fy = 0; ++cch; } }
+                if (++stage == NS) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
         // ======================================= MMA issuer (leader CTA only) ============
         if (rank == 0) {
-            int ws = 0, ps = 0, buf = 0, fy = 0;
-            uint32_t wphase = 0, pphase = 0, bphase = 0;
+            int stage = 0, buf = 0;
+            uint32_t phase = 0, bphase = 0;
             for (long long w = pair_id; w < p.total_tiles; w += npairs) {
                 mbar_wait(tempty_bar + 8 * buf, bphase ^ 1);    // both CTAs' epilogues have drained this buffer
                 tc_fence_after();
                 for (int kb = 0; kb < p.nkb; ++kb) {
-                    if (fy == 0) mbar_wait(pfull_bar + 8 * ps, pphase);
-                    mbar_wait(wfull_bar + 8 * ws, wphase);
+                    mbar_wait(full_bar + 8 * stage, phase);
                     tc_fence_after();
                     if (lane == 0) {
-                        const uint64_t dw = make_smem_desc(base + w_off + ws * kCsWStageBytes);
-                        // filter row fy: the same box, fy tile rows (fy x 16 slots x 128 B) further down
-                        const uint64_t dx = make_smem_desc(base + ps * cp.pstage_bytes + (uint32_t)fy * (kCsTCB * 128));
+                        const uint64_t dw = make_smem_desc(base + w_off + stage * kCsWStageBytes);
+                        const uint64_t dx = make_smem_desc(base + stage * kCsPixStageBytes);
 #pragma unroll
                         for (int ks = 0; ks < kBlockK / 8; ++ks)
                             umma2_tf32(tmem_base + (uint32_t)(buf * 256), dw + 2 * ks, dx + 2 * ks, cp.idesc2,
                                        (kb | ks) != 0 ? 1u : 0u);
-                        umma2_commit_mc(wempty_bar + 8 * ws, 3);         // frees the weight stage in both CTAs
-                        if (fy == g.F - 1) umma2_commit_mc(pempty_bar + 8 * ps, 3);   // ... and the pixel box
+                        umma2_commit_mc(empty_bar + 8 * stage, 3);       // frees the stage in both CTAs
                         if (kb == p.nkb - 1) umma2_commit_mc(tfull_bar + 8 * buf, 3);
                     }
                     __syncwarp();
-                    if (++ws == kCsWStages) { ws = 0; wphase ^= 1; }
-                    if (++fy == g.F) {
-                        fy = 0;
-                        if (++ps == kCsPStages) { ps = 0; pphase ^= 1; }
-                    }
+                    if (++stage == NS) { stage = 0; phase ^= 1; }
                 }
                 if (++buf == 2) { buf = 0; bphase ^= 1; }
             }
@@ -1418,9 +1379,10 @@ tc_block_cs_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_const
         const bool do_lrn = g.lrn.N_lrn > 0;
         const float al = g.lrn.mode == B200_LRN_ALPHA_OVER_N ? g.lrn.alpha / (float)max(g.lrn.N_lrn, 1) : g.lrn.alpha;
         const float nbeta = -g.lrn.beta;
-        // conv row ri of the tile sits in the 16 TMEM columns from col(ri) of the buffer (CTA half h = ri / HR)
-        auto row_col = [&](int ri) { const int h = ri >= cp.HR ? 1 : 0; return 128 * h + (ri - h * cp.HR) * kCsTCB; };
-        auto row_shift = [&](int) { return 0; };               // HR <= 8 rows of 16 slots: a row never leaves its half
+        // conv row ri of the tile sits in TMEM columns col(ri) .. col(ri)+TC-1 of the buffer; 16 columns are loaded from
+        // min(col, 240), so tile column 0 lands in strip column col - start
+        auto row_col = [&](int ri) { const int h = ri >= cp.HR ? 1 : 0; return 128 * h + (ri - h * cp.HR) * p.TC; };
+        auto row_shift = [&](int ri) { const int c = row_col(ri); return c + 16 > 256 ? c - (256 - 16) : 0; };
         int buf = 0, it = 0;
         uint32_t bphase = 0;
         for (long long w = pair_id; w < p.total_tiles; w += npairs, ++it) {
@@ -1861,8 +1823,6 @@ inline bool cs_requested(const b200_block_geom* g) {
     return !is_patch_mode(g->C) && (policy().conv2 == 0 || policy().conv2 == 4);
 }
 
-size_t smem_bytes_cs(const CsParams& cp);
-
 int fill_cs(const TcConv* t, const b200_block_geom* g, CsParams* cp, CUtensorMap* tmapX, int flags) {
     if (is_patch_mode(g->C) || !t->half_ok || g->S != 1 || g->K != 256 || t->sms < 2) return B200_ERR_UNSUPPORTED;
     if (g->lrn.N_lrn != 0 && g->lrn.N_lrn != 5) return B200_ERR_UNSUPPORTED;   // halo of two channels per side
@@ -1871,14 +1831,14 @@ int fill_cs(const TcConv* t, const b200_block_geom* g, CsParams* cp, CUtensorMap
     memset(cp, 0, sizeof(*cp));
     TcParams& p = cp->t;
     p.g = *g;
-    // tile plan: PR x PC pooled per tile (both <= 7); each CTA supplies HR = PR+1 <= 8 pixel rows of 16 slots
+    // tile plan: PR x PC pooled per tile, each CTA stages HR = PR+1 pixel rows of TC = 2PC+1 <= 16 columns
     const int rows = g->p1 - g->p0, pairs = t->sms / 2;
     long best_waves = -1, best_tiles = 0;
     int best_slots = 0;
-    for (int PR = 1; PR <= rows && PR <= 7; ++PR)
+    for (int PR = 1; PR <= rows && PR <= 31; ++PR)
         for (int PC = 1; PC <= 7 && PC <= g->Wp; ++PC) {
             const int HR = PR + 1, TC = 2 * PC + 1;
-            if (PR * PC > kMaxPooled) continue;
+            if (HR * TC > 128 || PR * PC > kMaxPooled) continue;
             const long tiles = (long)cdiv(rows, PR) * cdiv(g->Wp, PC);
             const long waves = (tiles * g->N + pairs - 1) / pairs;
             const int slots = 2 * HR * TC;
@@ -1894,31 +1854,33 @@ int fill_cs(const TcConv* t, const b200_block_geom* g, CsParams* cp, CUtensorMap
     p.nkb = num_kblocks(g->F, g->C);
     p.round_out = flags & 1;
     p.dbg = 0;
-    p.stages = kCsWStages;
     p.total_tiles = (long long)g->N * p.tiles_r * p.tiles_c;
     for (int s = 0; s < g->nseg; ++s)
         if (g->seg[s].flag) p.any_flag = 1;
-    const int box_rows = cp->HR + g->F - 1;                    // one pixel box serves the F filter rows of a (chunk, fx)
-    cp->pstage_bytes = (uint32_t)(box_rows * kCsTCB * 128);   // a multiple of 1 KB: rows are 2 KB
+    cp->pix_bytes = (uint32_t)(kBlockK * p.TC * cp->HR * 4);
     const size_t strips = 4 * (size_t)kCsStripFloats * 4;
     const size_t pbuf_bytes = (size_t)kMaxPooled * kCsPbufPitch * 4;
     const size_t xh_bytes = 2 * (size_t)kMaxPooled * 2 * 4;
-    cp->w_off = kCsPStages * cp->pstage_bytes;
-    cp->strip_off = cp->w_off + kCsWStages * kCsWStageBytes;
+    const size_t ctl = 192 + 128 * 4 + 64;
+    const long avail = 226 * 1024 - 1024 - (long)(strips + pbuf_bytes + xh_bytes + ctl);
+    int stages = (int)(avail / (kCsPixStageBytes + kCsWStageBytes));
+    if (stages > kCsMaxStages) stages = kCsMaxStages;
+    if (stages < 2) return B200_ERR_UNSUPPORTED;
+    p.stages = stages;
+    cp->strip_off = (uint32_t)(stages * (kCsPixStageBytes + kCsWStageBytes));
     cp->pbuf_off = cp->strip_off + (uint32_t)strips;
     cp->xh_off = cp->pbuf_off + (uint32_t)pbuf_bytes;
     cp->cs_ctl_off = cp->xh_off + (uint32_t)xh_bytes;
-    if (smem_bytes_cs(*cp) > 227 * 1024) return B200_ERR_UNSUPPORTED;
     p.tmem_cols = 512;
     cp->idesc2 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(256 >> 3) << 17) | ((256u >> 4) << 24);
     EncodeTiledFn enc = get_encode();
     if (!enc) return B200_ERR_UNSUPPORTED;
     const int pitch = g->in_pitch ? g->in_pitch : g->W * g->C;
     const int slab = g->seg[0].slab;
-    if (slab <= 0 || (pitch * 4) % 16 != 0 || box_rows > 256) return B200_ERR_UNSUPPORTED;
+    if (slab <= 0 || (pitch * 4) % 16 != 0) return B200_ERR_UNSUPPORTED;
     cuuint64_t dims[4] = {(cuuint64_t)g->C, (cuuint64_t)g->W, (cuuint64_t)slab, (cuuint64_t)g->N};
     cuuint64_t strides[3] = {(cuuint64_t)g->C * 4, (cuuint64_t)pitch * 4, (cuuint64_t)slab * pitch * 4};
-    cuuint32_t box[4] = {(cuuint32_t)kBlockK, (cuuint32_t)kCsTCB, (cuuint32_t)box_rows, 1};
+    cuuint32_t box[4] = {(cuuint32_t)kBlockK, (cuuint32_t)p.TC, (cuuint32_t)cp->HR, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     if (enc(tmapX, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)g->seg[0].ptr, dims, strides, box, estr,
             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -1927,7 +1889,7 @@ int fill_cs(const TcConv* t, const b200_block_geom* g, CsParams* cp, CUtensorMap
     return B200_OK;
 }
 
-size_t smem_bytes_cs(const CsParams& cp) { return 1024 + (size_t)cp.cs_ctl_off + 256 + 128 * 4 + 64; }
+size_t smem_bytes_cs(const CsParams& cp) { return 1024 + (size_t)cp.cs_ctl_off + 192 + 128 * 4 + 64; }
 
 size_t smem_bytes_pair(const PairParams& pp) {
     return 1024 + (size_t)pp.pair_ctl_off + 176 + kMaxPooled * 8 + (size_t)pp.t.g.K * 4 + 64;
@@ -1963,7 +1925,7 @@ extern "C" int b200_tc_conv_create(const float* w_kcff, int K, int C, int F, voi
                 for (int fx = 0; fx < F; ++fx) {
                     const int kk = t->patch_mode
                                        ? fy * t->FCpad + fx * C + c
-                                       : ((c / kBlockK) * F * F + fx * F + fy) * kBlockK + c % kBlockK;
+                                       : ((c / kBlockK) * F * F + fy * F + fx) * kBlockK + c % kBlockK;
                     wk[(size_t)k * t->Kpad + kk] =
                         host_tf32(w_kcff[(((size_t)k * C + c) * F + fy) * F + fx]);
                 }

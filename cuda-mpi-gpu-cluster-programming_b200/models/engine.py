@@ -456,9 +456,15 @@ class Blocks12Engine:
                     self._graphs[key] = (g, self.launches - l0)
                     self.launches, self.epoch = l0, e0    # capture launched nothing
                     return self.forward_enqueue(in_idx, out_idx)
-                except Exception as ex:                   # capture unsupported: stay eager
+                except Exception as ex:
+                    # never fall back silently: a forward that is timed as one graph replay must BE one (an eager
+                    # multi-GPU forward is launch-bound and would be reported as if it were the product)
+                    import os
+                    if os.environ.get("B200_ALLOW_EAGER") != "1":
+                        raise RuntimeError(f"[Rank {self.rank}] CUDA graph capture of the forward failed: {ex} "
+                                           f"(use_graph=False or B200_ALLOW_EAGER=1 to run eagerly on purpose)") from ex
                     import warnings
-                    warnings.warn(f"CUDA graph capture failed ({ex}); running eagerly")
+                    warnings.warn(f"CUDA graph capture failed ({ex}); running eagerly (B200_ALLOW_EAGER=1)")
                     self.use_graph = False
             self._enqueue_stages(in_idx, out_idx)
         return self.outs[out_idx]

@@ -13,7 +13,7 @@ from b200cnn.ops import tc
 
 
 def fwd(cfg, x, w, kind, reuse=0):
-    tc.set_policy(conv2=kind, cs_reuse=reuse)
+    tc.set_policy(conv2=kind)
     e = single_gpu_engine(cfg, w, "cuda:0", "tf32")
     e.use_graph = False
     y = e.forward(x.cuda()).clone()
@@ -26,11 +26,10 @@ for batch, hw in ((6, 227), (3, 99)):
     cfg = default_config(H=hw, W=hw, batch=batch, init=INIT_RAND, seed=2, precision="tf32")
     x, w = make_problem(cfg)
     a, _ = fwd(cfg, x, w, "db")
-    for reuse in (0, 1):
-        b, b2 = fwd(cfg, x, w, "cs", reuse)
-        rel = float((a - b).abs().max() / a.abs().max())
-        print(f"batch {batch} {hw}x{hw} cs reuse={reuse}: equal {torch.equal(a, b)} rel diff {rel:.3e} second forward "
-              f"equal {torch.equal(b, b2)}", flush=True)
+    b, b2 = fwd(cfg, x, w, "cs")
+    rel = float((a - b).abs().max() / a.abs().max())
+    print(f"batch {batch} {hw}x{hw}: equal {torch.equal(a, b)} rel diff {rel:.3e} second forward equal {torch.equal(b, b2)}",
+          flush=True)
 
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
@@ -49,9 +48,8 @@ def timeit(fn, n=10):
 cfg = default_config(batch=128, init=INIT_RAND, seed=1, precision="tf32")
 x, w = make_problem(cfg)
 xd = x.cuda()
-for kind, reuse, dbg in (("pair", 0, 0), ("cs", 0, 0), ("cs", 0, 64), ("cs", 1, 0)):
-    tc.set_policy(conv2=kind, cs_reuse=reuse, dbg=dbg)
-    kind = f"{kind} reuse={reuse} slots-per-row={'16' if (reuse or dbg) else 'TC'}"
+for kind in ("pair", "cs"):
+    tc.set_policy(conv2=kind)
     e = single_gpu_engine(cfg, w, "cuda:0")
     e.forward(xd); torch.cuda.synchronize()
     print(f"world 1 conv2={kind}: block2 {timeit(lambda: e.stage_block2(0)):.1f} us", flush=True)
@@ -61,4 +59,4 @@ for kind, reuse, dbg in (("pair", 0, 0), ("cs", 0, 0), ("cs", 0, 64), ("cs", 1, 
         ts = [timeit(lambda e=e: e.stage_block2(0)) for e in ew.engines[:2]]
         print(f"world {world} conv2={kind}: block2 rank0 {ts[0]:.1f} us rank1 {ts[1]:.1f} us", flush=True)
         del ew
-tc.set_policy(conv2="auto", cs_reuse=0, dbg=0)
+tc.set_policy(conv2="auto")
