@@ -30,8 +30,8 @@ from b200cnn.parallel.planner import make_plan
 
 
 class NcclHaloRank:
-    def __init__(self, cfg, w, ctx, precision="tf32"):
-        self.cfg, self.ctx, self.precision = cfg, ctx, precision
+    def __init__(self, cfg, w, ctx, precision="tf32", sharded=False):
+        self.cfg, self.ctx, self.precision, self.sharded = cfg, ctx, precision, sharded
         self.plan = make_plan(cfg, ctx.world, "halo")
         self.rp = self.plan.ranks[ctx.rank]
         sh = self.sh = self.plan.shapes
@@ -62,9 +62,11 @@ class NcclHaloRank:
     def forward(self):
         cfg, sh, rp, ctx = self.cfg, self.sh, self.rp, self.ctx
         p1, p2 = cfg.conv1, cfg.conv2
-        # ---- scatter (rank 0 -> all) ----------------------------------------------------------
+        # ---- scatter (rank 0 -> all); skipped when the rows are already in place (--sharded) ------
         ops = []
-        if ctx.rank == 0:
+        if self.sharded:
+            pass
+        elif ctx.rank == 0:
             for q in self.plan.ranks[1:]:
                 if q.in_rows[1] > q.in_rows[0]:
                     ops.append(td.P2POp(td.isend, self.full_in[:, q.in_rows[0]:q.in_rows[1]].contiguous(), q.rank))
@@ -135,12 +137,19 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--precision", default="tf32")
     ap.add_argument("--check", action="store_true", help="compare with the fused engine's output")
+    ap.add_argument("--sharded", action="store_true",
+                    help="every rank already holds its input rows (no scatter in the timed step): the like-for-like "
+                         "baseline of bench.py's sharded placement; halo and gather still go through NCCL")
     a = ap.parse_args()
     ctx = bdist.init()
     cfg = b200cnn.default_config(batch=a.batch, init=INIT_RAND, seed=1, precision=a.precision)
     x, w = make_problem(cfg)
-    r = NcclHaloRank(cfg, w, ctx, a.precision)
-    if ctx.rank == 0:
+    r = NcclHaloRank(cfg, w, ctx, a.precision, a.sharded)
+    if a.sharded:
+        i0, i1 = r.rp.in_rows
+        if i1 > i0:
+            r.x.copy_(x[:, i0:i1].to(ctx.device))
+    elif ctx.rank == 0:
         r.full_in = x.to(ctx.device)
     for _ in range(a.warmup):
         r.forward()
@@ -151,7 +160,8 @@ def main():
         out = r.forward()
     e1.record(); e1.synchronize()
     ms = ctx.max_float(e0.elapsed_time(e1) / a.steps)
-    res = {"baseline": "nccl send/recv scatter+halo+gather, unfused", "n_gpus": ctx.world, "batch": a.batch,
+    res = {"baseline": "nccl send/recv " + ("halo+gather (inputs sharded)" if a.sharded else "scatter+halo+gather") + ", unfused",
+           "n_gpus": ctx.world, "batch": a.batch,
            "ms_per_step": round(ms, 4), "images_per_s": round(a.batch / ms * 1e3, 1), "precision": a.precision}
     if a.check and ctx.rank == 0 and ctx.world >= 1:
         from b200cnn.models.engine import single_gpu_engine

@@ -5,13 +5,14 @@
 set -u
 ROOT="$(cd "$(dirname "${BASH_SOURCE[0]}")/.." && pwd)"
 cd "$ROOT"
-OUT=gpurun_out/baselines; mkdir -p $OUT
+OUT=${OUTB:-gpurun_out/baselines}; mkdir -p $OUT
 export LD_LIBRARY_PATH=/usr/local/cuda/lib64:${LD_LIBRARY_PATH:-}
 NG=$(nvidia-smi -L | wc -l)
 [ -x baseline/_ref/src/final_project/v4_mpi_cuda/template ] || python baseline/build_reference.py > $OUT/build.log 2>&1
 R=baseline/_ref/src/final_project
+[ -x baseline/v5_reconstruction/template ] || make -C baseline/v5_reconstruction > $OUT/v5_build.log 2>&1
 echo "== ref V1 (CPU, 3 runs)"; for i in 1 2 3; do $R/v1_serial/template | grep "completed in"; done | tee $OUT/ref_v1.log
-echo "== ref V3 (5 runs)"; for i in 1 2 3 4 5; do $R/v3_cuda_only/template | head -1; done | tee $OUT/ref_v3.log
+echo "== ref V3 (3 runs)"; for i in 1 2 3; do $R/v3_cuda_only/template | head -1; done | tee $OUT/ref_v3.log
 echo "== reference forward functions in a warm loop (128 images after 3 warm-up calls; baseline/ref_loop)"
 make -C baseline/ref_loop > $OUT/ref_loop_build.log 2>&1 || tail -3 $OUT/ref_loop_build.log
 for v in v3 v4; do [ -x baseline/ref_loop/ref_loop_$v ] && baseline/ref_loop/ref_loop_$v 128 3; done | tee $OUT/ref_loop.log
@@ -24,6 +25,7 @@ for np in 1 2 4 8; do
     for i in 1 2 3; do (cd baseline/v5_reconstruction && "$ROOT/bin/mpirun" --oversubscribe -np $np ./template 2>&1 | grep -E "Shape|completed"); done | tee $OUT/v5rec_np$np.log
   fi
   echo "== NCCL halo baseline np=$np"
-  python -m torch.distributed.run --nnodes=1 --nproc-per-node $np --master-addr 127.0.0.1 --master-port 29541 baseline/nccl_halo.py --check 2>$OUT/nccl_np$np.err | tee $OUT/nccl_halo_np$np.json
+  timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $np --master-addr 127.0.0.1 --master-port 2954$np baseline/nccl_halo.py --check 2>$OUT/nccl_np$np.err | grep "^{" | tee $OUT/nccl_halo_np$np.json | cut -c1-300
+  timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $np --master-addr 127.0.0.1 --master-port 2955$np baseline/nccl_halo.py --check --sharded 2>>$OUT/nccl_np$np.err | grep "^{" | tee $OUT/nccl_halo_sharded_np$np.json | cut -c1-300
 done
-echo "== bench --impl reference"; python bench.py --impl reference --steps 5 --warmup 1 | tee $OUT/bench_reference_np1.json
+
