@@ -540,6 +540,7 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    grid_dep_launch();          // the next block's CTAs may take SMs as ours exit (they wait for this grid's end)
     const uint32_t tmem_base = *tmem_slot;
     const int tiles_per_img = p.tiles_r * p.tiles_c;
 
@@ -1293,10 +1294,16 @@ tc_block_cs_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_const
             mbar_init(xbar + 8 * b, 1);
         }
         fence_mbar_init();
-        block_gate_wait(g);
     }
     for (int i = threadIdx.x; i < 128; i += kCsThreads) s_bias[i] = bias[128 * rank + i];
     if (warp == 1) tmem_alloc2(smem_u32(tmem_slot), 512);
+    // Everything above touches only weights and this CTA's own state, so with a programmatic launch (flags bit 1)
+    // it overlaps the tail of the previous kernel in the stream.  From here on its output is read.
+    grid_dep_wait();
+    if (threadIdx.x == 0) {
+        block_gate_wait(g);
+        fence_proxy_async_global();                           // the previous grid's generic stores -> our TMA reads
+    }
     tc_fence_before();
     cluster_sync_all();                                       // both CTAs' barriers and TMEM exist
     tc_fence_after();
@@ -1490,6 +1497,7 @@ struct Policy {
     int no_swap = 0;      // conv1-type layers through the generic kernel (experiments)
     int no_direct = 0;    // conv1: shared-memory patch instead of the direct loader (experiments)
     int dbg = 0;          // perf-decomposition knobs of tc_block_kernel (TcParams::dbg)
+    int pdl = 1;          // honour flags bit 1 (programmatic dependent launch of the channel-split kernel)
 };
 
 int parse_conv2(const char* v) {
@@ -1509,6 +1517,7 @@ Policy& policy() {
         q.no_swap = getenv("B200_TC_NO_SWAP") != nullptr;
         q.no_direct = getenv("B200_TC_NO_DIRECT") != nullptr;
         if (const char* e = getenv("B200_TC_DBG")) q.dbg = atoi(e);
+        if (const char* e = getenv("B200_TC_PDL")) q.pdl = atoi(e);
         return q;
     }();
     return pol;
@@ -2002,6 +2011,7 @@ extern "C" int b200_tc_set_policy(const char* key, const char* value) {
     else if (!strcmp(key, "no_swap")) q.no_swap = atoi(value);
     else if (!strcmp(key, "no_direct")) q.no_direct = atoi(value);
     else if (!strcmp(key, "dbg")) q.dbg = atoi(value);
+    else if (!strcmp(key, "pdl")) q.pdl = atoi(value);
     else return B200_ERR_ARG;
     return B200_OK;
 }
@@ -2043,6 +2053,9 @@ extern "C" int b200_tc_block_tiles(const b200_block_geom* g) {
 }
 
 // flags bit 0: round the stored outputs to TF32 (use for activations feeding another tc block)
+// flags bit 1: the kernel may become resident before the previous kernel in `stream` has finished (programmatic
+//              dependent launch); it waits for that kernel's completion before reading anything it wrote.  Honoured
+//              by the channel-split kernel, ignored by the others (they launch with the normal stream order).
 extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const b200_block_geom* g,
                              int flags, void* stream) {
     TcConv* t = (TcConv*)handle;
@@ -2090,7 +2103,18 @@ extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const 
             B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_cs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             long long ctas = 2 * cp.t.total_tiles;
             if (ctas > (sms & ~1)) ctas = sms & ~1;
-            tc_block_cs_kernel<<<(unsigned)ctas, kCsThreads, smem, (cudaStream_t)stream>>>(t->tmap_half, tmapX, cp, bias, out);
+            cudaLaunchConfig_t cfg;
+            memset(&cfg, 0, sizeof(cfg));
+            cfg.gridDim = dim3((unsigned)ctas);
+            cfg.blockDim = dim3(kCsThreads);
+            cfg.dynamicSmemBytes = smem;
+            cfg.stream = (cudaStream_t)stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = ((flags & 2) && policy().pdl) ? 1 : 0;
+            B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, tc_block_cs_kernel, t->tmap_half, tmapX, cp, bias, (float*)out));
             B200_CUDA_TRY(cudaGetLastError());
             return B200_OK;
         }

@@ -54,6 +54,12 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
 __device__ __forceinline__ void fence_proxy_async_global() {
     asm volatile("fence.proxy.async.global;" ::: "memory");
 }
+// Programmatic dependent launch: a kernel launched with the stream-serialization attribute may become resident while
+// the kernel before it in the stream still runs; grid_dep_wait() returns once that kernel has finished and its
+// writes are visible (no-op without the attribute).  grid_dep_launch() in the earlier kernel lets the later one be
+// scheduled onto SMs as they free up instead of after the last CTA has exited.
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1,
                                             uint32_t bar) {
     asm volatile(

@@ -417,7 +417,7 @@ class Blocks12Engine:
         if self.precision == "simt":
             cu.simt_block(self.w2p, self.b2, out_ptr, g)
         else:
-            self.tc2.run(self.b2, out_ptr, g)
+            self.tc2.run(self.b2, out_ptr, g, overlap_prev=True)     # prologue overlaps block 1's tail
         self.launches += 1
 
     def stage_done_wait(self) -> None:

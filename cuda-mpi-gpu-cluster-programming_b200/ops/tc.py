@@ -34,7 +34,8 @@ def _lib():
 
 def set_policy(**kw) -> None:
     """Process-wide kernel choice (csrc/cuda/tc_block.cu ``Policy``): ``conv2="auto"|"single"|"db"|"pair"``,
-    ``conv1="auto"|"cpasync"``, ``no_swap`` / ``no_direct`` / ``dbg`` integers.  Every choice gives bit-identical
+    ``conv1="auto"|"cpasync"``, ``no_swap`` / ``no_direct`` / ``dbg`` integers, ``pdl=0|1`` (programmatic
+    dependent launch of block 2 behind block 1).  Every choice gives bit-identical
     outputs; tests and experiments use it to compare the kernels."""
     for k, v in kw.items():
         cu.cu_check(_lib().b200_tc_set_policy(k.encode(), str(v).encode()), f"tc_set_policy({k}={v})")
@@ -51,9 +52,13 @@ class TcConv:
                         "tc_conv_create")
         self._h = h
 
-    def run(self, bias: torch.Tensor, out_ptr: int, g: cu.BlockGeom, round_out: bool = False) -> None:
+    def run(self, bias: torch.Tensor, out_ptr: int, g: cu.BlockGeom, round_out: bool = False,
+            overlap_prev: bool = False) -> None:
+        """``overlap_prev``: programmatic dependent launch — the kernel's prologue may overlap the tail of the
+        previous kernel in the stream; it waits for that kernel before reading what it wrote (flags bit 1)."""
         cu.cu_check(_lib().b200_tc_block(self._h, fptr(bias), C.c_void_p(out_ptr), C.byref(g),
-                                         1 if round_out else 0, cu.current_stream_ptr()), "tc_block")
+                                         (1 if round_out else 0) | (2 if overlap_prev else 0),
+                                         cu.current_stream_ptr()), "tc_block")
 
     def __del__(self):
         try:
