@@ -27,6 +27,7 @@
 // warp 9 TMA issuer.  Persistent: grid = min(tiles, SMs), static round-robin over tiles.
 #include "tc_ptx.cuh"
 
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -58,7 +59,9 @@ struct TcParams {
     int stages, b_stage_bytes;
     int tmem_cols;
     int any_flag;
-    int dbg;                     // perf experiments only: 1 skip A copies, 2 skip B TMA, 4 skip epilogue math
+    int dbg;                     // perf experiments only: 1 skip A copies, 2 skip B TMA, 4 skip epilogue math;
+                                 // conv1 kernel: 64 skip pixel TMA, 128 skip weight TMA, 256 skip epilogue, 512 skip MMAs;
+                                 // plan-time: 1024 keep the 3-stage ring, 2048 pool through smem strips
     int round_out;               // round stored outputs to TF32 (next layer's A operand is then exact)
     int FCpad;                   // patch mode: floats per filter row in K (F*C rounded up to 4)
     int patch_rows, patch_pitch; // patch mode: staged input patch (rows incl. 1 guard row, floats per row)
@@ -485,11 +488,12 @@ struct SwParams {
     int direct;                                      // 1: B rows are cp.async'd straight from global memory
     int nstages;                                     // 2 (patch) or 3 (direct)
     int cpr;                                         // direct: 16 B chunks per filter row run (F*C/4)
-    int nkb_main;                                    // pixel-TMA mode: k-blocks fed by TMA (= F), rest by cp.async
+    int nkb_main;                                    // pixel-TMA mode: k-blocks of whole filter rows (= F), rest = tails
     uint32_t pix_bytes;                              // pixel-TMA mode: bytes of one pixel box (32 x TC x TR floats)
+    int regpool;                                     // epilogue pools in registers (TC <= 16): no smem strips
 };
 
-// Pixel-TMA mode (DRAFT, B200_TC_TMA1=1, not yet run on a GPU): one tensor map per input
+// Pixel-TMA mode (the default conv1 loader; B200_TC_CONV1=cpasync selects the other one): one tensor map per input
 // row phase r = fy % S over an overlapping-stride view of the resident input,
 //   element (i, x, y, n) = in[n][S*y + r][x*S*C + i],  dims {32, Wc, rows/S, N},
 // so the first 32 floats of every pixel's filter-row run, for a whole TR x TC tile, are ONE box {32, TC, TR, 1}
@@ -520,17 +524,29 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + sp.sw_ctl_off + 96);
     const float** rowtab = reinterpret_cast<const float**>(gbase + sp.sw_ctl_off + 112);
     float* s_bias = reinterpret_cast<float*>(gbase + sp.sw_ctl_off + 112 + kRowTab * 8);
+    // Pixel-TMA mode, tail k-block t (0 or 1) of every tile: the producers cp.async its pixel half into the ring stage
+    // the block will use.  tail_free[t]: that stage's previous occupant (k-block nkb_main + t - NS of the same tile) has
+    // been consumed; tail_bar[t]: the copies have landed.  Both complete once per tile, so their parity is the tile's;
+    // the ring's own empty barriers cannot be used here because the producers skip the main blocks and a parity wait
+    // is only safe for a waiter that follows every phase.
+    const uint32_t tail_bar = full_bar + 112 + kRowTab * 8 + 128 * 4;    // [2]
+    const uint32_t tail_free = tail_bar + 16;                            // [2]
     float* patch = reinterpret_cast<float*>(gbase + p.patch_off);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
         for (int s = 0; s < NS; ++s) {
-            mbar_init(full_bar + 8 * s, ((sp.direct && !kPixTma) ? kProducerThreads : kProducerWarps) + 1);
+            // pixel-TMA mode: the TMA warp's expect_tx is the only arrival (tail k-blocks: see tail_bar)
+            mbar_init(full_bar + 8 * s, kPixTma ? 1 : (sp.direct ? kProducerThreads : kProducerWarps) + 1);
             mbar_init(empty_bar + 8 * s, 1);
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(tfull_bar + 8 * b, 1);
             mbar_init(tempty_bar + 8 * b, kSwEpiWarps);
+            if (kPixTma) {
+                mbar_init(tail_bar + 8 * b, kProducerThreads);     // one asynchronous arrival per producer thread
+                mbar_init(tail_free + 8 * b, 1);                   // tcgen05.commit by the MMA warp
+            }
         }
         fence_mbar_init();
         block_gate_wait(g);
@@ -560,7 +576,8 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
         }
         int stage = 0;
         uint32_t phase = 0;
-        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
+        long long tile_it = 0;
+        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x, ++tile_it) {
             const int n = (int)(w / tiles_per_img);
             const int rem = (int)(w - (long long)n * tiles_per_img);
             const int tr_i = rem / p.tiles_c, tc_i = rem - tr_i * p.tiles_c;
@@ -596,33 +613,45 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                     hsel[i] = ok ? pi * g.S : -1;
                     xb[i] = ((cc0 + pj) * g.S - g.P) * g.C * 4;
                 }
+                if (sp.direct == 2 && kPixTma) {
+                    // Row K order, main k-blocks by TMA (warp 9): only the tail blocks are ours.  Their ring position
+                    // follows from the k-block count; the copies are fire-and-forget (each thread's cp.asyncs arrive
+                    // on the tail barrier when they land), so a producer never waits for data.
+                    for (int kb = sp.nkb_main; kb < p.nkb; ++kb) {
+                        const int tt = kb - sp.nkb_main;
+                        const int st = (int)((tile_it * p.nkb + kb) % NS);
+                        mbar_wait(tail_free + 8 * tt, (uint32_t)(tile_it & 1));
+                        const uint32_t a_dst = base + st * kAStageBytes + dst0;
+                        const int tfy = 8 * tt + j;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            if (i >= 4 * p.nacc) break;
+                            const char* rp = (tfy < g.F && hsel[i] >= 0)
+                                                 ? reinterpret_cast<const char*>(rowtab[hsel[i] + tfy]) : nullptr;
+                            cp_async16(a_dst + i * 4096u, rp + (xb[i] + 128), rp ? 16u : 0u);
+                        }
+                        cp_async_mbar_arrive_noinc(tail_bar + 8 * tt);
+                    }
+                    continue;
+                }
                 if (sp.direct == 2) {
                     // Row K order (shared by both loaders, so they are bit-identical): k-block kb < nkb_main holds
                     // floats 0..31 of filter row kb's run of every pixel; tail block t holds, as chunk j, the 16 B at
-                    // run offset 128 B of filter row 8t + j.  kPixTma: the main blocks arrive by TMA (warp 9) and the
-                    // producers only keep the barrier counts uniform there.
+                    // run offset 128 B of filter row 8t + j.
                     for (int kb = 0; kb < p.nkb; ++kb) {
                         mbar_wait(empty_bar + 8 * stage, phase ^ 1);
                         const bool tail = kb >= sp.nkb_main;
-                        if (tail || !kPixTma) {
-                            const uint32_t a_dst = base + stage * kAStageBytes + dst0;
-                            const int tfy = tail ? 8 * (kb - sp.nkb_main) + j : kb;
-                            const int boff = tail ? 128 : 16 * j;
+                        const uint32_t a_dst = base + stage * kAStageBytes + dst0;
+                        const int tfy = tail ? 8 * (kb - sp.nkb_main) + j : kb;
+                        const int boff = tail ? 128 : 16 * j;
 #pragma unroll
-                            for (int i = 0; i < 8; ++i) {
-                                if (i >= 4 * p.nacc) break;
-                                const char* rp = (tfy < g.F && hsel[i] >= 0)
-                                                     ? reinterpret_cast<const char*>(rowtab[hsel[i] + tfy]) : nullptr;
-                                cp_async16(a_dst + i * 4096u, rp + (xb[i] + boff), rp ? 16u : 0u);
-                            }
+                        for (int i = 0; i < 8; ++i) {
+                            if (i >= 4 * p.nacc) break;
+                            const char* rp = (tfy < g.F && hsel[i] >= 0)
+                                                 ? reinterpret_cast<const char*>(rowtab[hsel[i] + tfy]) : nullptr;
+                            cp_async16(a_dst + i * 4096u, rp + (xb[i] + boff), rp ? 16u : 0u);
                         }
-                        if (kPixTma) {
-                            if (tail) { cp_async_wait_all(); fence_proxy_async_smem(); }
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive(full_bar + 8 * stage);
-                        } else {
-                            cp_async_mbar_arrive_noinc(full_bar + 8 * stage);
-                        }
+                        cp_async_mbar_arrive_noinc(full_bar + 8 * stage);
                         if (++stage == NS) { stage = 0; phase ^= 1; }
                     }
                     continue;
@@ -694,22 +723,28 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
     } else if (warp == kMmaWarp) {
         // ======================================= MMA issuer ==============================
         int stage = 0, buf = 0;
-        uint32_t phase = 0, bphase = 0;
-        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x) {
+        uint32_t phase = 0, bphase = 0, tile_par = 0;
+        for (long long w = blockIdx.x; w < p.total_tiles; w += gridDim.x, tile_par ^= 1u) {
             mbar_wait(tempty_bar + 8 * buf, bphase ^ 1);        // epilogue has drained this accumulator
             tc_fence_after();
             for (int kb = 0; kb < p.nkb; ++kb) {
                 mbar_wait(full_bar + 8 * stage, phase);
+                if (kPixTma && kb >= sp.nkb_main)               // pixel half of a tail block: the producers' cp.asyncs
+                    mbar_wait(tail_bar + 8 * (kb - sp.nkb_main), tile_par);
                 fence_proxy_async_smem();                       // producers' cp.async data -> async-proxy reads
                 tc_fence_after();
                 if (lane == 0) {
                     const uint64_t dpix = make_smem_desc(base + stage * kAStageBytes);
                     const uint64_t dwgt = make_smem_desc(base + w_off + stage * kSwWStageBytes);
+                    if (!(p.dbg & 512)) {
 #pragma unroll
-                    for (int ks = 0; ks < kBlockK / 8; ++ks)
-                        umma_tf32(tmem_base + (uint32_t)(buf * 256), dwgt + 2 * ks, dpix + 2 * ks, sp.sw_idesc,
-                                  (kb | ks) != 0 ? 1u : 0u);
+                        for (int ks = 0; ks < kBlockK / 8; ++ks)
+                            umma_tf32(tmem_base + (uint32_t)(buf * 256), dwgt + 2 * ks, dpix + 2 * ks, sp.sw_idesc,
+                                      (kb | ks) != 0 ? 1u : 0u);
+                    }
                     umma_commit(empty_bar + 8 * stage);
+                    if (kPixTma && kb + NS >= sp.nkb_main && kb + NS < p.nkb)      // the next user of this stage is a tail block
+                        umma_commit(tail_free + 8 * (kb + NS - sp.nkb_main));
                     if (kb == p.nkb - 1) umma_commit(tfull_bar + 8 * buf);
                 }
                 __syncwarp();
@@ -734,15 +769,14 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                 mbar_wait(empty_bar + 8 * stage, phase ^ 1);
                 if (lane == 0) {
                     const uint32_t fb = full_bar + 8 * stage;
-                    if (kPixTma && kb < sp.nkb_main) {
-                        // filter row fy = kb: input row S*(cr0+pi) + fy = S*(cr0 + pi + fy/S) + fy%S
-                        mbar_arrive_expect_tx(fb, (uint32_t)(KO * 128) + sp.pix_bytes);
+                    // dbg 64 / 128: timing experiments without the pixel / weight loads (results are garbage)
+                    const bool pix = kPixTma && kb < sp.nkb_main && !(p.dbg & 64);
+                    const bool wgt = !(p.dbg & 128);
+                    mbar_arrive_expect_tx(fb, (wgt ? (uint32_t)(KO * 128) : 0u) + (pix ? sp.pix_bytes : 0u));
+                    if (pix)    // filter row fy = kb: input row S*(cr0+pi) + fy = S*(cr0 + pi + fy/S) + fy%S
                         tma_load_4d(base + stage * kAStageBytes, &pm.m[kb % g.S], 0, pcc0,
                                     pcr0 + kb / g.S - g.seg[0].base / g.S, pn, fb);
-                    } else {
-                        mbar_arrive_expect_tx(fb, (uint32_t)(KO * 128));
-                    }
-                    tma_load_2d(base + w_off + stage * kSwWStageBytes, &tmapW, kb * kBlockK, 0, fb);
+                    if (wgt) tma_load_2d(base + w_off + stage * kSwWStageBytes, &tmapW, kb * kBlockK, 0, fb);
                 }
                 __syncwarp();
                 if (++stage == NS) { stage = 0; phase ^= 1; }
@@ -766,7 +800,55 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
             const int pr0 = g.p0 + tr_i * p.PR, pc0 = tc_i * p.PC;
             mbar_wait(tfull_bar + 8 * buf, bphase);
             tc_fence_after();
-            if (live) {
+            if (live && sp.regpool && !(p.dbg & 256)) {
+                // Lane = channel and TMEM columns = pixel slots, so a 3x3 window is nine registers of ONE lane:
+                // three 16-column loads (conv rows 2pr, 2pr+1, 2pr+2 of the tile; TC <= 16) and the row is pooled
+                // without touching shared memory.  The stores are 128 B per pixel (32 channels of the warp).
+                for (int pr = half; pr < p.PR; pr += 2) {
+                    const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * 256 + 2 * pr * p.TC);
+                    uint32_t ra[16], rb[16], rc[16];
+                    tmem_ld16(t0, ra);
+                    tmem_ld16(t0 + (uint32_t)p.TC, rb);
+                    tmem_ld16(t0 + (uint32_t)(2 * p.TC), rc);
+                    const int prg = pr0 + pr;
+                    const bool row_ok = prg < g.p1 && prg < g.Hp && ch < KO;
+                    float* orow = out + (((size_t)n * g.out_slab + (prg - g.out_base)) * g.Wp) * KO + ch;
+                    float* mrow[B200_MAX_MIRROR] = {nullptr, nullptr, nullptr, nullptr};
+                    bool pushed = false;
+                    if (g.n_mirror > 0) {
+#pragma unroll
+                        for (int m = 0; m < B200_MAX_MIRROR; ++m) {
+                            const bool in = m < g.n_mirror && prg >= g.mirror[m].lo && prg < g.mirror[m].hi;
+                            if (in)
+                                mrow[m] = g.mirror[m].ptr +
+                                          (((size_t)n * g.mirror[m].slab + (prg - g.mirror[m].base)) * g.Wp) * KO + ch;
+                            pushed |= in;
+                        }
+                    }
+#pragma unroll
+                    for (int pc = 0; pc < 7; ++pc) {
+                        if (pc < p.PC) {
+                            float mx = fmaxf(fmaxf(__uint_as_float(ra[2 * pc]), __uint_as_float(ra[2 * pc + 1])),
+                                             __uint_as_float(ra[2 * pc + 2]));
+                            mx = fmaxf(mx, fmaxf(fmaxf(__uint_as_float(rb[2 * pc]), __uint_as_float(rb[2 * pc + 1])),
+                                                 __uint_as_float(rb[2 * pc + 2])));
+                            mx = fmaxf(mx, fmaxf(fmaxf(__uint_as_float(rc[2 * pc]), __uint_as_float(rc[2 * pc + 1])),
+                                                 __uint_as_float(rc[2 * pc + 2])));
+                            float val = fmaxf(mx + bch, 0.f);
+                            if (p.round_out) val = to_tf32(val);
+                            const int pcg = pc0 + pc;
+                            if (row_ok && pcg < g.Wp) {
+                                orow[(size_t)pcg * KO] = val;
+                                if (pushed) {
+#pragma unroll
+                                    for (int m = 0; m < B200_MAX_MIRROR; ++m)
+                                        if (mrow[m]) mrow[m][(size_t)pcg * KO] = val;
+                                }
+                            }
+                        }
+                    }
+                }
+            } else if (live && !(p.dbg & 256)) {               // dbg 256: timing experiment without the epilogue's work
                 for (int pr = half; pr < p.PR; pr += 2) {
                     // conv rows 2pr..2pr+2 = slots [col0, col0 + 3*TC); load whole 32-column groups
                     const int col0 = 2 * pr * p.TC;
@@ -841,7 +923,7 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
 
 
 // ------------------------------------------ double-buffered kernel (C % 32 == 0 layers) ----
-// DRAFT, off by default (B200_TC_DB=1), not yet run on a GPU: DESIGN.md §6 step 1.
+// Selected with conv2=db (Policy); the fallback of the pair kernels for geometries they refuse.
 // tc_block_kernel<false> fills all of TMEM with one 256-pixel tile and its producer warps are its
 // epilogue warps, so drain, max-pool and LRN (55 us of conv2's 282 us) never overlap an MMA.  Here a
 // tile is 128 pixel slots (one M=128 accumulator of N <= 256 columns), TMEM holds two of them, and
@@ -1052,7 +1134,7 @@ tc_block_db_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_const
 
 
 // ------------------------------------------ CTA-pair kernel (stride-1 layers, C % 32 == 0) ----
-// DRAFT, off by default (B200_TC_PAIR=1), not yet run on a GPU: DESIGN.md §6 step 1, second half.
+// Selected with conv2=pair (Policy); the channel-split pair kernel below is the default.
 // tc_block_db_kernel overlaps the epilogue but streams the whole weight k-block (32 KB) into every SM for only
 // 128 pixels: 48 KB per 640 MMA cycles is more than an SM can take in from L2, and it runs at ~80 % of the
 // MMA rate.  Here two CTAs of a cluster form a tcgen05 pair (cta_group::2): each stages its own 128 pixel rows
@@ -1616,7 +1698,9 @@ bool plan_tiles(const b200_block_geom* g, TcParams* p, int max_nacc = 2) {
                 const double tile_cycles = nkb * per_kb + 14000.0 + nacc * (g->K / 32) * 900.0 +
                                            (g->lrn.N_lrn > 0 ? 20000.0 : 0.0);
                 const long waves = (tiles * (long)g->N + kPlanSms - 1) / kPlanSms;
-                const double cost = waves * tile_cycles + slots * 1e-3;
+                // conv1 kernel: tiles at most 15 conv columns wide pool in registers (no smem strips, deeper ring)
+                const double wide = (is_patch_mode(g->C) && g->K <= 128 && g->lrn.N_lrn == 0 && TC > 15) ? 0.5 : 0.0;
+                const double cost = waves * tile_cycles + slots * 1e-3 + wide;
                 if (best < 0 || cost < best) {
                     best = cost;
                     p->PR = PR; p->PC = PC; p->TR = TR; p->TC = TC; p->nacc = nacc;
@@ -1666,6 +1750,20 @@ int fill_params(const b200_block_geom* g, TcParams* p, int flags, int max_nacc =
 }
 
 // swapped kernel: layout [pixel stages | weight stages | patch | 4 epilogue strips | ctl]
+// smem layout of the conv1 kernel for a given ring depth: [pixel stages | weight stages | patch | strips | ctl]
+int layout_swapped(SwParams* sp, int nstages) {
+    TcParams& p = sp->t;
+    sp->nstages = nstages;
+    const size_t stages = (size_t)nstages * (kAStageBytes + kSwWStageBytes);
+    const size_t patch_bytes = sp->direct ? 0 : (size_t)p.patch_rows * p.patch_pitch * 4;
+    p.patch_off = (uint32_t)stages;
+    sp->strip_off = (uint32_t)((stages + patch_bytes + 15) & ~(size_t)15);
+    sp->strip_bytes = sp->regpool ? 0u : (uint32_t)(32 * sp->nload * kCbufPitch * 4);
+    sp->sw_ctl_off = (uint32_t)((sp->strip_off + kSwEpiWarps * (size_t)sp->strip_bytes + 15) & ~(size_t)15);
+    const size_t total = 1024 + sp->sw_ctl_off + 112 + kRowTab * 8 + 128 * 4 + 64;
+    return total > 227 * 1024 ? B200_ERR_UNSUPPORTED : B200_OK;
+}
+
 int fill_swapped(const b200_block_geom* g, SwParams* sp, int flags) {
     int rc = fill_params(g, &sp->t, flags);
     if (rc != B200_OK) return rc;
@@ -1677,18 +1775,11 @@ int fill_swapped(const b200_block_geom* g, SwParams* sp, int flags) {
     // and row sizes multiples of 4 floats): cp.async from global, no smem patch, no smem->smem im2col
     sp->direct = (direct_eligible(g) && (p.TR - 1) * g->S + g->F <= kRowTab) ? 1 : 0;
     sp->cpr = fcpad(g->F, g->C) / 4;
-    sp->nstages = sp->direct ? 3 : 2;
-    const size_t stages = (size_t)sp->nstages * (kAStageBytes + kSwWStageBytes);
-    const size_t patch_bytes = sp->direct ? 0 : (size_t)p.patch_rows * p.patch_pitch * 4;
-    p.patch_off = (uint32_t)stages;
-    sp->strip_off = (uint32_t)((stages + patch_bytes + 15) & ~(size_t)15);
-    sp->strip_bytes = (uint32_t)(32 * sp->nload * kCbufPitch * 4);
-    sp->sw_ctl_off = (uint32_t)((sp->strip_off + kSwEpiWarps * (size_t)sp->strip_bytes + 15) & ~(size_t)15);
+    // register pooling: a pooled row is three 16-column TMEM loads that stay inside the accumulator
+    sp->regpool = (p.PC <= 7 && (p.TR - 1) * p.TC + 16 <= 128 * p.nacc && !(policy().dbg & 2048)) ? 1 : 0;
     // D = channels x pixels: M = 128 (K_out rows padded), N = pixel slots
     sp->sw_idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)((128 * p.nacc) >> 3) << 17) | ((128u >> 4) << 24);
-    const size_t total = 1024 + sp->sw_ctl_off + 112 + kRowTab * 8 + 128 * 4 + 64;
-    if (total > 227 * 1024) return B200_ERR_UNSUPPORTED;
-    return B200_OK;
+    return layout_swapped(sp, sp->direct ? 3 : 2);
 }
 
 // double-buffered kernel: layout [A stages | B stages | 2 cbuf | pbuf | ctl]
@@ -1735,6 +1826,7 @@ bool try_pixel_tma(const TcConv* t, const b200_block_geom* g, SwParams* sp, PixM
         }
     }
     if (g->S < 1 || g->S > 4 || g->seg[0].base % g->S != 0 || g->P != 0) return false;
+    if (g->F < 4 || t->nkb_tma - g->F > 2) return false;             // tail handshake: two barriers, ring <= 4 deep
     const TcParams& p = sp->t;
     if (p.TC > 256 || p.TR > 256) return false;
     EncodeTiledFn enc = get_encode();
@@ -1760,6 +1852,13 @@ bool try_pixel_tma(const TcConv* t, const b200_block_geom* g, SwParams* sp, PixM
     for (int r = g->S; r < 4; ++r) maps.m[r] = maps.m[0];
     *pm = maps;
     sp->pix_bytes = (uint32_t)(kBlockK * p.TC * p.TR * 4);
+    if (sp->regpool && !(policy().dbg & 1024)) {      // the smem the strips no longer need buys a deeper ring
+        const int keep = sp->nstages;
+        if (layout_swapped(sp, 4) != B200_OK) layout_swapped(sp, keep);
+    }
+    if (getenv("B200_TC_VERBOSE"))
+        fprintf(stderr, "[b200 tc] conv1: pixel operand by TMA, tile %dx%d conv pixels, %d stages, pooling in %s\n",
+                p.TR, p.TC, sp->nstages, sp->regpool ? "registers" : "smem strips");
     return true;
 }
 
@@ -2070,7 +2169,6 @@ extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const 
         SwParams sp;
         memset(&sp, 0, sizeof(sp));
         if (fill_swapped(g, &sp, flags) == B200_OK) {       // else fall through to the generic kernel
-            const size_t smem = smem_bytes_swapped(sp);
             const unsigned grid = (unsigned)(sp.t.total_tiles < sms ? sp.t.total_tiles : sms);
             PixMaps pm;
             memset(&pm, 0, sizeof(pm));
@@ -2080,7 +2178,9 @@ extern "C" int b200_tc_block(void* handle, const float* bias, float* out, const 
                 sp.nkb_main = g->F;
                 sp.t.nkb = t->nkb_tma;
             }
-            if (row_order && try_pixel_tma(t, g, &sp, &pm)) {
+            const bool pix_tma = row_order && try_pixel_tma(t, g, &sp, &pm);   // may deepen the ring: size smem after it
+            const size_t smem = smem_bytes_swapped(sp);
+            if (pix_tma) {
                 B200_CUDA_TRY(cudaFuncSetAttribute(tc_block_swapped_kernel<true>,
                                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
                 tc_block_swapped_kernel<true><<<grid, kSwThreads, smem, (cudaStream_t)stream>>>(t->tmap_tma, sp, bias,

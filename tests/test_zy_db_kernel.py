@@ -24,7 +24,7 @@ def _forward(cfg, x, w, **policy):
         y2 = e.forward(x.cuda()).clone()          # second forward: barrier phases and TMEM buffers wrap
         e.check_status()
     finally:
-        tc.set_policy(conv2="auto", conv1="auto")
+        tc.set_policy(conv2="auto", conv1="auto", dbg=0)
     return y.cpu(), y2.cpu()
 
 
@@ -48,6 +48,20 @@ def test_conv1_loaders_bit_identical(batch, hw):
     b, b2 = _forward(cfg, x, w, conv1="auto")
     assert torch.equal(a, a2) and torch.equal(b, b2)
     assert torch.equal(a, b), f"TMA-fed conv1 differs from cp.async-fed: {float((a - b).abs().max()):.3e}"
+
+
+@pytest.mark.parametrize("batch,hw", [(6, 227), (3, 99), (2, 131), (5, 163)])
+def test_conv1_all_tma_and_register_pooling_bit_identical(batch, hw):
+    """conv1 with every k-block by TMA (5-D tail maps), a 4-stage ring and the 3x3 pooling done in registers
+    against the same kernel with cp.async tails (dbg 1024) and / or the shared-memory strips (dbg 2048)."""
+    cfg = default_config(H=hw, W=hw, batch=batch, init=INIT_RAND, seed=6, precision="tf32")
+    x, w = make_problem(cfg)
+    ref, ref2 = _forward(cfg, x, w, dbg=1024 | 2048)
+    assert torch.equal(ref, ref2)
+    for knob in (0, 1024, 2048):
+        y, y2 = _forward(cfg, x, w, dbg=knob)
+        assert torch.equal(y, ref), f"dbg={knob} differs: max |diff| {float((y - ref).abs().max()):.3e}"
+        assert torch.equal(y2, ref), f"dbg={knob}: second forward differs"
 
 
 @pytest.mark.parametrize("graph", [False, True])
