@@ -44,16 +44,22 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 // returns true when the flag reached the target, false on watchdog expiry (status latched)
 __device__ __forceinline__ bool wait_flag_ge(const int* flag, int target, int* status,
                                              unsigned long long timeout_ns) {
-    if (ld_acquire_sys(flag) - target >= 0) return true;
-    const unsigned long long t0 = globaltimer_ns();
+    unsigned spins = 0;
+    unsigned long long t0 = 0;
     while (true) {
         if (ld_acquire_sys(flag) - target >= 0) return true;
-        if (status && *(volatile int*)status != 0) return false;          // someone already failed
-        if (globaltimer_ns() - t0 > timeout_ns) {
-            if (status) atomicCAS(status, 0, B200_ERR_TIMEOUT);
-            return false;
+        // the first polls are back to back (a flag that is about to flip is seen at load latency); the error latch
+        // and the timer — the expensive reads — are looked at every 64th poll only
+        if ((++spins & 63) == 0) {
+            if (status && *(volatile int*)status != 0) return false;      // someone already failed
+            const unsigned long long now = globaltimer_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > timeout_ns) {
+                if (status) atomicCAS(status, 0, B200_ERR_TIMEOUT);
+                return false;
+            }
         }
-        __nanosleep(64);
+        if (spins > 32) __nanosleep(32);
     }
 }
 // Arrival signals of one finished tile that produced pooled rows [r0, r1): called by ONE thread after a barrier

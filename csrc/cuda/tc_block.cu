@@ -60,7 +60,7 @@ struct TcParams {
     int tmem_cols;
     int any_flag;
     int dbg;                     // perf experiments only: 1 skip A copies, 2 skip B TMA, 4 skip epilogue math;
-                                 // conv1 kernel: 64 skip pixel TMA, 128 skip weight TMA, 256 skip epilogue, 512 skip MMAs;
+                                 // conv1 kernel: 64 skip pixel TMA, 128 skip weight TMA, 256 skip epilogue, 512 skip MMAs, 4096 skip the tail copies;
                                  // plan-time: 1024 keep the 3-stage ring, 2048 pool through smem strips
     int round_out;               // round stored outputs to TF32 (next layer's A operand is then exact)
     int FCpad;                   // patch mode: floats per filter row in K (F*C rounded up to 4)
@@ -477,13 +477,16 @@ tc_block_kernel(const __grid_constant__ CUtensorMap tmapB, const __grid_constant
 //     barrier anywhere in the epilogue.
 constexpr int kSwThreads = 576;                     // 8 producer + MMA + TMA + 8 epilogue warps
 constexpr int kSwEpiWarps = 8;                      // two per TMEM lane quarter: even / odd pooled rows
-constexpr int kSwWStageBytes = 128 * 128;            // weight stage: 128 rows (K_out rows valid) x 128 B
+constexpr int kSwCtlHead = 208;                      // barriers + TMEM slot in front of the row table
+constexpr int kSwCtlBytes = kSwCtlHead + kRowTab * 8 + 128 * 4;
+constexpr int kSwMaxStages = 6;
 
 struct SwParams {
     TcParams t;
     int nload;                                       // 32-column TMEM loads per pooled row (3*TC slots)
     uint32_t strip_off, strip_bytes;                 // per-epilogue-warp smem strip
     uint32_t sw_ctl_off;
+    uint32_t w_stage_bytes;                          // one weight slot: K_out rows x 128 B, whole 1 KB swizzle atoms
     uint32_t sw_idesc;
     int direct;                                      // 1: B rows are cp.async'd straight from global memory
     int nstages;                                     // 2 (patch) or 3 (direct)
@@ -516,21 +519,22 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
     const int NS = sp.nstages;
-    const uint32_t w_off = NS * kAStageBytes;                 // pixel stages first, then weight stages
-    const uint32_t full_bar = base + sp.sw_ctl_off;           // [4]
-    const uint32_t empty_bar = full_bar + 32;                 // [4]
-    const uint32_t tfull_bar = full_bar + 64;                 // [2] accumulator ready
-    const uint32_t tempty_bar = full_bar + 80;                // [2] accumulator drained
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + sp.sw_ctl_off + 96);
-    const float** rowtab = reinterpret_cast<const float**>(gbase + sp.sw_ctl_off + 112);
-    float* s_bias = reinterpret_cast<float*>(gbase + sp.sw_ctl_off + 112 + kRowTab * 8);
+    const uint32_t wsb = sp.w_stage_bytes;                    // weight slots first (K_out rows x 128 B each), then the
+    const uint32_t pixs = base + NS * wsb;                     // pixel stages: the MMA's rows K_out..127 read on into smem we own
+    const uint32_t full_bar = base + sp.sw_ctl_off;           // [8]
+    const uint32_t empty_bar = full_bar + 64;                 // [8]
+    const uint32_t tfull_bar = full_bar + 128;                // [2] accumulator ready
+    const uint32_t tempty_bar = full_bar + 144;               // [2] accumulator drained
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(gbase + sp.sw_ctl_off + 160);
+    const float** rowtab = reinterpret_cast<const float**>(gbase + sp.sw_ctl_off + kSwCtlHead);
+    float* s_bias = reinterpret_cast<float*>(gbase + sp.sw_ctl_off + kSwCtlHead + kRowTab * 8);
     // Pixel-TMA mode, tail k-block t (0 or 1) of every tile: the producers cp.async its pixel half into the ring stage
     // the block will use.  tail_free[t]: that stage's previous occupant (k-block nkb_main + t - NS of the same tile) has
     // been consumed; tail_bar[t]: the copies have landed.  Both complete once per tile, so their parity is the tile's;
     // the ring's own empty barriers cannot be used here because the producers skip the main blocks and a parity wait
     // is only safe for a waiter that follows every phase.
-    const uint32_t tail_bar = full_bar + 112 + kRowTab * 8 + 128 * 4;    // [2]
-    const uint32_t tail_free = tail_bar + 16;                            // [2]
+    const uint32_t tail_bar = full_bar + 176;                 // [2]
+    const uint32_t tail_free = full_bar + 192;                // [2]
     float* patch = reinterpret_cast<float*>(gbase + p.patch_off);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -621,14 +625,14 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                         const int tt = kb - sp.nkb_main;
                         const int st = (int)((tile_it * p.nkb + kb) % NS);
                         mbar_wait(tail_free + 8 * tt, (uint32_t)(tile_it & 1));
-                        const uint32_t a_dst = base + st * kAStageBytes + dst0;
+                        const uint32_t a_dst = pixs + st * kAStageBytes + dst0;
                         const int tfy = 8 * tt + j;
 #pragma unroll
                         for (int i = 0; i < 8; ++i) {
                             if (i >= 4 * p.nacc) break;
                             const char* rp = (tfy < g.F && hsel[i] >= 0)
                                                  ? reinterpret_cast<const char*>(rowtab[hsel[i] + tfy]) : nullptr;
-                            cp_async16(a_dst + i * 4096u, rp + (xb[i] + 128), rp ? 16u : 0u);
+                            if (!(p.dbg & 4096)) cp_async16(a_dst + i * 4096u, rp + (xb[i] + 128), rp ? 16u : 0u);
                         }
                         cp_async_mbar_arrive_noinc(tail_bar + 8 * tt);
                     }
@@ -641,7 +645,7 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                     for (int kb = 0; kb < p.nkb; ++kb) {
                         mbar_wait(empty_bar + 8 * stage, phase ^ 1);
                         const bool tail = kb >= sp.nkb_main;
-                        const uint32_t a_dst = base + stage * kAStageBytes + dst0;
+                        const uint32_t a_dst = pixs + stage * kAStageBytes + dst0;
                         const int tfy = tail ? 8 * (kb - sp.nkb_main) + j : kb;
                         const int boff = tail ? 128 : 16 * j;
 #pragma unroll
@@ -660,7 +664,7 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                 while (ch >= sp.cpr) { ch -= sp.cpr; ++fy; }
                 for (int kb = 0; kb < p.nkb; ++kb) {
                     mbar_wait(empty_bar + 8 * stage, phase ^ 1);
-                    const uint32_t a_dst = base + stage * kAStageBytes + dst0;
+                    const uint32_t a_dst = pixs + stage * kAStageBytes + dst0;
                     const bool kv = fy < g.F;                   // beyond F*F*C: zero columns of the K padding
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
@@ -699,7 +703,7 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
             int pfy = (4 * j) / p.FCpad, pt = (4 * j) - pfy * p.FCpad;
             for (int kb = 0; kb < p.nkb; ++kb) {
                 mbar_wait(empty_bar + 8 * stage, phase ^ 1);
-                const uint32_t a_dst = base + stage * kAStageBytes + dst0;
+                const uint32_t a_dst = pixs + stage * kAStageBytes + dst0;
                 const float* src = patch + pfy * p.patch_pitch + pt;
                 float4 v[8];                                    // all loads first: the stores are asm
 #pragma unroll                                                  // volatile and would fence each load
@@ -734,8 +738,8 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                 fence_proxy_async_smem();                       // producers' cp.async data -> async-proxy reads
                 tc_fence_after();
                 if (lane == 0) {
-                    const uint64_t dpix = make_smem_desc(base + stage * kAStageBytes);
-                    const uint64_t dwgt = make_smem_desc(base + w_off + stage * kSwWStageBytes);
+                    const uint64_t dpix = make_smem_desc(pixs + stage * kAStageBytes);
+                    const uint64_t dwgt = make_smem_desc(base + stage * wsb);
                     if (!(p.dbg & 512)) {
 #pragma unroll
                         for (int ks = 0; ks < kBlockK / 8; ++ks)
@@ -774,9 +778,9 @@ tc_block_swapped_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_
                     const bool wgt = !(p.dbg & 128);
                     mbar_arrive_expect_tx(fb, (wgt ? (uint32_t)(KO * 128) : 0u) + (pix ? sp.pix_bytes : 0u));
                     if (pix)    // filter row fy = kb: input row S*(cr0+pi) + fy = S*(cr0 + pi + fy/S) + fy%S
-                        tma_load_4d(base + stage * kAStageBytes, &pm.m[kb % g.S], 0, pcc0,
+                        tma_load_4d(pixs + stage * kAStageBytes, &pm.m[kb % g.S], 0, pcc0,
                                     pcr0 + kb / g.S - g.seg[0].base / g.S, pn, fb);
-                    if (wgt) tma_load_2d(base + w_off + stage * kSwWStageBytes, &tmapW, kb * kBlockK, 0, fb);
+                    if (wgt) tma_load_2d(base + stage * wsb, &tmapW, kb * kBlockK, 0, fb);
                 }
                 __syncwarp();
                 if (++stage == NS) { stage = 0; phase ^= 1; }
@@ -1340,6 +1344,7 @@ struct CsParams {
     uint32_t strip_off, pbuf_off, xh_off, cs_ctl_off;
     uint32_t pix_bytes;                               // bytes of one pixel box (32 x TC x HR floats)
     uint32_t idesc2;                                  // M = 256, N = 256
+    int regpool;                                      // 3x3 pooling in registers (every 16-column row load fits its half)
 };
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kCsThreads, 1)
@@ -1420,9 +1425,13 @@ tc_block_cs_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_const
                 mbar_wait(empty_bar + 8 * stage, phase ^ 1);
                 if (lane == 0) {
                     const uint32_t fb = full_bar + 8 * stage;
-                    if (rank == 0) mbar_arrive_expect_tx(fb, 2u * (cp.pix_bytes + (uint32_t)kCsWStageBytes));
-                    tma2_load_4d(base + stage * kCsPixStageBytes, &tmapX, cch * kBlockK, cc0 + fx - g.P, y0 + fy, n, fb);
-                    tma2_load_2d(base + w_off + stage * kCsWStageBytes, &tmapW, kb * kBlockK, (int)rank * 128, fb);
+                    const bool lpix = !(p.dbg & 64), lwgt = !(p.dbg & 128);     // timing experiments (garbage results)
+                    if (rank == 0)
+                        mbar_arrive_expect_tx(fb, 2u * ((lpix ? cp.pix_bytes : 0u) + (lwgt ? (uint32_t)kCsWStageBytes : 0u)));
+                    if (lpix)
+                        tma2_load_4d(base + stage * kCsPixStageBytes, &tmapX, cch * kBlockK, cc0 + fx - g.P, y0 + fy, n, fb);
+                    if (lwgt)
+                        tma2_load_2d(base + w_off + stage * kCsWStageBytes, &tmapW, kb * kBlockK, (int)rank * 128, fb);
                 }
                 __syncwarp();
                 if (++fx == g.F) { fx = 0; if (++fy == g.F) { fy = 0; ++cch; } }
@@ -1445,8 +1454,9 @@ tc_block_cs_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_const
                         const uint64_t dx = make_smem_desc(base + stage * kCsPixStageBytes);
 #pragma unroll
                         for (int ks = 0; ks < kBlockK / 8; ++ks)
-                            umma2_tf32(tmem_base + (uint32_t)(buf * 256), dw + 2 * ks, dx + 2 * ks, cp.idesc2,
-                                       (kb | ks) != 0 ? 1u : 0u);
+                            if (!(p.dbg & 512))
+                                umma2_tf32(tmem_base + (uint32_t)(buf * 256), dw + 2 * ks, dx + 2 * ks, cp.idesc2,
+                                           (kb | ks) != 0 ? 1u : 0u);
                         umma2_commit_mc(empty_bar + 8 * stage, 3);       // frees the stage in both CTAs
                         if (kb == p.nkb - 1) umma2_commit_mc(tfull_bar + 8 * buf, 3);
                     }
@@ -1483,7 +1493,44 @@ tc_block_cs_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_const
                                                                // already push the next tile's while we read this one)
             mbar_wait(tfull_bar + 8 * buf, bphase);
             tc_fence_after();
-            for (int pr = 0; pr < p.PR; ++pr) {
+            if (cp.regpool && !(p.dbg & 256)) {
+                // Lane = channel, TMEM columns = pixels: the 3x3 window is nine registers of one lane.  Three 16-column
+                // rows roll through registers (row 2pr+2 of one pooled row is row 2pr of the next); no smem strip.
+                uint32_t ra[16], rb[16], rc[16];
+                const uint32_t tq = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * 256);
+                tmem_ld16(tq + (uint32_t)row_col(0), rc);
+                for (int pr = 0; pr < p.PR; ++pr) {
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) ra[c] = rc[c];
+                    tmem_ld16(tq + (uint32_t)row_col(2 * pr + 1), rb);
+                    tmem_ld16(tq + (uint32_t)row_col(2 * pr + 2), rc);
+                    const int prg = pr0 + pr;
+#pragma unroll
+                    for (int pc = 0; pc < 7; ++pc) {
+                        if (pc < p.PC) {
+                            float mx = fmaxf(fmaxf(__uint_as_float(ra[2 * pc]), __uint_as_float(ra[2 * pc + 1])),
+                                             __uint_as_float(ra[2 * pc + 2]));
+                            mx = fmaxf(mx, fmaxf(fmaxf(__uint_as_float(rb[2 * pc]), __uint_as_float(rb[2 * pc + 1])),
+                                                 __uint_as_float(rb[2 * pc + 2])));
+                            mx = fmaxf(mx, fmaxf(fmaxf(__uint_as_float(rc[2 * pc]), __uint_as_float(rc[2 * pc + 1])),
+                                                 __uint_as_float(rc[2 * pc + 2])));
+                            float val = fmaxf(mx + bch, 0.f);
+                            const int pp = pr * p.PC + pc;
+                            if (do_lrn) {
+                                pbuf[pp * kCsPbufPitch + 2 + cl] = val;
+                                if (rank == 1 && cl < 2) st_partner_f32(smem_u32(xh_t + pp * 2 + cl), val);
+                                if (rank == 0 && cl >= 126) st_partner_f32(smem_u32(xh_t + pp * 2 + (cl - 126)), val);
+                            } else {
+                                const int pcg = pc0 + pc;
+                                if (p.round_out) val = to_tf32(val);
+                                if (prg < g.p1 && prg < g.Hp && pcg < g.Wp)
+                                    out_ptr_at(out, n, g.out_slab, g.out_base, prg, g.Wp, pcg, N)[128 * rank + cl] = val;
+                            }
+                        }
+                    }
+                }
+            }
+            for (int pr = 0; pr < ((cp.regpool || (p.dbg & 256)) ? 0 : p.PR); ++pr) {
                 // conv rows 2pr, 2pr+1, 2pr+2 live in row buffers (row % 3); the first is left over from pr-1
                 for (int ri = (pr == 0 ? 0 : 2 * pr + 1); ri <= 2 * pr + 2; ++ri) {
                     const int start = row_col(ri) - row_shift(ri);
@@ -1524,7 +1571,7 @@ tc_block_cs_kernel(const __grid_constant__ CUtensorMap tmapW, const __grid_const
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_leader(tempty_bar + 8 * buf);
-            if (do_lrn) {
+            if (do_lrn && !(p.dbg & 256)) {
                 bar_epilogue();                                 // pbuf is whole; this CTA's halo pushes are issued
                 // two barriers used alternately: the partner can only arrive for tile t+2 after it has seen OUR arrival
                 // for t+1, which we issue after this wait — so a barrier never runs two phases ahead of its waiter
@@ -1750,18 +1797,22 @@ int fill_params(const b200_block_geom* g, TcParams* p, int flags, int max_nacc =
 }
 
 // swapped kernel: layout [pixel stages | weight stages | patch | 4 epilogue strips | ctl]
-// smem layout of the conv1 kernel for a given ring depth: [pixel stages | weight stages | patch | strips | ctl]
+size_t smem_bytes_swapped(const SwParams& sp) { return 1024 + (size_t)sp.sw_ctl_off + kSwCtlBytes + 16; }
+
+// smem layout of the conv1 kernel for a given ring depth: [weight slots | pixel stages | patch | strips | ctl]
 int layout_swapped(SwParams* sp, int nstages) {
     TcParams& p = sp->t;
+    if (nstages > kSwMaxStages) return B200_ERR_UNSUPPORTED;
     sp->nstages = nstages;
-    const size_t stages = (size_t)nstages * (kAStageBytes + kSwWStageBytes);
+    sp->w_stage_bytes = (uint32_t)((p.g.K * 128 + 1023) & ~1023);
+    const size_t stages = (size_t)nstages * (kAStageBytes + sp->w_stage_bytes);
     const size_t patch_bytes = sp->direct ? 0 : (size_t)p.patch_rows * p.patch_pitch * 4;
     p.patch_off = (uint32_t)stages;
     sp->strip_off = (uint32_t)((stages + patch_bytes + 15) & ~(size_t)15);
     sp->strip_bytes = sp->regpool ? 0u : (uint32_t)(32 * sp->nload * kCbufPitch * 4);
     sp->sw_ctl_off = (uint32_t)((sp->strip_off + kSwEpiWarps * (size_t)sp->strip_bytes + 15) & ~(size_t)15);
-    const size_t total = 1024 + sp->sw_ctl_off + 112 + kRowTab * 8 + 128 * 4 + 64;
-    return total > 227 * 1024 ? B200_ERR_UNSUPPORTED : B200_OK;
+    // the MMA reads 128 weight rows per slot: the last slot's rows K_out..127 must still be ours (pixel stages follow)
+    return smem_bytes_swapped(*sp) > 227 * 1024 ? B200_ERR_UNSUPPORTED : B200_OK;
 }
 
 int fill_swapped(const b200_block_geom* g, SwParams* sp, int flags) {
@@ -1826,7 +1877,7 @@ bool try_pixel_tma(const TcConv* t, const b200_block_geom* g, SwParams* sp, PixM
         }
     }
     if (g->S < 1 || g->S > 4 || g->seg[0].base % g->S != 0 || g->P != 0) return false;
-    if (g->F < 4 || t->nkb_tma - g->F > 2) return false;             // tail handshake: two barriers, ring <= 4 deep
+    if (g->F < 4 || t->nkb_tma - g->F > 2) return false;             // tail handshake: two barriers, ring no deeper than F
     const TcParams& p = sp->t;
     if (p.TC > 256 || p.TR > 256) return false;
     EncodeTiledFn enc = get_encode();
@@ -1852,9 +1903,10 @@ bool try_pixel_tma(const TcConv* t, const b200_block_geom* g, SwParams* sp, PixM
     for (int r = g->S; r < 4; ++r) maps.m[r] = maps.m[0];
     *pm = maps;
     sp->pix_bytes = (uint32_t)(kBlockK * p.TC * p.TR * 4);
-    if (sp->regpool && !(policy().dbg & 1024)) {      // the smem the strips no longer need buys a deeper ring
-        const int keep = sp->nstages;
-        if (layout_swapped(sp, 4) != B200_OK) layout_swapped(sp, keep);
+    if (!(policy().dbg & 1024)) {                     // as deep a ring as fits (the strips' smem, when pooling in registers)
+        int ns = sp->nstages;
+        while (ns < kSwMaxStages && ns < g->F && layout_swapped(sp, ns + 1) == B200_OK) ++ns;
+        layout_swapped(sp, ns);
     }
     if (getenv("B200_TC_VERBOSE"))
         fprintf(stderr, "[b200 tc] conv1: pixel operand by TMA, tile %dx%d conv pixels, %d stages, pooling in %s\n",
@@ -1961,11 +2013,12 @@ int fill_cs(const TcConv* t, const b200_block_geom* g, CsParams* cp, CUtensorMap
     if (best_waves < 0) return B200_ERR_UNSUPPORTED;
     p.nkb = num_kblocks(g->F, g->C);
     p.round_out = flags & 1;
-    p.dbg = 0;
+    p.dbg = policy().dbg;
     p.total_tiles = (long long)g->N * p.tiles_r * p.tiles_c;
     for (int s = 0; s < g->nseg; ++s)
         if (g->seg[s].flag) p.any_flag = 1;
     cp->pix_bytes = (uint32_t)(kBlockK * p.TC * cp->HR * 4);
+    cp->regpool = (p.PC <= 7 && (cp->HR - 1) * p.TC + 16 <= 128 && !(policy().dbg & 2048)) ? 1 : 0;
     const size_t strips = 4 * (size_t)kCsStripFloats * 4;
     const size_t pbuf_bytes = (size_t)kMaxPooled * kCsPbufPitch * 4;
     const size_t xh_bytes = 2 * (size_t)kMaxPooled * 2 * 4;
@@ -2003,9 +2056,7 @@ size_t smem_bytes_pair(const PairParams& pp) {
     return 1024 + (size_t)pp.pair_ctl_off + 176 + kMaxPooled * 8 + (size_t)pp.t.g.K * 4 + 64;
 }
 
-size_t smem_bytes_swapped(const SwParams& sp) {
-    return 1024 + (size_t)sp.sw_ctl_off + 112 + kRowTab * 8 + 128 * 4 + 64;
-}
+
 
 size_t smem_bytes(const TcParams& p) {
     return 1024 + (size_t)p.ctl_off + 16 * p.stages + 32 + kRowTab * 8 + kMaxPooled * 8 +

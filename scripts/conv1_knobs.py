@@ -36,7 +36,9 @@ e = single_gpu_engine(cfg, w, "cuda:0")
 e.forward(xd); torch.cuda.synchronize()
 names = {0: "as shipped", 64: "no pixel TMA", 128: "no weight TMA", 192: "no TMA at all", 256: "no epilogue work",
          512: "no MMAs", 64 | 128 | 256: "no TMA, no epilogue (MMA issue only)", 256 | 512: "loads only",
-         64 | 256 | 512: "weight loads only", 128 | 256 | 512: "pixel loads only"}
+         64 | 256 | 512: "weight loads only", 128 | 256 | 512: "pixel loads only", 4096: "no tail copies",
+         4096 | 256 | 512: "TMA loads only, no tail copies", 4096 | 64 | 128 | 256: "MMA issue only, no tail copies",
+         4096 | 64 | 128 | 256 | 512: "handshakes only"}
 for k in [int(v) for v in os.environ.get("KNOBS", ",".join(str(k) for k in names)).split(",")]:
     tc.set_policy(dbg=k)
     t1 = timeit(lambda: e.stage_block1(0))
