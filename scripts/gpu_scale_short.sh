@@ -1,9 +1,9 @@
 #!/usr/bin/env bash
-# The few multi-GPU numbers that matter most, in under five minutes of box time
-# (gpurun --gpus 8 --timeout 300 -- 'bash scripts/gpu_scale_short.sh').  Logs under gpurun_out/r2_8gpu/.
+# The few multi-GPU numbers that matter most, in about two minutes of box time
+# (gpurun --gpus 8 --timeout 200 -- 'bash scripts/gpu_scale_short.sh').  Logs under gpurun_out/r2_8gpu_v2/.
 set -u
 ROOT="$(cd "$(dirname "${BASH_SOURCE[0]}")/.." && pwd)"; cd "$ROOT"
-OUT=gpurun_out/r2_8gpu; mkdir -p $OUT
+OUT=gpurun_out/r2_8gpu_v2; mkdir -p $OUT
 export LD_LIBRARY_PATH=/usr/local/cuda/lib64:${LD_LIBRARY_PATH:-}
 NG=$(nvidia-smi -L | wc -l)
 T0=$(date +%s)
@@ -12,10 +12,15 @@ stamp() { echo "[$(( $(date +%s) - T0 )) s] $*"; }
 for n in 8 4; do
   [ $n -le $NG ] || continue
   stamp "bench ours N=$n"
-  trun 110 $n 2960$n bench.py --gpus $n --steps 20 --warmup 5 --alt 2>$OUT/bench_$n.err | grep "^{" | tee $OUT/bench_ours_$n.json | cut -c1-200
+  trun 90 $n 2960$n bench.py --gpus $n --steps 20 --warmup 5 --alt 2>$OUT/bench_$n.err | grep "^{" | tee $OUT/bench_ours_$n.json | cut -c1-200
 done
-[ 8 -le $NG ] && { stamp "stage timings N=8"; HALOS=push STRATEGIES=halo trun 60 8 29618 scripts/mgpu_experiments.py 2>$OUT/mg_8.err | tee $OUT/mgpu_experiments_np8.log | grep -E "^---|slowest" | cut -c1-170; }
-[ 8 -le $NG ] && { stamp "bench reference N=8"; trun 60 8 29628 bench.py --impl reference --gpus 8 --steps 3 --warmup 1 2>$OUT/benchref_8.err | grep "^{" | tee $OUT/bench_reference_8.json | cut -c1-300; }
-stamp "bench ours N=2"
-trun 80 2 29602 bench.py --gpus 2 --steps 20 --warmup 5 --alt 2>$OUT/bench_2.err | grep "^{" | tee $OUT/bench_ours_2.json | cut -c1-200
+[ 8 -le $NG ] && { stamp "stage timings N=8"; HALOS=push STRATEGIES=halo,recompute trun 60 8 29618 scripts/mgpu_experiments.py 2>$OUT/mg_8.err | tee $OUT/mgpu_experiments_np8.log | grep -E "^---|slowest" | cut -c1-170; }
+for n in 8 4 2; do
+  [ $n -le $NG ] || continue
+  stamp "host link ceiling N=$n"
+  trun 40 $n 2972$n scripts/h2d_roofline.py 2>$OUT/h2d_$n.err | tee $OUT/h2d_roofline_np$n.json | cut -c1-300
+done
+[ 8 -le $NG ] && { stamp "config 4 (2048x2048x3, batch 16) N=8"; HW=2048 BATCH=16 ROWGROUPS=rows HALOS=push,pull STRATEGIES=halo,recompute trun 80 8 29818 scripts/mgpu_experiments.py 2>$OUT/c4_8.err | tee $OUT/config4_2048_np8.log | grep -E "^---|slowest" | cut -c1-170; }
+stamp "config 5 (full network, batch 256) N=$NG"
+PYTHONPATH=. timeout 90 bin/mpirun -np $NG python -m b200cnn.runners.full --batch 256 --iters 10 --row-groups auto 2>$OUT/c5_$NG.err | tee $OUT/config5_full_np$NG.log | grep -E "completed|device_forward|images_per_s"
 stamp done
