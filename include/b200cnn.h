@@ -180,14 +180,20 @@ int b200_simt_block_tiles_rows(const b200_block_geom* g, int lo, int hi);
 int b200_tc_conv_create(const float* w_kcff, int K, int C, int F, void** handle);
 int b200_tc_conv_destroy(void* handle);
 int b200_tc_block(void* handle, const float* bias, float* out, const b200_block_geom* g,
-                  int flags /* bit0: round outputs to TF32 */, void* stream);
+                  int flags /* bit0: round outputs to TF32; bit1: programmatic dependent launch - the kernel may
+                               become resident while the previous kernel in `stream` still runs and waits for its
+                               completion before reading what it wrote (channel-split conv2 kernel; others ignore it) */,
+                  void* stream);
 int b200_tc_block_tiles(const b200_block_geom* g);
 int b200_tc_block_tiles_rows(const b200_block_geom* g, int lo, int hi);
 /* Process-wide kernel choice (default: environment B200_TC_CONV2 / B200_TC_CONV1 at first use, else auto):
  * key "conv2" = auto|single|db|pair|cs (single-buffered, double-buffered TMEM, tcgen05 CTA pair splitting the
  * pixels, CTA pair splitting the channels),
- * key "conv1" = auto|cpasync (pixel operand by TMA when eligible, or always the cp.async loader).
- * All choices produce bit-identical outputs; they differ in speed only. */
+ * key "conv1" = auto|cpasync (pixel operand by TMA when eligible, or always the cp.async loader),
+ * key "pdl" = 1|0 (honour flags bit1 of b200_tc_block; environment B200_TC_PDL),
+ * key "dbg" = integer (timing experiments and plan-time variants of the conv kernels, see TcParams::dbg; 0 in production).
+ * All choices produce bit-identical outputs; they differ in speed only (dbg bits below 1024 switch work off and
+ * produce garbage). */
 int b200_tc_set_policy(const char* key, const char* value);
 
 /* Stand-alone convolution on NCHW device tensors with reference-layout weights [K][C][F][F]
