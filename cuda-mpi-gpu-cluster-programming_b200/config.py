@@ -88,6 +88,10 @@ def add_cli_flags(ap: argparse.ArgumentParser, *, init_default: str = INIT_CONST
     ap.add_argument("--precision", choices=["simt", "tf32"], default="tf32")
     ap.add_argument("--iters", type=int, default=0,
                     help="extra warm device-timed iterations (adds key=value lines)")
+    ap.add_argument("--load-weights", default=None, metavar="FILE",
+                    help="take the parameters from a weight file (utils/checkpoint.py) instead of --init")
+    ap.add_argument("--save-weights", default=None, metavar="FILE",
+                    help="write the parameters this run used to a weight file (rank 0)")
 
 
 def config_from_args(ns: argparse.Namespace, seed_default: Optional[int] = None) -> NetConfig:

@@ -25,6 +25,24 @@ def make_parser(prog: str, *, init_default: str = INIT_CONST, lrn_default: str =
     return ap
 
 
+def weight_flags(cfg, ns, w, rank: int = 0):
+    """--load-weights / --save-weights for blocks 1-2: returns the Blocks12Weights the run uses.  A file of the
+    full-network kind is accepted too (its first two blocks are taken)."""
+    from ..utils import checkpoint as ck
+    load = getattr(ns, "load_weights", None)
+    if load:
+        try:
+            got = ck.load_weights(load)
+            ck.check_against(cfg, got)
+        except (OSError, ValueError) as ex:
+            fail(rank, f"--load-weights {load}: {ex}")
+        w = got if not hasattr(got, "blocks12") else got.blocks12
+    save = getattr(ns, "save_weights", None)
+    if save and rank == 0:
+        ck.save_weights(save, w, meta={"seed": int(cfg.seed), "init": str(cfg.init), "kind": "blocks12"})
+    return w
+
+
 class WallTimer:
     def __enter__(self):
         self.t0 = time.perf_counter()

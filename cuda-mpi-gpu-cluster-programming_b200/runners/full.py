@@ -27,7 +27,7 @@ from ..ops.cpu import fnv1a64
 from ..parallel import dist as bdist
 from ..parallel.symm import DevBuf
 from ..utils import logfmt as L
-from .common import make_parser, fail
+from .common import make_parser, fail, weight_flags
 
 
 def batch_shard(batch: int, rank: int, world: int):
@@ -48,6 +48,17 @@ def main(argv=None) -> int:
         fail(bdist.env_rank_world()[0], "the full-network runner needs one GPU per rank")
     ctx = bdist.init()
     x, w12 = make_problem(cfg)
+    loaded = None
+    if ns.load_weights:                      # a full-network file: every rank maps it and reads only what it uses
+        from ..utils import checkpoint as ck
+        try:
+            loaded = ck.load_weights(ns.load_weights, mmap=True)
+            ck.check_against(cfg, loaded)
+            if not hasattr(loaded, "blocks12"):
+                raise ValueError("a blocks-1-2 file; the full network needs kind 'full'")
+        except (OSError, ValueError) as ex:
+            fail(ctx.rank, f"--load-weights {ns.load_weights}: {ex}")
+        w12 = loaded.blocks12
     from .v4 import _row_groups
     from ..parallel.planner import split_rows
     sess = Session(cfg, w12, dist=ctx if ctx.world > 1 else None, device=ctx.device, precision=cfg.precision,
@@ -55,7 +66,16 @@ def main(argv=None) -> int:
     e = sess.engine
     sh, plan, rp = e.sh, e.plan, e.rp
     feat = ((sh.Hp2 - 3) // 2 + 1) * ((sh.Wp2 - 3) // 2 + 1) * 256
-    w = make_full_weights(w12, seed=cfg.seed, feat=feat)
+    if loaded is not None:
+        if tuple(loaded.w6.shape) != (4096, feat):
+            fail(ctx.rank, f"--load-weights {ns.load_weights}: w6 has shape {tuple(loaded.w6.shape)}, "
+                           f"this input size needs (4096, {feat})")
+        w = loaded
+    else:
+        w = make_full_weights(w12, seed=cfg.seed, feat=feat)
+    if ns.save_weights and ctx.rank == 0:
+        from ..utils import checkpoint as ck
+        ck.save_weights(ns.save_weights, w, meta={"seed": int(cfg.seed), "init": str(cfg.init), "feat": int(feat)})
     tp = TPClassifier(w, sess.symm, ctx.rank, ctx.world, cfg.batch, feat)
     sess.symm.commit()
     # Conv3-5 + pool5 by batch: the ranks that split the rows of one image set share its images out among themselves;

@@ -9,7 +9,7 @@ from ..models.alexnet import forward_cpu
 from ..models.init import make_problem
 from ..ops.cpu import fnv1a64
 from ..utils import logfmt as L
-from .common import make_parser, WallTimer
+from .common import make_parser, WallTimer, weight_flags
 
 
 def main(argv=None) -> int:
@@ -18,6 +18,7 @@ def main(argv=None) -> int:
     L.emit(L.V1_BANNER)
     L.emit("Initializing data and parameters...")
     x, w = make_problem(cfg)
+    w = weight_flags(cfg, ns, w)
     L.emit("Initialization complete.")
     L.emit("Starting AlexNet Serial Forward Pass...")
 

@@ -25,16 +25,18 @@ from ..parallel import dist as bdist
 from ..parallel.planner import make_plan
 from ..shapes import block12_shapes
 from ..utils import logfmt as L
-from .common import make_parser
+from .common import make_parser, weight_flags
 
 TAG_SCATTER, TAG_HALO, TAG_GATHER = 10, 2, 20     # ref uses tags 0/1 (halo1) and 2/3 (halo2)
 
 
-def _bcast_problem(ctx, cfg, need_input: bool):
-    """rank 0 initialises, everybody receives weights (and the input for V2.1)."""
+def _bcast_problem(ctx, cfg, need_input: bool, ns=None):
+    """rank 0 initialises (or loads --load-weights), everybody receives weights (and the input for V2.1)."""
     p1, p2 = cfg.conv1, cfg.conv2
     if ctx.rank == 0:
         x, w = make_problem(cfg)
+        if ns is not None:
+            w = weight_flags(cfg, ns, w, 0)
     else:
         x = torch.empty((cfg.batch, cfg.H, cfg.W, cfg.C)) if need_input else None
         w = Blocks12Weights(torch.empty((p1.K, cfg.C, p1.F, p1.F)), torch.empty(p1.K),
@@ -46,8 +48,8 @@ def _bcast_problem(ctx, cfg, need_input: bool):
     return x, w
 
 
-def run_v21(ctx, cfg):
-    x, w = _bcast_problem(ctx, cfg, need_input=True)
+def run_v21(ctx, cfg, ns=None):
+    x, w = _bcast_problem(ctx, cfg, need_input=True, ns=ns)
     ctx.barrier()
     t0 = time.perf_counter()
     y = forward_cpu(x, w, cfg)
@@ -55,8 +57,8 @@ def run_v21(ctx, cfg):
     return y if ctx.rank == 0 else None, (time.perf_counter() - t0) * 1e3
 
 
-def run_v22(ctx, cfg, strategy="halo"):
-    x, w = _bcast_problem(ctx, cfg, need_input=False)
+def run_v22(ctx, cfg, strategy="halo", ns=None):
+    x, w = _bcast_problem(ctx, cfg, need_input=False, ns=ns)
     sh = block12_shapes(cfg)
     plan = make_plan(cfg, ctx.world, strategy)
     rp = plan.ranks[ctx.rank]
@@ -126,9 +128,9 @@ def main(argv=None, variant="2.2") -> int:
     ctx = bdist.init(device="cpu")
     try:
         if variant == "2.1":
-            y, ms = run_v21(ctx, cfg)
+            y, ms = run_v21(ctx, cfg, ns=ns)
         else:
-            y, ms = run_v22(ctx, cfg, ns.strategy)
+            y, ms = run_v22(ctx, cfg, ns.strategy, ns=ns)
     except Exception as ex:            # fail-stop: MPI_Abort semantics
         L.rank_err(ctx.rank, f"{type(ex).__name__}: {ex}")
         ctx.abort(1)

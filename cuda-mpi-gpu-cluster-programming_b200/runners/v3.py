@@ -16,7 +16,7 @@ from ..models.init import make_problem
 from ..models.session import Session
 from ..ops.cpu import fnv1a64
 from ..utils import logfmt as L
-from .common import make_parser, WallTimer, fail
+from .common import make_parser, WallTimer, fail, weight_flags
 
 
 def warm_device_ms(sess: Session, iters: int) -> float:
@@ -39,6 +39,7 @@ def main(argv=None) -> int:
     if not torch.cuda.is_available():
         fail(0, "CUDA no CUDA-capable device is detected")
     x, w = make_problem(cfg)
+    w = weight_flags(cfg, ns, w)
     xp = x.pin_memory()
     with WallTimer() as t:
         sess = Session(cfg, w, device="cuda:0", precision=cfg.precision)

@@ -26,7 +26,7 @@ from ..models.session import Session
 from ..ops.cpu import fnv1a64
 from ..parallel import dist as bdist
 from ..utils import logfmt as L
-from .common import make_parser, fail
+from .common import make_parser, fail, weight_flags
 from .v3 import warm_device_ms
 
 
@@ -43,6 +43,7 @@ def main(argv=None, variant: str = "v4") -> int:
     ctx = bdist.init()
     try:
         x, w = make_problem(cfg)                  # identical on every rank (seeded): no weight bcast
+        w = weight_flags(cfg, ns, w, ctx.rank)    # or the same file read by every rank
         ctx.barrier()
         t0 = time.perf_counter()
         sess = Session(cfg, w, dist=ctx if ctx.world > 1 else None, device=ctx.device,
@@ -98,6 +99,7 @@ def _oversubscribed(ns, cfg, variant, scatter) -> int:
         from ..ops import cuda as cu
         cu.lib()
         x, w = make_problem(cfg)
+        w = weight_flags(cfg, ns, w, 0)
     ctx.barrier()
     t0 = time.perf_counter()
     y = None
