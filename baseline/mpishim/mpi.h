@@ -1,8 +1,10 @@
 /* mpi.h — the 18-call MPI subset the reference uses, implemented over named pipes.
  *
- * Purpose: BASELINE builds only.  The image ships no MPI, so the UNMODIFIED reference sources
- * (V2.1, V2.2, V4, HW1) are compiled against this header and launched with bin/mpirun, which
- * provides OMPI_COMM_WORLD_RANK/SIZE.  Not product code: the framework itself never uses it.
+ * The image ships no MPI.  Compiled against this header and launched with bin/mpirun (which provides
+ * OMPI_COMM_WORLD_RANK/SIZE): the UNMODIFIED reference sources (V2.1, V2.2, V4, HW1) as same-box baselines, and
+ * the framework's own native MPI programs — the V2 `template` binaries (csrc/apps/v2_main.cpp) and the native
+ * homework skeleton (templates/template.c.template).  With a real MPI installed they build against that instead
+ * (make CXX=mpicxx MPI_INC= MPI_SRC=); the GPU paths never use MPI at all (peer memory + torch.distributed bootstrap).
  *
  * Transport: one FIFO per ordered rank pair under $B200_MPISHIM_DIR (default /tmp/b200mpi_<port>);
  * messages are [tag,int32][bytes,int64][payload]; Isend runs on a helper thread so symmetric

@@ -19,6 +19,39 @@ from ..shapes import conv_out_dim_or_zero, pool_out_dim_or_zero
 _lib = None
 
 
+class PlanBlock(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("F", "S", "P", "F_pool", "S_pool")]
+
+
+class PlanHalo(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("peer", "lo", "hi")]
+
+
+PLAN_MAX_HALO = 8
+
+
+class RankPlanC(C.Structure):
+    """``b200_rank_plan`` of include/b200cnn.h (the native planner's answer for one rank)."""
+    _fields_ = [(n, C.c_int) for n in ("rank", "world", "row_group", "batch_group", "row_groups", "batch_groups",
+                                       "img0", "img1", "out0", "out1", "conv2_0", "conv2_1", "need0", "need1",
+                                       "own0", "own1", "conv1_0", "conv1_1", "in0", "in1", "n_halo", "n_serves")] + \
+               [("halo", PlanHalo * PLAN_MAX_HALO), ("serves", PlanHalo * PLAN_MAX_HALO)] + \
+               [(n, C.c_int) for n in ("Hc1", "Hp1", "Hc2", "Hp2")]
+
+
+def native_plan_rank(cfg, world: int, rank: int, strategy: str = "halo", row_groups: int = 0) -> RankPlanC:
+    """The native planner (csrc/cpu/planner_cpu.cpp) for one rank of ``world``; ``row_groups`` 0 = pure row split."""
+    p1, p2 = cfg.conv1, cfg.conv2
+    b1 = PlanBlock(p1.F, p1.S, p1.P, p1.F_pool, p1.S_pool)
+    b2 = PlanBlock(p2.F, p2.S, p2.P, p2.F_pool, p2.S_pool)
+    out = RankPlanC()
+    rc = lib().b200_plan_rank(cfg.H, cfg.batch, C.byref(b1), C.byref(b2), world,
+                              {"halo": 0, "recompute": 1}[strategy], int(row_groups or 0), rank, C.byref(out))
+    if rc != 0:
+        raise ValueError(f"b200_plan_rank failed with status {rc}")
+    return out
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -41,6 +74,8 @@ def lib():
         L.b200_hw1_init_data.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.b200_hw1_init_data.restype = None
         L.b200_hw1_check.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_double]
+        L.b200_plan_rank.argtypes = [C.c_int, C.c_int, C.POINTER(PlanBlock), C.POINTER(PlanBlock), C.c_int, C.c_int,
+                                     C.c_int, C.c_int, C.POINTER(RankPlanC)]
         _lib = L
     return _lib
 

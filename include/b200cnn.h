@@ -78,6 +78,32 @@ void b200_grand_fill_weights(b200_grand* st, float* out, size_t n);   /* (rand/R
 /* FNV-1a 64 over raw bytes: the output digest summary.md:108 describes but never implements. */
 uint64_t b200_fnv1a64(const void* data, size_t nbytes);
 
+/* Exact row (x batch) decomposition of conv -> pool -> conv -> pool (csrc/cpu/planner_cpu.cpp; the Python planner
+ * pkg/parallel/planner.py is its twin).  Final rows are split base+remainder over the `row_groups` ranks of a group
+ * (0 = all ranks: the reference's pure row split), every group takes its share of the batch, and each earlier layer's
+ * row range follows from the receptive field.  strategy 0 = halo (pool1 rows disjointly owned, the rest read from / pushed
+ * by the peers listed in halo[] / serves[]), 1 = recompute (every rank computes all pool1 rows it needs).  Ranges are
+ * half-open; an empty range is (x, x). */
+typedef struct { int F, S, P, F_pool, S_pool; } b200_plan_block;
+typedef struct { int peer, lo, hi; } b200_plan_halo;
+#define B200_PLAN_MAX_HALO 8
+typedef struct {
+    int rank, world, row_group, batch_group, row_groups, batch_groups;
+    int img0, img1;          /* images of the global batch this rank works on               */
+    int out0, out1;          /* owned final rows (pool2 / LRN2)                             */
+    int conv2_0, conv2_1;    /* conv2 rows computed                                         */
+    int need0, need1;        /* pool1 rows conv2 reads (clipped; outside = zero padding)    */
+    int own0, own1;          /* pool1 rows produced                                         */
+    int conv1_0, conv1_1;    /* conv1 rows computed for them                                */
+    int in0, in1;            /* input rows conv1 reads: the rank's "scatter" slab           */
+    int n_halo, n_serves;
+    b200_plan_halo halo[B200_PLAN_MAX_HALO];     /* pool1 rows [lo,hi) read from `peer`     */
+    b200_plan_halo serves[B200_PLAN_MAX_HALO];   /* pool1 rows [lo,hi) `peer` reads from me */
+    int Hc1, Hp1, Hc2, Hp2;  /* full heights of the four layers                             */
+} b200_rank_plan;
+int b200_plan_rank(int H, int batch, const b200_plan_block* b1, const b200_plan_block* b2, int world,
+                   int strategy, int row_groups, int rank, b200_rank_plan* out);
+
 /* HW1 (ref homeworks/hw1/src/template.c:195-238): C = A*B row block, init, check. */
 void b200_cpu_matmul_f64(const double* A, const double* B, double* C, int rows, int n);
 void b200_hw1_init_data(double* M, int rows, int cols);   /* fixed srand48(1) stream like init_data */

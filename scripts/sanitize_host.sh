@@ -1,6 +1,6 @@
 #!/usr/bin/env bash
 # Host-side memory / undefined-behaviour checking (AddressSanitizer + UBSan) of the native code that runs on the
-# CPU: the oracle library (csrc/cpu) through the native V1 binary, and the MPI-subset shim (baseline/mpishim)
+# CPU: the oracle library and planner (csrc/cpu) through the native V1 and V2 binaries, and the MPI-subset shim (baseline/mpishim)
 # through its self-test at np 1, 2 and 4 and the reference's HW1 under it.  compute-sanitizer is closed on the GPU
 # pool, so this is the checked half; the device half relies on watchdogs and bit-exact multi-rank tests
 # (DESIGN.md 4b).  The reference ships a .clang-tidy that nothing runs (ref final_project/v4_mpi_cuda/.clang-tidy:4).
@@ -17,6 +17,18 @@ run() { echo "\$ $*" >> "$LOG"; "$@" >> "$LOG" 2>&1; local rc=$?; echo "rc=$rc" 
 run g++ -std=c++17 $SAN -ffp-contract=off -fopenmp -Wall -Wextra -Werror -Iinclude \
     csrc/apps/v1_main.cpp csrc/cpu/*.cpp -o "$OUT/v1_asan"
 run "$OUT/v1_asan" --seed 7 --quiet-extras
+
+# 1b. native V2.2 / V2.1 (planner, slab layers, scatter / halo / gather over the MPI subset) at np 1 / 3 / 4
+run gcc $SAN -c -Wall -Wextra -Werror baseline/mpishim/mpishim.c -o "$OUT/mpishim_asan.o"
+run g++ -std=c++17 $SAN -ffp-contract=off -fopenmp -Wall -Wextra -Werror -Iinclude -Ibaseline/mpishim \
+    csrc/apps/v2_main.cpp csrc/cpu/*.cpp "$OUT/mpishim_asan.o" -lpthread -o "$OUT/v22_asan"
+run g++ -std=c++17 $SAN -ffp-contract=off -fopenmp -Wall -Wextra -Werror -DV2_BROADCAST_ALL -Iinclude -Ibaseline/mpishim \
+    csrc/apps/v2_main.cpp csrc/cpu/*.cpp "$OUT/mpishim_asan.o" -lpthread -o "$OUT/v21_asan"
+for np in 1 3 4; do
+  run python bin/mpirun --oversubscribe -np $np "$OUT/v22_asan" --height 99 --width 131 --batch 2 --init rand --seed 7 --quiet-extras
+done
+run python bin/mpirun --oversubscribe -np 2 "$OUT/v22_asan" --height 99 --width 99 --strategy recompute --quiet-extras
+run python bin/mpirun --oversubscribe -np 2 "$OUT/v21_asan" --height 99 --width 99 --quiet-extras
 
 # 2. MPI shim + its self-test, -Wall -Wextra -Werror, at np 1 / 2 / 4 through bin/mpirun
 run gcc $SAN -Wall -Wextra -Werror -Ibaseline/mpishim tests/data/mpi_selftest.c baseline/mpishim/mpishim.c \

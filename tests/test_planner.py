@@ -120,3 +120,36 @@ def test_splitk_and_batch_shard_plans():
         assert parts[0][0] == 0 and parts[-1][1] == batch
         assert all(a[1] == b[0] for a, b in zip(parts, parts[1:]))     # contiguous, disjoint, complete
         assert all(0 <= b1 - b0 <= -(-batch // world) for b0, b1 in parts)
+
+
+def _same_plan(cfg, world, strategy, R):
+    from b200cnn.ops.cpu import native_plan_rank
+    plan = make_plan(cfg, world, strategy, row_groups=R or None)
+    for rp in plan.ranks:
+        c = native_plan_rank(cfg, world, rp.rank, strategy, R)
+        assert (c.row_group, c.batch_group, c.row_groups, c.batch_groups) == \
+            (rp.row_group, rp.batch_group, plan.row_groups, plan.batch_groups)
+        assert (c.img0, c.img1) == tuple(rp.images)
+        for name, rng in (("out", rp.out_rows), ("conv2_", rp.conv2_rows), ("need", rp.pool1_need),
+                          ("own", rp.pool1_own), ("conv1_", rp.conv1_rows), ("in", rp.in_rows)):
+            got = (getattr(c, name + "0"), getattr(c, name + "1"))
+            assert got == tuple(rng) or (got[1] <= got[0] and rng[1] <= rng[0]), (name, got, rng, rp.rank)
+        assert [(h.peer, h.lo, h.hi) for h in c.halo[:c.n_halo]] == list(rp.halo)
+        assert sorted((h.peer, h.lo, h.hi) for h in c.serves[:c.n_serves]) == sorted(rp.serves)
+        sh = plan.shapes
+        assert (c.Hc1, c.Hp1, c.Hc2, c.Hp2) == (sh.Hc1, sh.Hp1, sh.Hc2, sh.Hp2)
+
+
+@pytest.mark.parametrize("world,R", [(1, 0), (2, 0), (3, 0), (4, 0), (8, 0), (4, 2), (8, 2), (8, 4), (6, 3), (16, 0)])
+@pytest.mark.parametrize("strategy", ["halo", "recompute"])
+def test_native_planner_equals_python_planner_227(world, R, strategy):
+    """csrc/cpu/planner_cpu.cpp (the planner a native host uses) against parallel/planner.py, rank by rank."""
+    _same_plan(default_config(batch=13), world, strategy, R)
+
+
+@settings(max_examples=120, deadline=None)
+@given(H=st.integers(min_value=40, max_value=700), batch=st.integers(min_value=0, max_value=9),
+       R=st.integers(min_value=1, max_value=6), B=st.integers(min_value=1, max_value=3),
+       strategy=st.sampled_from(["halo", "recompute"]))
+def test_native_planner_equals_python_planner_any_shape(H, batch, R, B, strategy):
+    _same_plan(default_config(H=H, W=max(H, 67), batch=batch), R * B, strategy, R)
