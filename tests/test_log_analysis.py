@@ -144,3 +144,32 @@ def test_sql_views_and_notebook_figures(tmp_path):
         assert txt.startswith("<svg") and txt.rstrip().endswith("</svg>")
     assert "V1 Serial" in (out / "radar.svg").read_text()
     assert "n=2" in (out / "runtime_cv.svg").read_text()                       # V1 Serial np=1 has two runs
+
+
+def test_analysis_notebook_cells_execute(tmp_path, monkeypatch):
+    """analysis.ipynb (counterpart of the reference's notebook, generated by scripts/make_notebook.py) is valid
+    nbformat-4 JSON, is what the generator writes, and every code cell runs in order on a small log tree."""
+    import json
+    import subprocess
+    import sys
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    nb = json.load(open(os.path.join(repo, "analysis.ipynb")))
+    assert nb["nbformat"] == 4 and [c["cell_type"] for c in nb["cells"]].count("code") >= 8
+    fresh = tmp_path / "fresh.ipynb"
+    subprocess.run([sys.executable, os.path.join(repo, "scripts", "make_notebook.py"), str(fresh)], check=True,
+                   capture_output=True)
+    assert json.load(open(fresh)) == nb, "analysis.ipynb is stale: run python scripts/make_notebook.py"
+    root = _make_tree(tmp_path)
+    monkeypatch.setenv("B200_ANALYSIS_ROOT", repo)
+    monkeypatch.setenv("B200_ANALYSIS_LOGS", str(root))
+    monkeypatch.setenv("B200_ANALYSIS_OUT", str(tmp_path / "nb_out"))
+    env = {"__name__": "__notebook__"}
+    for c in nb["cells"]:
+        if c["cell_type"] == "code":
+            exec(compile("".join(c["source"]), "<analysis.ipynb>", "exec"), env)
+    out = tmp_path / "nb_out"
+    for f in ("best_runs.csv", "best_runs.md", "stats.csv", "all_runs.csv", "stats.parquet", "radar_table.csv"):
+        assert (out / f).stat().st_size > 0, f
+    plots = {p.name for p in (out / "plots").glob("*.svg")}
+    assert {"efficiency.svg", "runtime_cv.svg", "radar.svg"} <= plots and any(p.startswith("speedup_") for p in plots)
+    assert not env["top"].empty and not env["radar"].empty and "S" in env["sp_best"].columns
