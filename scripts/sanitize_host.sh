@@ -43,6 +43,12 @@ if [ -f /root/reference/homeworks/hw1/src/template.c ]; then
       -lpthread -lm -o "$OUT/hw1_asan"
   run python bin/mpirun --oversubscribe -np 2 "$OUT/hw1_asan" 128
 fi
+# 4. our own native HW1 (homeworks/hw1/src/template.c) on the sanitized shim and library sources, n = 128, np 1 / 4
+run gcc -std=c11 $SAN -Wall -Wextra -Werror -Iinclude -Ibaseline/mpishim -c homeworks/hw1/src/template.c -o "$OUT/hw1n_asan.o"
+run g++ -std=c++17 $SAN -fopenmp "$OUT/hw1n_asan.o" csrc/cpu/*.cpp "$OUT/mpishim_asan.o" -Iinclude -lpthread -lm -o "$OUT/hw1_native_asan"
+for np in 1 4; do
+  run python bin/mpirun --oversubscribe -np $np "$OUT/hw1_native_asan" 128
+done
 grep -c "ERROR: AddressSanitizer\|runtime error:" "$LOG" | sed 's/^/sanitizer reports: /'
 [ $fail -eq 0 ] && echo "sanitize_host: clean" || echo "sanitize_host: FAILURES (see $LOG)"
 exit $fail
