@@ -21,9 +21,11 @@ static void dims(const char* layer, int H, int W, int C) {
 int main(int argc, char** argv) {
     unsigned seed = (unsigned)time(nullptr);
     bool extras = true;
+    const char* load_weights = nullptr;
     for (int i = 1; i < argc; ++i) {
         if (!strcmp(argv[i], "--seed") && i + 1 < argc) seed = (unsigned)strtoul(argv[++i], nullptr, 10);
         else if (!strcmp(argv[i], "--quiet-extras")) extras = false;
+        else if (!strcmp(argv[i], "--load-weights") && i + 1 < argc) load_weights = argv[++i];
     }
     std::cout << "--- AlexNet Serial CPU Version (V1) ---" << std::endl;
     const int H = 227, W = 227, C = 3;
@@ -36,6 +38,18 @@ int main(int argc, char** argv) {
     b200_grand_fill_data(&st, x.data(), x.size());          // draw order: input, W1, W2
     b200_grand_fill_weights(&st, w1.data(), w1.size());
     b200_grand_fill_weights(&st, w2.data(), w2.size());
+    if (load_weights) {                        // parameters from a weight file (utils/checkpoint.py); input as drawn
+        struct { const char* name; std::vector<float>* t; } want[] = {{"w1", &w1}, {"b1", &b1}, {"w2", &w2}, {"b2", &b2}};
+        for (auto& q : want) {
+            size_t n = 0;
+            if (b200_weights_read(load_weights, q.name, nullptr, 0, &n, nullptr, nullptr) || n != q.t->size() ||
+                b200_weights_read(load_weights, q.name, q.t->data(), q.t->size(), &n, nullptr, nullptr)) {
+                std::cerr << "[Rank 0] --load-weights " << load_weights << ": cannot read " << q.name
+                          << " (missing file, wrong shape or checksum mismatch)" << std::endl;
+                return 1;
+            }
+        }
+    }
     std::cout << "Initialization complete." << std::endl;
 
     std::cout << "Starting AlexNet Serial Forward Pass..." << std::endl;

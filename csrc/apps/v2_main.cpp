@@ -29,6 +29,7 @@ struct Args {
     unsigned seed = 1;
     int lrn_mode = B200_LRN_ALPHA_OVER_N;
     int strategy = 0;        // 0 halo, 1 recompute
+    const char* load_weights = nullptr;    // a weight file written by the Python side (utils/checkpoint.py)
 };
 
 const int K1 = 96, F1 = 11, S1 = 4, P1 = 0, K2 = 256, F2 = 5, S2 = 1, P2 = 2, FP = 3, SP = 2;
@@ -58,6 +59,7 @@ Args parse(int argc, char** argv, int rank) {
         }
         else if (!strcmp(argv[i], "--strategy")) a.strategy = !strcmp(val("--strategy"), "recompute") ? 1 : 0;
         else if (!strcmp(argv[i], "--quiet-extras")) a.extras = false;
+        else if (!strcmp(argv[i], "--load-weights")) a.load_weights = val("--load-weights");
         else die(rank, (std::string("unknown argument ") + argv[i]).c_str());
     }
     if (a.H < F1 || a.W < F1 || a.batch < 1) die(rank, "bad --height / --width / --batch");
@@ -87,6 +89,16 @@ void init_problem(const Args& a, std::vector<float>& x, Weights& w) {
         std::fill(w.w2.begin(), w.w2.end(), 0.01f);
         w.b1.assign(K1, 0.f);
         w.b2.assign(K2, 0.f);
+    }
+    if (a.load_weights) {                      // parameters from a file; the input stays as initialised above
+        struct { const char* name; std::vector<float>* t; } want[] = {{"w1", &w.w1}, {"b1", &w.b1}, {"w2", &w.w2}, {"b2", &w.b2}};
+        for (auto& q : want) {
+            size_t n = 0;
+            const int rc = b200_weights_read(a.load_weights, q.name, nullptr, 0, &n, nullptr, nullptr);
+            if (rc || n != q.t->size() || b200_weights_read(a.load_weights, q.name, q.t->data(), q.t->size(), &n, nullptr, nullptr))
+                die(0, (std::string("--load-weights ") + a.load_weights + ": cannot read " + q.name +
+                        " (missing file, wrong shape or checksum mismatch)").c_str());
+        }
     }
 }
 

@@ -52,6 +52,21 @@ def native_plan_rank(cfg, world: int, rank: int, strategy: str = "halo", row_gro
     return out
 
 
+def native_weights_read(path: str, name: str) -> torch.Tensor:
+    """Tensor ``name`` of a weight file through the native reader (``b200_weights_read``): what a C/C++ host gets."""
+    n, nd = C.c_size_t(0), C.c_int(0)
+    shape = (C.c_int * 4)()
+    rc = lib().b200_weights_read(path.encode(), name.encode(), None, 0, C.byref(n), shape, C.byref(nd))
+    if rc != 0:
+        raise ValueError(f"b200_weights_read({path}, {name}) failed with status {rc}")
+    t = torch.empty(n.value, dtype=torch.float32)
+    rc = lib().b200_weights_read(path.encode(), name.encode(), C.c_void_p(t.data_ptr()), n.value, C.byref(n), shape,
+                                 C.byref(nd))
+    if rc != 0:
+        raise ValueError(f"b200_weights_read({path}, {name}) failed with status {rc}")
+    return t.view(*[shape[i] for i in range(nd.value)]) if nd.value else t
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -74,6 +89,8 @@ def lib():
         L.b200_hw1_init_data.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.b200_hw1_init_data.restype = None
         L.b200_hw1_check.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_double]
+        L.b200_weights_read.argtypes = [C.c_char_p, C.c_char_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t),
+                                        C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.b200_plan_rank.argtypes = [C.c_int, C.c_int, C.POINTER(PlanBlock), C.POINTER(PlanBlock), C.c_int, C.c_int,
                                      C.c_int, C.c_int, C.POINTER(RankPlanC)]
         _lib = L

@@ -104,6 +104,14 @@ typedef struct {
 int b200_plan_rank(int H, int batch, const b200_plan_block* b1, const b200_plan_block* b2, int world,
                    int strategy, int row_groups, int rank, b200_rank_plan* out);
 
+/* Weight files written by pkg/utils/checkpoint.py (save_weights): read tensor `name` ("w1", "b1", "w2", "b2", and
+ * "w3".."b8" in full-network files) into dst[capacity].  *count = its float count (also with dst == NULL, to size a
+ * buffer); shape[0..*ndim) when both are non-NULL (at most 4 dims).  B200_ERR_ARG: file cannot be opened;
+ * B200_ERR_UNSUPPORTED: not a weight file or no such tensor; B200_ERR_RANGE: buffer too small, truncated file, or the
+ * tensor's FNV-1a64 does not match the header. */
+int b200_weights_read(const char* path, const char* name, float* dst, size_t capacity, size_t* count,
+                      int* shape, int* ndim);
+
 /* HW1 (ref homeworks/hw1/src/template.c:195-238): C = A*B row block, init, check. */
 void b200_cpu_matmul_f64(const double* A, const double* B, double* C, int rows, int n);
 void b200_hw1_init_data(double* M, int rows, int cols);   /* fixed srand48(1) stream like init_data */

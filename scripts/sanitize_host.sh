@@ -17,6 +17,9 @@ run() { echo "\$ $*" >> "$LOG"; "$@" >> "$LOG" 2>&1; local rc=$?; echo "rc=$rc" 
 run g++ -std=c++17 $SAN -ffp-contract=off -fopenmp -Wall -Wextra -Werror -Iinclude \
     csrc/apps/v1_main.cpp csrc/cpu/*.cpp -o "$OUT/v1_asan"
 run "$OUT/v1_asan" --seed 7 --quiet-extras
+# ... and with parameters from a weight file through the native reader (csrc/cpu/weights_cpu.cpp)
+run env PYTHONPATH=. python -c "from b200cnn import default_config; from b200cnn.config import INIT_RAND; from b200cnn.models.init import make_problem; from b200cnn.utils.checkpoint import save_weights; save_weights('$OUT/w.b2w', make_problem(default_config(init=INIT_RAND, seed=5))[1])"
+run "$OUT/v1_asan" --seed 7 --quiet-extras --load-weights "$OUT/w.b2w"
 
 # 1b. native V2.2 / V2.1 (planner, slab layers, scatter / halo / gather over the MPI subset) at np 1 / 3 / 4
 run gcc $SAN -c -Wall -Wextra -Werror baseline/mpishim/mpishim.c -o "$OUT/mpishim_asan.o"

@@ -108,3 +108,42 @@ def test_v1_runner_saves_and_loads_weights(tmp_path):
     c = subprocess.run(base + ["--load-weights", str(tmp_path / "missing.b2w")], env=env, capture_output=True,
                        text=True, timeout=300)
     assert c.returncode != 0 and "missing.b2w" in (c.stderr + c.stdout)
+
+
+def test_native_reader_and_native_binaries_load_the_same_file(tmp_path):
+    """b200_weights_read (csrc/cpu/weights_cpu.cpp) returns what Python wrote, refuses a flipped bit, and the native
+    V1 / V2.2 binaries started with --load-weights print the checksum of the Python runner given the same file."""
+    from b200cnn.ops.cpu import native_weights_read
+    cfg = default_config(batch=1, init=INIT_RAND, seed=21)
+    _, w = make_problem(cfg)
+    path = str(tmp_path / "w.b2w")
+    ck.save_weights(path, w)
+    for k in ("w1", "b1", "w2", "b2"):
+        assert torch.equal(native_weights_read(path, k), getattr(w, k))
+    with pytest.raises(ValueError):
+        native_weights_read(path, "w9")
+    h = ck.read_header(path)
+    raw = bytearray(open(path, "rb").read())
+    raw[h["_data_start"] + h["tensors"][0]["offset"] + 8] ^= 0x10
+    bad = str(tmp_path / "bad.b2w")
+    open(bad, "wb").write(raw)
+    with pytest.raises(ValueError):
+        native_weights_read(bad, "w1")
+    # native binaries: V1 (seed 3 input, parameters from the file) == native V2.2 np 3 == Python V1 runner
+    fp = os.path.join(ROOT, "final_project")
+    for sub in ("v1_serial", "v2_mpi_only/2.2_scatter_halo"):
+        assert subprocess.run(["make"], cwd=os.path.join(fp, sub), capture_output=True, timeout=600).returncode == 0
+
+    def fnv(out):
+        return [l for l in out.splitlines() if "FNV1a64" in l]
+    a = subprocess.run([os.path.join(fp, "v1_serial", "template"), "--seed", "3", "--load-weights", path],
+                       capture_output=True, text=True, timeout=300)
+    b = subprocess.run([sys.executable, os.path.join(ROOT, "bin", "mpirun"), "--oversubscribe", "-np", "3",
+                        os.path.join(fp, "v2_mpi_only/2.2_scatter_halo", "template"), "--init", "rand", "--seed", "3",
+                        "--load-weights", path], capture_output=True, text=True, timeout=300)
+    c = subprocess.run([sys.executable, "-m", "b200cnn.runners.v1", "--init", "rand", "--seed", "3", "--load-weights", path],
+                       env=dict(os.environ, PYTHONPATH=ROOT), capture_output=True, text=True, timeout=300)
+    assert a.returncode == 0 and b.returncode == 0 and c.returncode == 0, (a.stderr, b.stderr, c.stderr)
+    assert fnv(a.stdout) and fnv(a.stdout) == fnv(b.stdout) == fnv(c.stdout)
+    d = subprocess.run([os.path.join(fp, "v1_serial", "template"), "--load-weights", bad], capture_output=True, text=True)
+    assert d.returncode != 0 and "--load-weights" in d.stderr
