@@ -224,17 +224,18 @@ class Orchestrator:
                  f"{row['OutputShape']}")
         return row
 
-    def run(self, max_np: int, single_node: bool = True):
+    def run(self, max_np: int, single_node: bool = True, np_list=None, variants=("2.1", "2.2")):
         total = sum(h.slots for h in self.hosts)
-        nps = [n for n in (1, 2, 4, 8) if n <= min(total, max_np)]
+        nps = [n for n in (np_list or (1, 2, 4, 8)) if n <= min(total, max_np)]
         self.log(f"--- suite: np in {nps} (total slots {total}) ---")
         if single_node:
             self.sh(f"cd {shlex.quote(REPO_ROOT)} && python -m b200cnn.harness.suite --session-prefix fullsuite "
                     f"--only 'V1 Serial,V3' --np 1", check=False)
         for n in nps:
-            for name, tag, mod in (("V2 2.1-broadcast-all", "v2_2_1_broadcast_all", "b200cnn.runners.v2_1"),
-                                   ("V2 2.2-scatter-halo", "v2_2_2_scatter_halo", "b200cnn.runners.v2_2")):
-                self.launch_multi_host(name, tag, mod, n)
+            for var, name, tag, mod in (("2.1", "V2 2.1-broadcast-all", "v2_2_1_broadcast_all", "b200cnn.runners.v2_1"),
+                                        ("2.2", "V2 2.2-scatter-halo", "v2_2_2_scatter_halo", "b200cnn.runners.v2_2")):
+                if var in variants:
+                    self.launch_multi_host(name, tag, mod, n)
         if single_node:
             self.sh(f"cd {shlex.quote(REPO_ROOT)} && python -m b200cnn.harness.suite --session-prefix fullsuite "
                     f"--only 'V4,V5' --np {','.join(str(n) for n in nps if n <= self.hosts[0].slots) or '1'}",
@@ -256,6 +257,8 @@ def main(argv=None) -> int:
     ap.add_argument("--multi-host-only", action="store_true",
                     help="skip the single-node parts of the suite (V1, V3, V4/V5 on the master)")
     ap.add_argument("--runner-args", default="", help="extra flags for the version runners, e.g. '--height 63 --width 63'")
+    ap.add_argument("--np", dest="np_list", default="", help="comma list of process counts (default 1,2,4,8 up to the slots)")
+    ap.add_argument("--variants", default="2.1,2.2", help="which multi-host versions to run")
     ap.add_argument("--timeout", type=int, default=900)
     ap.add_argument("--logs-root", default="")
     ns = ap.parse_args(argv)
@@ -270,7 +273,8 @@ def main(argv=None) -> int:
     o = Orchestrator(hosts, ns.dry_run, shared, os.environ.get("VERBOSE_RSYNC", "false") == "true", iface,
                      transport=ns.transport, timeout=ns.timeout, runner_args=ns.runner_args, logs_root=ns.logs_root)
     o.setup()
-    o.run(ns.max_np, single_node=not ns.multi_host_only)
+    o.run(ns.max_np, single_node=not ns.multi_host_only,
+          np_list=[int(v) for v in ns.np_list.split(",") if v] or None, variants=tuple(ns.variants.split(",")))
     bad = [r for r in o.rows if r.get("OverallStatusSymbol") != "✔"]
     return 1 if bad else 0
 

@@ -94,8 +94,9 @@ def test_multi_machine_local_transport_runs_two_nodes(tmp_path):
     """The multi-host path for real: two host entries = two torchrun agents on this box (nnodes 2, one rank each),
     V2.1 and V2.2 over gloo across them, workers started before the master, per-node logs, the 20-column CSV."""
     from b200cnn.harness import multi_machine as mm
-    rc = mm.main(["--hosts", "nodeA:100a:1,nodeB:100a:1", "--transport", "local", "--multi-host-only", "--max-np", "2",
-                  "--runner-args", "--height 63 --width 63", "--logs-root", str(tmp_path), "--timeout", "300"])
+    rc = mm.main(["--hosts", "nodeA:100a:1,nodeB:100a:1", "--transport", "local", "--multi-host-only", "--np", "1,2",
+                  "--variants", "2.2", "--runner-args", "--height 63 --width 63", "--logs-root", str(tmp_path),
+                  "--timeout", "300"])
     assert rc == 0
     sess = [d for d in os.listdir(tmp_path) if d.startswith("fullsuite_session_")]
     assert len(sess) == 1
@@ -105,8 +106,7 @@ def test_multi_machine_local_transport_runs_two_nodes(tmp_path):
     assert "run_v2_2_2_scatter_halo_np2.log" in names and "run_v2_2_2_scatter_halo_np2_node1.log" in names
     import csv
     rows = list(csv.DictReader(open(d / [n for n in names if n.startswith("summary_report_")][0])))
-    assert [(r["ProjectVariant"], r["NumProcesses"]) for r in rows] == [
-        ("V2 2.1-broadcast-all", "1"), ("V2 2.2-scatter-halo", "1"), ("V2 2.1-broadcast-all", "2"), ("V2 2.2-scatter-halo", "2")]
+    assert [(r["ProjectVariant"], r["NumProcesses"]) for r in rows] == [("V2 2.2-scatter-halo", "1"), ("V2 2.2-scatter-halo", "2")]
     assert all(r["OverallStatusSymbol"] == "✔" and r["OutputShape"] == "2x2x256" for r in rows)
     assert len({r["OutputFirst5Values"] for r in rows}) == 1          # np 2 over two agents == np 1
     assert "--nnodes 2 --node-rank 1" in open(d / "run_v2_2_2_scatter_halo_np2_node1.log").read()
