@@ -147,6 +147,10 @@ class Orchestrator:
         placed = self.placement(np_)
         master = "127.0.0.1" if self.transport == "local" else self.hosts[0].host
         port = 29555 + (len(self.rows) % 200)
+        if self.transport == "local" and not self.dry:       # one box: ask the kernel for a port nobody holds
+            with socket.socket() as sk:
+                sk.bind(("127.0.0.1", 0))
+                port = sk.getsockname()[1]
         env = f"GLOO_SOCKET_IFNAME={self.iface} " if self.iface else ""
         lines = []
         for node, (h, k) in enumerate(placed):
