@@ -86,5 +86,13 @@ class ClockSampler:
 
 
 def rejected(clocks: dict) -> bool:
-    bad = {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
-    return bool(bad & set(clocks.get("reasons", [])))
+    """A timed region must be measured again when the GPU was slowed down by hardware or thermals, or when its SM clock
+    sat well below the maximum for no stated reason (a leftover clock lock).  A software power cap is kept and
+    reported: that is the card's steady state under this load."""
+    reasons = set(clocks.get("reasons", []))
+    if reasons & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}:
+        return True
+    sm, top = clocks.get("sm_mhz"), clocks.get("sm_max_mhz")
+    if sm and top and sm < 0.8 * top and not (reasons & {"sw_power_cap", "hw_power_brake_slowdown"}):
+        return True
+    return False
