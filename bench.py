@@ -218,7 +218,7 @@ def run_ours(a):
             ctx.finalize()
             sys.exit(3)
     total_ms, launches, clocks = measure_device(sess)
-    if rejected(clocks):                                  # thermal/hw slowdown: re-measure once
+    if ctx.max_float(1.0 if rejected(clocks) else 0.0) > 0:   # any rank slowed down (or clock-locked): all re-measure, once
         total_ms, launches, clocks = measure_device(sess)
     clocks.pop("samples", None)
     host_binding = getattr(sess, "host_binding", None)
