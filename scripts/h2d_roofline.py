@@ -1,6 +1,8 @@
 """What the host links allow for the end-to-end number: every rank copies its share of one step's input
 (pinned host -> device) and of one step's result (device -> pinned host) at the same time as all other ranks,
-with nothing else running.  The aggregate rate is the ceiling of `e2e` in bench.py at that world size.
+with nothing else running: what the host links give a plain copy loop (one stream per direction and rank, copies back
+to back).  bench.py's `e2e` is bound by the same links; with three steps in flight it lands within a few percent of this
+number and at 8 GPUs slightly above it (the files under profiles/r2 call the field `e2e_ceiling_images_per_s`).
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port 29720 \
         scripts/h2d_roofline.py            (N = 1: plain `python scripts/h2d_roofline.py`)
@@ -62,7 +64,7 @@ def main():
             "aggregate_h2d_GBps": round(h2d, 1), "aggregate_d2h_GBps": round(d2h, 1),
             "aggregate_both_directions_GBps": round(both, 1),
             "step_ms_copies_only": round(res["both"] * 1e3, 4),
-            "e2e_ceiling_images_per_s": round(128 / res["both"], 1),
+            "copy_loop_images_per_s": round(128 / res["both"], 1),
             "note": "slowest rank, wall clock over %d back-to-back steps of copies, nothing else running" % reps}),
             flush=True)
     if world > 1:
